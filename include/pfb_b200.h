@@ -1,0 +1,117 @@
+/* pfb_b200 -- C-ABI of the B200-native pfb-imaging minor-cycle hot path.
+ *
+ * The reference (pfb-imaging v0.0.4, pure Python) has no FFI layer of its own:
+ * its hot path is Python callables over caller-owned numpy buffers whose
+ * arithmetic runs in ducc0 (C++), numba and numexpr.  Each entry point below
+ * replaces one of those callables; the reference interface it stands in for is
+ * cited as file:line relative to the reference tree.  INTEGRATION.md shows the
+ * ctypes binding a pfb-imaging maintainer would add.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer owned by the caller unless named *_host;
+ *  - arrays are C-contiguous; `dtype` is PFB_F32 or PFB_F64 (complex arrays are
+ *    interleaved re,im of that real type);
+ *  - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls
+ *    enqueue work and return without synchronising unless stated otherwise;
+ *  - return value is a pfb_status; pfb_last_error() gives the message of the
+ *    last failure on the calling thread;
+ *  - plans own only scratch memory; they are not re-entrant (like the
+ *    reference's shared xpad/xhat/xout scratch).
+ */
+#ifndef PFB_B200_H
+#define PFB_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    PFB_OK = 0,
+    PFB_ERR_BAD_ARG = 1,     /* null pointer, non-positive size, unknown enum */
+    PFB_ERR_ODD_SIZE = 2,    /* image sizes must be even (tests/test_wavelets.py:9-10) */
+    PFB_ERR_NLEVEL = 3,      /* ValueError of pfb/operators/psi.py:43-46 */
+    PFB_ERR_FFT_SIZE = 4,    /* padded size not supported by the FFT kernels */
+    PFB_ERR_CUDA = 5,        /* CUDA runtime error, see pfb_last_error() */
+    PFB_ERR_ALLOC = 6,
+    PFB_ERR_NBAND = 7        /* more bands than a kernel supports */
+} pfb_status;
+
+typedef enum { PFB_F32 = 0, PFB_F64 = 1 } pfb_dtype;
+
+/* cross-band reduction of the l21 prox: sum (prox_21m) or l2 norm (prox_21) */
+typedef enum { PFB_BAND_SUM = 0, PFB_BAND_L2 = 1 } pfb_band_mode;
+
+int pfb_version(void);
+const char *pfb_last_error(void);
+/* number of kernel launches issued by this library since load (bench.py's
+ * gpu_launches is the difference around the timed region) */
+long long pfb_launch_count(void);
+
+/* ------------------------------------------------------------------ prox --
+ * Coefficient arrays are (nband, n) with n = nbasis*Nymax*Nxmax flattened;
+ * weight is (n).  Scalar math is fp64 as in the reference's numba kernels.   */
+
+/* prox_21m_numba(v, result, lam, sigma, weight)  pfb/prox/prox_21m.py:30-61
+ * (mode PFB_BAND_SUM);  prox_21_numba  pfb/prox/prox_21.py:25-52 (PFB_BAND_L2) */
+int pfb_prox21(const void *v, void *result, const void *weight, int nband,
+               long long n, double lam, double sigma, int mode, int dtype,
+               void *stream);
+
+/* dual_update_numba(vp, v, lam, sigma, weight), in place on v
+ * pfb/prox/prox_21m.py:75-103 (PFB_BAND_SUM), pfb/prox/prox_21.py:66-91 (L2).
+ * If u != NULL additionally u = 2*v_new - vp, the numexpr line that follows
+ * it in primal_dual_optimised (pfb/opt/primal_dual.py:137); u may alias vp. */
+int pfb_dual_update(const void *vp, void *v, const void *weight, void *u,
+                    int nband, long long n, double lam, double sigma, int mode,
+                    int dtype, void *stream);
+
+/* Band-sharded split of the same update (the reference's distributed analogue
+ * is vtilde_update + get_ratio + update, pfb/opt/primal_dual.py:183-222):
+ *   partial: v <- vp + sigma*v ; bsum[k] = sum (or sum of squares) over the
+ *            LOCAL bands.  The caller all-reduces bsum (SUM) across ranks.
+ *   apply  : v <- v * (1 - max(a - lam w/sigma, 0)/a), a from bsum; u as above */
+int pfb_dual_partial(const void *vp, void *v, void *bsum, int nband, long long n,
+                     double sigma, int mode, int dtype, void *stream);
+int pfb_dual_apply(const void *vp, void *v, const void *bsum, const void *weight,
+                   void *u, int nband, long long n, double lam, double sigma,
+                   int mode, int dtype, void *stream);
+
+/* ------------------------------------------------- fused vector updates --
+ * Reductions accumulate in fp64 in a fixed order (bitwise reproducible) and
+ * write K doubles to a DEVICE buffer outK; they use one library-owned
+ * workspace, so issue them from one stream at a time.                        */
+
+/* out = a*x + b*y ('2.0*v - vp', 'xp - tau*xout' pfb/opt/primal_dual.py:137,140;
+ * axpys of pfb/opt/pcg.py:92-104) */
+int pfb_axpby(void *out, double a, const void *x, double b, const void *y,
+              long long n, int dtype, void *stream);
+/* out2 = {sum a*b, sum c*d} (c,d may both be NULL)  np.vdot in pfb/opt/pcg.py:76,91 */
+int pfb_vdot(const void *a, const void *b, const void *c, const void *d,
+             long long n, int dtype, double *out2, void *stream);
+/* out2 = {sum (x-xp)^2, sum x^2}; eps = sqrt(out2[0]/(1e-12+out2[1]))
+ * norm_diff  pfb/utils/misc.py:1316-1351 */
+int pfb_norm_diff(const void *x, const void *xp, long long n, int dtype,
+                  double *out2, void *stream);
+/* primal step of primal_dual_optimised, pfb/opt/primal_dual.py:139-150:
+ * x = P+(xp - tau*(xout + conv - data)), out2 as pfb_norm_diff.  conv/data may
+ * be NULL.  positivity: 0 none, 1 clamp, 2 zero pixel if any band <= 0. */
+int pfb_pd_primal(void *x, const void *xp, const void *xout, const void *conv,
+                  const void *data, double tau, int positivity, int nband,
+                  long long npix, int dtype, double *out2, void *stream);
+/* pcg line update, pfb/opt/pcg.py:92-101: x = xp + alpha p; r = rp + alpha Ap;
+ * out3 = {<r, minv*r>, sum (x-xp)^2, sum x^2} */
+int pfb_pcg_update(void *x, void *r, const void *xp, const void *rp, const void *p,
+                   const void *Ap, double alpha, double minv, long long n,
+                   int dtype, double *out3, void *stream);
+/* p = beta*p - minv*r ; out1 = {number of non-zero p}  pfb/opt/pcg.py:103-107 */
+int pfb_pcg_direction(void *p, const void *r, double beta, double minv,
+                      long long n, int dtype, double *out1, void *stream);
+
+/* @PSI@ */
+
+/* @HESS@ */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PFB_B200_H */

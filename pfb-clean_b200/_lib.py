@@ -1,0 +1,70 @@
+"""ctypes binding of libpfb_b200.so (the C-ABI declared in include/pfb_b200.h).
+
+There is no CPU fallback: if the shared library has not been built
+(``python -c 'import __graft_entry__ as g; g.build()'``) every operator raises.
+"""
+import ctypes
+import os
+from ctypes import c_int, c_longlong, c_double, c_void_p, c_char_p, POINTER
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "csrc", "libpfb_b200.so")
+
+F32, F64 = 0, 1
+BAND_SUM, BAND_L2 = 0, 1
+
+STATUS = {1: "bad argument", 2: "odd image size", 3: "nlevel too large",
+          4: "unsupported FFT size", 5: "CUDA error", 6: "allocation failed",
+          7: "too many bands"}
+
+
+class PfbError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"pfb_b200 status {status} ({STATUS.get(status, '?')}): {msg}")
+        self.status = status
+
+
+_P = c_void_p
+_SIGS = {
+    "pfb_version": (c_int, []),
+    "pfb_last_error": (c_char_p, []),
+    "pfb_launch_count": (c_longlong, []),
+    "pfb_prox21": (c_int, [_P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
+    "pfb_dual_update": (c_int, [_P, _P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
+    "pfb_dual_partial": (c_int, [_P, _P, _P, c_int, c_longlong, c_double, c_int, c_int, _P]),
+    "pfb_dual_apply": (c_int, [_P, _P, _P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
+    "pfb_axpby": (c_int, [_P, c_double, _P, c_double, _P, c_longlong, c_int, _P]),
+    "pfb_vdot": (c_int, [_P, _P, _P, _P, c_longlong, c_int, _P, _P]),
+    "pfb_norm_diff": (c_int, [_P, _P, c_longlong, c_int, _P, _P]),
+    "pfb_pd_primal": (c_int, [_P, _P, _P, _P, _P, c_double, c_int, c_int, c_longlong, c_int, _P, _P]),
+    "pfb_pcg_update": (c_int, [_P, _P, _P, _P, _P, _P, c_double, c_double, c_longlong, c_int, _P, _P]),
+    "pfb_pcg_direction": (c_int, [_P, _P, c_double, c_double, c_longlong, c_int, _P, _P]),
+}
+
+
+def bind(cdll):
+    """Attach prototypes for every symbol of include/pfb_b200.h."""
+    for name, (res, args) in _SIGS.items():
+        fn = getattr(cdll, name)      # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    return cdll
+
+
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(SO_PATH):
+            raise ImportError(
+                f"{SO_PATH} not found: build the CUDA library first "
+                "(__graft_entry__.build()); pfb_b200 has no CPU fallback")
+        _LIB = bind(ctypes.CDLL(SO_PATH))
+    return _LIB
+
+
+def check(status):
+    if status != 0:
+        raise PfbError(status, lib().pfb_last_error().decode())

@@ -1,0 +1,73 @@
+// Shared helpers for the pfb_b200 CUDA library (sm_100a only).
+#pragma once
+#include "../../include/pfb_b200.h"
+
+#ifndef PFB_EMU
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#endif
+#include <string>
+
+namespace pfb {
+
+extern thread_local std::string g_last_error;
+extern long long g_launch_count;
+
+int fail(int status, const char *fmt, ...);
+
+#ifndef PFB_EMU
+template <class... KA, class... A>
+static inline void pfb_launch(void (*k)(KA...), dim3 g, dim3 b, size_t smem,
+                              cudaStream_t st, A... a) {
+    k<<<g, b, smem, st>>>(a...);
+}
+#define PFB_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
+#else
+using ::pfb_launch;
+#endif
+
+// every kernel launch of the library goes through here (counted)
+template <class... KA, class... A>
+static inline void launch(void (*k)(KA...), dim3 g, dim3 b, size_t smem,
+                          cudaStream_t st, A... a) {
+    ++g_launch_count;
+    pfb_launch(k, g, b, smem, st, a...);
+}
+
+#define PFB_CUDA_OK(expr)                                                      \
+    do {                                                                       \
+        cudaError_t e__ = (expr);                                              \
+        if (e__ != cudaSuccess)                                                \
+            return pfb::fail(PFB_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,     \
+                             cudaGetErrorString(e__), __FILE__, __LINE__);     \
+    } while (0)
+
+#define PFB_CHECK_LAUNCH()                                                     \
+    do {                                                                       \
+        cudaError_t e__ = cudaPeekAtLastError();                               \
+        if (e__ != cudaSuccess)                                                \
+            return pfb::fail(PFB_ERR_CUDA, "kernel launch failed: %s (%s:%d)", \
+                             cudaGetErrorString(e__), __FILE__, __LINE__);     \
+    } while (0)
+
+static inline cudaStream_t as_stream(void *s) { return (cudaStream_t)s; }
+
+template <class T> struct vec2;
+template <> struct vec2<float> { typedef float2 type; };
+template <> struct vec2<double> { typedef double2 type; };
+
+static inline size_t dtype_size(int dtype) { return dtype == PFB_F64 ? 8 : 4; }
+
+static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
+
+// B200: 148 SMs.  Grid-stride kernels use a multiple of the SM count.
+#ifdef PFB_EMU
+static const int kNumSM = 2;  // CPU emulator (tests only): keep grids tiny
+#else
+static const int kNumSM = 148;
+#endif
+
+}  // namespace pfb
