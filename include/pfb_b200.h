@@ -107,7 +107,31 @@ int pfb_pcg_update(void *x, void *r, const void *xp, const void *rp, const void 
 int pfb_pcg_direction(void *p, const void *r, double beta, double minv,
                       long long n, int dtype, double *out1, void *stream);
 
-/* @PSI@ */
+/* ------------------------------------------------------------------- Psi --
+ * Multi-basis wavelet dictionary, pfb/operators/psi.py:269-310 (class Psi) over
+ * pfb/wavelets/wavelets.py dwt2d :174 / idwt2d :260.  basis_ids: 0 = 'self',
+ * N = 'dbN' (1..5).  Coefficients are (nband, nbasis, Nymax, Nxmax).         */
+typedef struct pfb_psi_plan pfb_psi_plan;
+/* Psi(nband, nx, ny, bases, nlevel, nthreads) + psi_band_maker
+ * pfb/operators/psi.py:17-123, :270-282.  PFB_ERR_NLEVEL mirrors the
+ * ValueError of psi.py:43-46, PFB_ERR_ODD_SIZE the even-size restriction. */
+int pfb_psi_plan_create(pfb_psi_plan **out, int nband, int nx, int ny, int nbasis,
+                        const int *basis_ids, int nlevel, int dtype);
+int pfb_psi_plan_destroy(pfb_psi_plan *plan);
+/* Psi.Nxmax / Psi.Nymax  pfb/operators/psi.py:281-282 */
+int pfb_psi_plan_query(const pfb_psi_plan *plan, int *Nxmax, int *Nymax);
+/* per-basis pyramid tables (host ints, 6*nlevel: highx, highy, sx, sy, spx, spy)
+ * = ix/iy/sx/sy/spx/spy of psi_band_maker, for tests and integration */
+int pfb_psi_plan_tables(const pfb_psi_plan *plan, int basis, int *tabs, int *Ntotx,
+                        int *Ntoty);
+/* Psi.dot(x, alphao): image -> coeffs; cells outside the pyramid blocks are
+ * left untouched exactly like the reference.  pfb/operators/psi.py:284-296 */
+int pfb_psi_dot(const pfb_psi_plan *plan, const void *x, void *alpha, void *stream);
+/* Psi.hdot(alpha, xo): coeffs -> image (sum over bases, xo overwritten)
+ * pfb/operators/psi.py:298-310.  If alpha2 != NULL the coefficients used are
+ * 2*alpha - alpha2 (fuses pfb/opt/primal_dual.py:137 into the loader). */
+int pfb_psi_hdot(const pfb_psi_plan *plan, const void *alpha, const void *alpha2,
+                 void *xo, void *stream);
 
 /* @HESS@ */
 
