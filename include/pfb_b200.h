@@ -133,7 +133,26 @@ int pfb_psi_dot(const pfb_psi_plan *plan, const void *x, void *alpha, void *stre
 int pfb_psi_hdot(const pfb_psi_plan *plan, const void *alpha, const void *alpha2,
                  void *xo, void *stream);
 
-/* @HESS@ */
+/* --------------------------------------------------------------- Hessian --
+ * psf_convolve_cube / psf_convolve_slice  pfb/operators/psf.py:32-56, :11-29
+ * hessian_psf_cube / _hessian_psf_slice   pfb/operators/hessian.py:254-281, :129-158
+ * x, out, beam: (nband, nx, ny) real; psfhat: (nband, nxp, nyp/2+1) complex,
+ * = r2c(ifftshift(psf)) as built by pfb/operators/gridder.py:712-714.
+ * The plan owns what the reference keeps in xpad/xhat (here: a pruned,
+ * transposed half-spectrum) and a transposed, 1/(nxp*nyp)-scaled copy of
+ * psfhat.  Padded sizes must be powers of two (PFB_ERR_FFT_SIZE otherwise).  */
+typedef struct pfb_hess_plan pfb_hess_plan;
+int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp,
+                         int nyp, int dtype);
+int pfb_hess_plan_destroy(pfb_hess_plan *plan);
+/* (re)load the PSF transfer function; call again whenever psfhat changes */
+int pfb_hess_plan_set_psfhat(pfb_hess_plan *plan, const void *psfhat, void *stream);
+/* out = conv(x)                                    beam NULL, add_x 0, has_wsum 0
+ * out = beam*conv(beam*x) [/wsum] + sigmainv*x     add_x 1
+ * out must not alias x. */
+int pfb_hess_apply(pfb_hess_plan *plan, const void *x, const void *beam, int add_x,
+                   double sigmainv, int has_wsum, double wsum, void *out,
+                   void *stream);
 
 #ifdef __cplusplus
 }

@@ -44,6 +44,10 @@ _SIGS = {
     "pfb_psi_plan_tables": (c_int, [_P, c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "pfb_psi_dot": (c_int, [_P, _P, _P, _P]),
     "pfb_psi_hdot": (c_int, [_P, _P, _P, _P, _P]),
+    "pfb_hess_plan_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_int, c_int, c_int]),
+    "pfb_hess_plan_destroy": (c_int, [_P]),
+    "pfb_hess_plan_set_psfhat": (c_int, [_P, _P, _P]),
+    "pfb_hess_apply": (c_int, [_P, _P, _P, c_int, c_double, c_int, c_double, _P, _P]),
     "pfb_pcg_direction": (c_int, [_P, _P, c_double, c_double, c_longlong, c_int, _P, _P]),
 }
 

@@ -1,0 +1,380 @@
+// Image-space PSF Hessian: zero-pad -> r2c -> x psfhat -> c2r -> crop, fused
+// into three shared-memory FFT passes (sm_100a).
+//
+// Reference: psf_convolve_cube pfb/operators/psf.py:32-56 (xpad = 0;
+// xpad[:, :nx, :ny] = x; r2c(axes=(1,2)); xhat *= psfhat; c2r(inorm=2,
+// lastsize=nyp); xout = xpad[:, :nx, :ny]) and hessian_psf_cube
+// pfb/operators/hessian.py:254-281 (beam prologue/epilogue, /wsum,
+// + sigmainv*x).  The padded image and the full half-spectrum are never
+// materialised:
+//   pass A  rows : the nx non-zero image rows only.  Row of ny reals (beam
+//                  fused) packed as nyp/2 complex, complex FFT, real-FFT
+//                  post-processing, stored TRANSPOSED: S[band][k][row].
+//   pass B  cols : for each of the nyo2 = nyp/2+1 columns: nx contiguous
+//                  points zero-extended to nxp, forward FFT, x psfhat^T
+//                  (pre-transposed, pre-scaled by 1/(nxp*nyp)), inverse FFT in
+//                  the same registers, first nx outputs stored in place.
+//   pass C  rows : the nx output rows only.  Transposed gather, real-FFT
+//                  pre-processing, inverse complex FFT, crop to ny, epilogue
+//                  (beam, /wsum, + sigmainv*x) fused into the store.
+// HBM traffic per band: x + out + psfhat^T + 4 x (nx x nyo2 complex) instead
+// of the reference's ~5 passes over the 4x larger padded arrays.
+#include "fft.cuh"
+#include <cmath>
+#include <vector>
+
+namespace pfb {
+
+template <class T> struct Epilogue {
+    const T *beam;   // nullable, (nband, nx, ny)
+    const T *x;      // nullable: adds sigmainv * x
+    T wsum;          // used if has_wsum
+    T sigmainv;
+    int has_wsum;
+};
+
+struct HessDims {
+    int nband, nx, ny, nxp, nyp, nyo2, M;   // M = nyp/2
+    int twN;                                 // twiddle table length
+    int R;                                   // rows (or columns) per CTA
+};
+
+// ------------------------------------------------------------------ pass A
+template <class T, int MAXT>
+__global__ void __launch_bounds__(MAXT) k_hess_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam,
+                                Cx<T> *__restrict__ S, const Cx<T> *__restrict__ tw,
+                                FftDesc d, HessDims h) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *smem = reinterpret_cast<Cx<T> *>(raw);
+    const int NT = d.NT, M = h.M;
+    const int stride = fft_smem_elems(M);
+    const int lr = threadIdx.x / NT, t = threadIdx.x - lr * NT;
+    const int band = blockIdx.y;
+    const int row = blockIdx.x * h.R + lr;
+    Cx<T> *buf = smem + (long)lr * stride;
+
+    Cx<T> v[16];
+    const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        int c0 = 2 * (t + e * NT);
+        T a = (T)0, b = (T)0;
+        if (row < h.nx) {
+            if (c0 < h.ny) { a = x[ro + c0]; if (beam) a *= beam[ro + c0]; }
+            if (c0 + 1 < h.ny) { b = x[ro + c0 + 1]; if (beam) b *= beam[ro + c0 + 1]; }
+        }
+        v[e] = cx<T>(a, b);
+    }
+    fft_run<T, -1>(v, d, t, buf, tw);
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 16; ++e) buf[fft_pad(t + e * NT)] = v[e];
+    __syncthreads();
+
+    // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
+    const int twm = h.twN / h.nyp;
+    for (int i = threadIdx.x; i < (M + 1) * h.R; i += blockDim.x) {
+        int k = i / h.R, l2 = i - k * h.R;
+        int row2 = blockIdx.x * h.R + l2;
+        const Cx<T> *b2 = smem + (long)l2 * stride;
+        Cx<T> zk = b2[fft_pad(k & (M - 1))], zm = cconj(b2[fft_pad((M - k) & (M - 1))]);
+        Cx<T> E = cx<T>((T)0.5 * (zk.x + zm.x), (T)0.5 * (zk.y + zm.y));
+        Cx<T> D = cx<T>((T)0.5 * (zk.x - zm.x), (T)0.5 * (zk.y - zm.y));
+        Cx<T> O = cx<T>(D.y, -D.x);
+        Cx<T> X = E + cmul(tw[(long)k * twm], O);
+        if (row2 < h.nx) S[((long)band * h.nyo2 + k) * h.nx + row2] = X;
+    }
+}
+
+// ------------------------------------------------------------------ pass B
+template <class T, int MAXT>
+__global__ void __launch_bounds__(MAXT) k_hess_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT,
+                            const Cx<T> *__restrict__ tw, FftDesc d, HessDims h) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *smem = reinterpret_cast<Cx<T> *>(raw);
+    const int NT = d.NT;
+    const int lc = threadIdx.x / NT, t = threadIdx.x - lc * NT;
+    const int band = blockIdx.y;
+    const int col = blockIdx.x * h.R + lc;
+    const bool live = col < h.nyo2;
+    Cx<T> *buf = smem + (long)lc * fft_smem_elems(h.nxp);
+    Cx<T> *line = S + ((long)band * h.nyo2 + (live ? col : 0)) * h.nx;
+    const Cx<T> *pl = psfT + ((long)band * h.nyo2 + (live ? col : 0)) * h.nxp;
+
+    Cx<T> v[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        int i = t + e * NT;
+        v[e] = (live && i < h.nx) ? line[i] : cx<T>((T)0, (T)0);
+    }
+    fft_run<T, -1>(v, d, t, buf, tw);
+#pragma unroll
+    for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], pl[t + e * NT]);
+    fft_run<T, +1>(v, d, t, buf, tw);
+    if (live) {
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            int i = t + e * NT;
+            if (i < h.nx) line[i] = v[e];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ pass C
+template <class T, int MAXT>
+__global__ void __launch_bounds__(MAXT) k_hess_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
+                                const Cx<T> *__restrict__ tw, FftDesc d, HessDims h,
+                                Epilogue<T> ep) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *smem = reinterpret_cast<Cx<T> *>(raw);
+    const int NT = d.NT, M = h.M;
+    const int stride = fft_smem_elems(M);
+    const int lr = threadIdx.x / NT, t = threadIdx.x - lr * NT;
+    const int band = blockIdx.y;
+    const int row = blockIdx.x * h.R + lr;
+    Cx<T> *buf = smem + (long)lr * stride;
+
+    for (int i = threadIdx.x; i < (M + 1) * h.R; i += blockDim.x) {
+        int k = i / h.R, l2 = i - k * h.R;
+        int row2 = blockIdx.x * h.R + l2;
+        Cx<T> X = cx<T>((T)0, (T)0);
+        if (row2 < h.nx) X = S[((long)band * h.nyo2 + k) * h.nx + row2];
+        smem[(long)l2 * stride + fft_pad(k)] = X;
+    }
+    __syncthreads();
+
+    // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m])
+    const int twm = h.twN / h.nyp;
+    Cx<T> v[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        int m = t + e * NT;
+        Cx<T> xm = buf[fft_pad(m)], xr = cconj(buf[fft_pad(M - m)]);
+        Cx<T> A = xm + xr, B = xm - xr;
+        Cx<T> wB = cmul(cconj(tw[(long)m * twm]), B);
+        v[e] = cx<T>(A.x - wB.y, A.y + wB.x);
+    }
+    fft_run<T, +1>(v, d, t, buf, tw);
+
+    if (row < h.nx) {
+        const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            int c0 = 2 * (t + e * NT);
+            T val[2] = {v[e].x, v[e].y};
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                int c = c0 + q;
+                if (c < h.ny) {
+                    T o = val[q];
+                    if (ep.beam) o *= ep.beam[ro + c];
+                    if (ep.has_wsum) o /= ep.wsum;
+                    if (ep.x) o += ep.x[ro + c] * ep.sigmainv;
+                    out[ro + c] = o;
+                }
+            }
+        }
+    }
+}
+
+// psfhat (nband, nxp, nyo2) -> psfT (nband, nyo2, nxp) * scale
+template <class T>
+__global__ void k_psfhat_prepare(const Cx<T> *__restrict__ in, Cx<T> *__restrict__ out,
+                                 int nxp, int nyo2, T scale) {
+    __shared__ Cx<T> tile[32][33];
+    int band = blockIdx.z;
+    const Cx<T> *src = in + (long)band * nxp * nyo2;
+    Cx<T> *dst = out + (long)band * nxp * nyo2;
+    int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        int r = r0 + i, c = c0 + threadIdx.x;
+        if (r < nxp && c < nyo2) tile[i][threadIdx.x] = src[(long)r * nyo2 + c];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        int c = c0 + i, r = r0 + threadIdx.x;
+        if (r < nxp && c < nyo2) {
+            Cx<T> v = tile[threadIdx.x][i];
+            dst[(long)c * nxp + r] = cx<T>(v.x * scale, v.y * scale);
+        }
+    }
+}
+
+}  // namespace pfb
+
+struct pfb_hess_plan {
+    int dtype;
+    pfb::HessDims h;
+    pfb::FftDesc drow, dcol;
+    int Rrow, Rcol;          // lines per CTA in the row / column passes
+    void *tw;                // twN complex twiddles exp(-2 pi i m / twN)
+    void *S;                 // (nband, nyo2, nx) complex scratch
+    void *psfT;              // (nband, nyo2, nxp) complex, scaled
+    int have_psf;
+};
+
+namespace pfb {
+
+static const size_t kMaxSmem = 200 * 1024;
+
+// kernels are compiled for several block-size caps so that the register
+// allocation always fits (1024 threads -> 64 regs, 512 -> 128, <= 256 -> 255)
+#define PFB_LAUNCH_T(MAXT, KERN, smem, grid, nthr, st, ...)                                   \
+    do {                                                                                       \
+        PFB_CUDA_OK(cudaFuncSetAttribute(&KERN<T, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); \
+        launch(&KERN<T, MAXT>, grid, dim3(nthr), smem, st, __VA_ARGS__);                       \
+        PFB_CHECK_LAUNCH();                                                                    \
+    } while (0)
+#define PFB_BY_THREADS(nthr, KERN, smem, grid, st, ...)                                       \
+    do {                                                                                       \
+        if ((nthr) <= 256) PFB_LAUNCH_T(256, KERN, smem, grid, nthr, st, __VA_ARGS__);         \
+        else if ((nthr) <= 512) PFB_LAUNCH_T(512, KERN, smem, grid, nthr, st, __VA_ARGS__);    \
+        else PFB_LAUNCH_T(1024, KERN, smem, grid, nthr, st, __VA_ARGS__);                      \
+    } while (0)
+
+template <class T>
+static int hess_set_psf_t(pfb_hess_plan *p, const void *psfhat, cudaStream_t st) {
+    const HessDims &h = p->h;
+    dim3 grid(cdiv(h.nyo2, 32), cdiv(h.nxp, 32), h.nband), block(32, 8);
+    T scale = (T)(1.0 / ((double)h.nxp * (double)h.nyp));
+    launch(&k_psfhat_prepare<T>, grid, block, 0, st, (const Cx<T> *)psfhat, (Cx<T> *)p->psfT,
+           h.nxp, h.nyo2, scale);
+    PFB_CHECK_LAUNCH();
+    p->have_psf = 1;
+    return PFB_OK;
+}
+
+template <class T>
+static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T *beam_out,
+                        const T *addx, double sigmainv, int has_wsum, double wsum, T *out,
+                        cudaStream_t st) {
+    const HessDims &h0 = p->h;
+    const Cx<T> *tw = (const Cx<T> *)p->tw;
+    Cx<T> *S = (Cx<T> *)p->S;
+    {
+        HessDims h = h0;
+        h.R = p->Rrow;
+        size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.M) * h.R;
+        int nthr = p->drow.NT * h.R;
+        PFB_BY_THREADS(nthr, k_hess_rows_fwd, smem, dim3(cdiv(h.nx, h.R), h.nband), st,
+                       x, beam_in, S, tw, p->drow, h);
+    }
+    {
+        HessDims h = h0;
+        h.R = p->Rcol;
+        size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.nxp) * h.R;
+        int nthr = p->dcol.NT * h.R;
+        PFB_BY_THREADS(nthr, k_hess_cols, smem, dim3(cdiv(h.nyo2, h.R), h.nband), st,
+                       S, (const Cx<T> *)p->psfT, tw, p->dcol, h);
+    }
+    {
+        HessDims h = h0;
+        h.R = p->Rrow;
+        size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.M) * h.R;
+        Epilogue<T> ep;
+        ep.beam = beam_out;
+        ep.x = addx;
+        ep.wsum = (T)wsum;
+        ep.sigmainv = (T)sigmainv;
+        ep.has_wsum = has_wsum;
+        int nthr = p->drow.NT * h.R;
+        PFB_BY_THREADS(nthr, k_hess_rows_inv, smem, dim3(cdiv(h.nx, h.R), h.nband), st,
+                       (const Cx<T> *)S, out, tw, p->drow, h, ep);
+    }
+    return PFB_OK;
+}
+
+// lines per CTA: fill up to 1024 threads / kMaxSmem, capped at `want`
+static int lines_per_cta(int NT, int N, size_t csize, int want) {
+    int r = want;
+    while (r > 1 && (NT * r > 1024 || csize * fft_smem_elems(N) * r > kMaxSmem)) r >>= 1;
+    return r;
+}
+
+}  // namespace pfb
+
+using namespace pfb;
+
+extern "C" {
+
+int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp, int nyp,
+                         int dtype) {
+    if (!out || nband < 1 || nx < 1 || ny < 1 || nxp < nx || nyp < ny ||
+        (dtype != PFB_F32 && dtype != PFB_F64))
+        return fail(PFB_ERR_BAD_ARG, "pfb_hess_plan_create: bad argument");
+    size_t cs = 2 * dtype_size(dtype);
+    int M = nyp / 2;
+    bool ok = (nyp % 2 == 0) && M >= 16 && !(M & (M - 1)) && nxp >= 16 && !(nxp & (nxp - 1)) &&
+              M / 16 <= 1024 && nxp / 16 <= 1024 &&
+              cs * fft_smem_elems(M) <= kMaxSmem && cs * fft_smem_elems(nxp) <= kMaxSmem;
+    if (!ok)
+        return fail(PFB_ERR_FFT_SIZE,
+                    "padded size (%d,%d) unsupported: need powers of two, nxp in [16,16384], "
+                    "nyp in [32,32768] and one line within %zu KB of shared memory",
+                    nxp, nyp, kMaxSmem / 1024);
+    pfb_hess_plan *p = new pfb_hess_plan();
+    memset(p, 0, sizeof *p);
+    p->dtype = dtype;
+    HessDims &h = p->h;
+    h.nband = nband; h.nx = nx; h.ny = ny; h.nxp = nxp; h.nyp = nyp;
+    h.nyo2 = nyp / 2 + 1; h.M = M;
+    h.twN = std::max(nxp, nyp);
+    fft_make_desc(M, h.twN, p->drow);
+    fft_make_desc(nxp, h.twN, p->dcol);
+    // rows: R lines so that the transposed scratch is written in >= 32 B runs
+    p->Rrow = lines_per_cta(p->drow.NT, M, cs, dtype == PFB_F32 ? 4 : 2);
+    if (p->drow.NT * p->Rrow < 128) p->Rrow = lines_per_cta(p->drow.NT, M, cs, 128 / p->drow.NT);
+    p->Rcol = lines_per_cta(p->dcol.NT, nxp, cs, std::max(1, 256 / p->dcol.NT));
+    std::vector<char> twh(cs * h.twN);
+    for (int m = 0; m < h.twN; ++m) {
+        long double a = -2.0L * 3.14159265358979323846264338327950288L * (long double)m / (long double)h.twN;
+        double c = (double)cosl(a), s = (double)sinl(a);
+        if (dtype == PFB_F32) { ((float *)twh.data())[2 * m] = (float)c; ((float *)twh.data())[2 * m + 1] = (float)s; }
+        else { ((double *)twh.data())[2 * m] = c; ((double *)twh.data())[2 * m + 1] = s; }
+    }
+    size_t sS = cs * (size_t)nband * h.nyo2 * nx, sP = cs * (size_t)nband * h.nyo2 * nxp;
+    if (cudaMalloc(&p->tw, twh.size()) != cudaSuccess || cudaMalloc(&p->S, sS) != cudaSuccess ||
+        cudaMalloc(&p->psfT, sP) != cudaSuccess) {
+        if (p->tw) cudaFree(p->tw);
+        if (p->S) cudaFree(p->S);
+        delete p;
+        return fail(PFB_ERR_ALLOC, "hessian plan allocation failed (%zu + %zu bytes)", sS, sP);
+    }
+    if (cudaMemcpy(p->tw, twh.data(), twh.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaFree(p->tw); cudaFree(p->S); cudaFree(p->psfT);
+        delete p;
+        return fail(PFB_ERR_CUDA, "twiddle upload failed");
+    }
+    *out = p;
+    return PFB_OK;
+}
+
+int pfb_hess_plan_destroy(pfb_hess_plan *p) {
+    if (!p) return PFB_OK;
+    cudaFree(p->tw); cudaFree(p->S); cudaFree(p->psfT);
+    delete p;
+    return PFB_OK;
+}
+
+int pfb_hess_plan_set_psfhat(pfb_hess_plan *p, const void *psfhat, void *stream) {
+    if (!p || !psfhat) return fail(PFB_ERR_BAD_ARG, "pfb_hess_plan_set_psfhat: null argument");
+    if (p->dtype == PFB_F32) return hess_set_psf_t<float>(p, psfhat, as_stream(stream));
+    return hess_set_psf_t<double>(p, psfhat, as_stream(stream));
+}
+
+int pfb_hess_apply(pfb_hess_plan *p, const void *x, const void *beam, int add_x,
+                   double sigmainv, int has_wsum, double wsum, void *out, void *stream) {
+    if (!p || !x || !out) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply: null argument");
+    if (!p->have_psf) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply: psfhat not set");
+    if (x == out) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply: out must not alias x");
+    cudaStream_t st = as_stream(stream);
+    if (p->dtype == PFB_F32)
+        return hess_apply_t<float>(p, (const float *)x, (const float *)beam, (const float *)beam,
+                                   add_x ? (const float *)x : nullptr, sigmainv, has_wsum, wsum,
+                                   (float *)out, st);
+    return hess_apply_t<double>(p, (const double *)x, (const double *)beam, (const double *)beam,
+                                add_x ? (const double *)x : nullptr, sigmainv, has_wsum, wsum,
+                                (double *)out, st);
+}
+
+}  // extern "C"

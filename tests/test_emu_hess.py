@@ -1,0 +1,94 @@
+"""hess.cu / fft.cuh (three-pass FFT Hessian) on the CPU emulator vs the
+reference's golden vectors, the oracle and a direct-summation known answer."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from oracle import ref
+from conftest import golden
+from emu.emulib import emu, ptr, ok
+
+pmp = pytest.mark.parametrize
+
+
+def rel(a, b):
+    return np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300)
+
+
+class EmuHess:
+    def __init__(self, nband, nx, ny, nxp, nyp, dtype):
+        self.L = emu()
+        self.plan = ctypes.c_void_p()
+        self.rc = self.L.pfb_hess_plan_create(ctypes.byref(self.plan), nband, nx, ny, nxp, nyp,
+                                              0 if dtype == np.float32 else 1)
+
+    def set_psfhat(self, psfhat):
+        ok(self.L.pfb_hess_plan_set_psfhat(self.plan, ptr(np.ascontiguousarray(psfhat)), None))
+
+    def apply(self, x, beam=None, add_x=0, sigmainv=0.0, wsum=None):
+        out = np.full(x.shape, np.nan, x.dtype)
+        ok(self.L.pfb_hess_apply(self.plan, ptr(x), ptr(beam), add_x, sigmainv,
+                                 int(wsum is not None), float(wsum or 0.0), ptr(out), None))
+        return out
+
+    def __del__(self):
+        if self.rc == 0:
+            self.L.pfb_hess_plan_destroy(self.plan)
+
+
+@pmp("tag", ["hess_f64", "hess_f32", "hess_f64_rect"])
+def test_hess_golden(tag):
+    g = golden(tag)
+    x, psfhat, beam = g["x"], g["psfhat"], g["beam"]
+    nband, nx, ny = x.shape
+    nxp, nyp = psfhat.shape[1], g["psf"].shape[2]
+    H = EmuHess(nband, nx, ny, nxp, nyp, x.dtype.type)
+    assert H.rc == 0
+    H.set_psfhat(psfhat)
+    tol = 1e-13 if x.dtype == np.float64 else 1e-6
+    assert rel(H.apply(x), g["conv"]) < tol
+    assert rel(H.apply(x, None, 1, 1e-3), g["h1"]) < tol
+    assert rel(H.apply(x, beam, 1, 0.25, 3.5), g["h2"]) < tol
+
+
+@pmp("dtype", [np.float32, np.float64])
+@pmp("nx,ny,nxp,nyp", [(8, 6, 16, 32), (20, 40, 64, 128), (100, 64, 256, 128), (30, 200, 32, 512),
+                             (6, 10, 4096, 64), (4, 10, 16, 8192), (5, 4, 8192, 32)])
+def test_hess_oracle(dtype, nx, ny, nxp, nyp):
+    rng = np.random.default_rng(11)
+    nband = 2
+    cdt = np.complex64 if dtype == np.float32 else np.complex128
+    psf = rng.standard_normal((nband, nxp, nyp))
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2)).astype(cdt)
+    x = rng.standard_normal((nband, nx, ny)).astype(dtype)
+    H = EmuHess(nband, nx, ny, nxp, nyp, dtype)
+    assert H.rc == 0
+    H.set_psfhat(psfhat)
+    xpad = np.empty((nband, nxp, nyp), dtype)
+    xhat = np.empty(psfhat.shape, cdt)
+    xout = np.empty(x.shape, dtype)
+    exp = ref.psf_convolve_cube(xpad, xhat, xout, psfhat, nyp, x)
+    assert rel(H.apply(x), exp) < (1e-13 if dtype == np.float64 else 1e-6)
+
+
+def test_hess_delta_kat():
+    """x = delta at (p,q)  =>  out[i,j] = psf[nxp//2+i-p, nyp//2+j-q]."""
+    rng = np.random.default_rng(12)
+    nx, ny, nxp, nyp = 16, 16, 32, 32
+    psf = rng.standard_normal((1, nxp, nyp))
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2))
+    H = EmuHess(1, nx, ny, nxp, nyp, np.float64)
+    H.set_psfhat(psfhat)
+    x = np.zeros((1, nx, ny))
+    p, q = 5, 11
+    x[0, p, q] = 1.0
+    out = H.apply(x)
+    ii, jj = np.meshgrid(np.arange(nx), np.arange(ny), indexing="ij")
+    assert np.abs(out[0] - psf[0, nxp // 2 + ii - p, nyp // 2 + jj - q]).max() < 1e-13
+
+
+def test_hess_plan_errors():
+    assert EmuHess(1, 8, 8, 24, 32, np.float64).rc == 4      # not a power of two
+    assert EmuHess(1, 8, 8, 16, 16, np.float64).rc == 4      # nyp/2 < 16
+    assert EmuHess(1, 40, 8, 32, 32, np.float64).rc == 1     # image larger than PSF
