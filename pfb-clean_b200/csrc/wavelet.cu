@@ -436,8 +436,27 @@ static void fill_common(const pfb_psi_plan *p, LevelArgs &a, int level) {
     a.ny = p->ny;
 }
 
+// level ping-pong scratch, allocated lazily so that a plan used only for size
+// queries (or only in the other precision) costs nothing
+static int ensure_scratch(const pfb_psi_plan *cp) {
+    pfb_psi_plan *p = const_cast<pfb_psi_plan *>(cp);
+    if (p->nlevel < 2 || p->scrA) return PFB_OK;
+    size_t bytes = dtype_size(p->dtype) * (size_t)p->scr_stride * p->nband * p->nbasis;
+    if (cudaMalloc(&p->scrA, bytes) != cudaSuccess) {
+        p->scrA = nullptr;
+        return fail(PFB_ERR_ALLOC, "psi plan scratch allocation failed (%zu bytes x2)", bytes);
+    }
+    if (cudaMalloc(&p->scrB, bytes) != cudaSuccess) {
+        cudaFree(p->scrA);
+        p->scrA = p->scrB = nullptr;
+        return fail(PFB_ERR_ALLOC, "psi plan scratch allocation failed (%zu bytes x2)", bytes);
+    }
+    return PFB_OK;
+}
+
 template <class T>
 static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t st) {
+    if (int rc = ensure_scratch(p)) return rc;
     size_t smem = sizeof(T) * kAnaSmemElems;
     PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_level<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     T *A = (T *)p->scrA, *B = (T *)p->scrB;
@@ -483,6 +502,7 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t s
 template <class T>
 static int psi_hdot_t(const pfb_psi_plan *p, const T *alpha, const T *alpha2, T *xo,
                       cudaStream_t st) {
+    if (int rc = ensure_scratch(p)) return rc;
     size_t smem = sizeof(T) * kSynSmemElems;
     PFB_CUDA_OK(cudaFuncSetAttribute(&k_idwt_level<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     T *A = (T *)p->scrA, *B = (T *)p->scrB;
@@ -578,15 +598,7 @@ int pfb_psi_plan_create(pfb_psi_plan **out, int nband, int nx, int ny, int nbasi
         delete p;
         return fail(PFB_ERR_BAD_ARG, "at least one wavelet basis is required");
     }
-    p->scr_stride = scr;
-    if (nlevel > 1) {
-        size_t bytes = dtype_size(dtype) * (size_t)scr * nband * nbasis;
-        if (cudaMalloc(&p->scrA, bytes) != cudaSuccess || cudaMalloc(&p->scrB, bytes) != cudaSuccess) {
-            if (p->scrA) cudaFree(p->scrA);
-            delete p;
-            return fail(PFB_ERR_ALLOC, "psi plan scratch allocation failed (%zu bytes x2)", bytes);
-        }
-    }
+    p->scr_stride = scr;   // scratch itself is allocated on first use
     *out = p;
     return PFB_OK;
 }

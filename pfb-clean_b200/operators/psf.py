@@ -1,0 +1,114 @@
+"""Drop-in for pfb/operators/psf.py (psf_convolve_slice :11-29,
+psf_convolve_cube :32-56) on top of the three-pass FFT Hessian kernels
+(csrc/hess.cu) through the C-ABI of include/pfb_b200.h.
+
+The reference's caller-owned scratch arrays `xpad` / `xhat` are accepted and
+ignored (pass None to save the memory): the padded image and full half-spectrum
+are never materialised on the GPU.  As in the reference the result is written
+into, and returned as, the caller's `xout`.
+"""
+import ctypes
+import weakref
+
+import torch
+
+from .. import _dev, _lib
+
+
+class HessPlan:
+    """RAII wrapper of pfb_hess_plan bound to one psfhat."""
+
+    def __init__(self, nband, nx, ny, nxp, nyp, dtype_code):
+        self._h = ctypes.c_void_p()
+        self._destroy = _lib.lib().pfb_hess_plan_destroy
+        _lib.check(_lib.lib().pfb_hess_plan_create(ctypes.byref(self._h), nband, nx, ny,
+                                                   nxp, nyp, dtype_code))
+        self.shape = (nband, nx, ny, nxp, nyp, dtype_code)
+        self.psf_key = None
+
+    def set_psfhat(self, psfhat_dev):
+        _lib.check(_lib.lib().pfb_hess_plan_set_psfhat(self._h, _dev.ptr(psfhat_dev), _dev.stream()))
+
+    def apply(self, x, out, beam=None, add_x=False, sigmainv=0.0, wsum=None):
+        _lib.check(_lib.lib().pfb_hess_apply(
+            self._h, _dev.ptr(x), _dev.ptr(beam), int(add_x), float(sigmainv),
+            int(wsum is not None), float(wsum) if wsum is not None else 0.0,
+            _dev.ptr(out), _dev.stream()))
+        return out
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+
+_PLANS = {}
+
+
+def _psf_key(psfhat):
+    if isinstance(psfhat, torch.Tensor):
+        return ("t", psfhat.data_ptr(), tuple(psfhat.shape), psfhat._version)
+    return ("n", psfhat.ctypes.data, psfhat.shape, psfhat.strides)
+
+
+def clear_plan_cache():
+    """Drop cached plans (call after modifying a psfhat array in place)."""
+    _PLANS.clear()
+
+
+def get_plan(psfhat, lastsize, x_shape, x_dtype_code):
+    """Plan for (shape, psfhat).  The transposed/scaled device copy of psfhat is
+    built once per psfhat object and reused by every later call."""
+    if len(x_shape) == 2:
+        nband, (nx, ny) = 1, x_shape
+    else:
+        nband, nx, ny = x_shape
+    nxp = psfhat.shape[-2]
+    if psfhat.shape[-1] != lastsize // 2 + 1:
+        raise ValueError(f"psfhat last axis {psfhat.shape[-1]} != lastsize//2+1 = {lastsize // 2 + 1}")
+    key = (nband, nx, ny, nxp, lastsize, x_dtype_code)
+    plan = _PLANS.get(key)
+    if plan is None:
+        plan = HessPlan(*key)
+        _PLANS[key] = plan
+    pk = _psf_key(psfhat)
+    if plan.psf_key != pk:
+        pd = _dev.to_dev(psfhat)
+        if _dev.dcode(pd) != x_dtype_code:
+            raise TypeError("psfhat precision does not match the image precision")
+        plan.set_psfhat(pd)
+        plan.psf_key = pk
+        plan._keep = psfhat      # keep the id()/data_ptr key valid
+    return plan
+
+
+def _convolve(psfhat, lastsize, x, xout, beam=None, add_x=False, sigmainv=0.0, wsum=None):
+    # like the reference (`xpad[...] = x`, xpad/xhat in the precision of the
+    # PSF) the transform runs in the precision of psfhat; x is cast if needed
+    rdt = torch.float32 if str(psfhat.dtype).endswith("complex64") else torch.float64
+    xd = _dev.to_dev(x)
+    if xd.dtype != rdt:
+        xd = xd.to(rdt)
+    plan = get_plan(psfhat, lastsize, tuple(xd.shape), _dev.dcode(xd))
+    od = _dev.out_dev(xout)
+    direct = od.dtype == rdt
+    res = od if direct else torch.empty(xd.shape, dtype=rdt, device=xd.device)
+    if res.data_ptr() == xd.data_ptr():
+        xd = xd.clone()
+    bd = _dev.to_dev(beam) if beam is not None else None
+    if bd is not None and bd.dtype != rdt:
+        bd = bd.to(rdt)
+    plan.apply(xd, res, bd, add_x, sigmainv, wsum)
+    if not direct:
+        od.copy_(res)
+    return _dev.to_out(od, xout)
+
+
+def psf_convolve_slice(xpad, xhat, xout, psfhat, lastsize, x, nthreads=1):
+    """pfb/operators/psf.py:11-29 (2-D arrays)."""
+    return _convolve(psfhat, lastsize, x, xout)
+
+
+def psf_convolve_cube(xpad, xhat, xout, psfhat, lastsize, x, nthreads=1):
+    """pfb/operators/psf.py:32-56: xout = crop(irfft2(rfft2(pad(x)) * psfhat))."""
+    return _convolve(psfhat, lastsize, x, xout)

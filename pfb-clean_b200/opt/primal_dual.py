@@ -1,0 +1,221 @@
+"""Drop-in for pfb/opt/primal_dual.py: primal_dual :12-87 (functional form) and
+primal_dual_optimised :91-180 (the in-place form the spotless worker runs).
+
+primal_dual_optimised keeps the reference's signature, including its quirks:
+`psi(xp, v)` is image -> coeffs (Psi.dot), `psiH(vp, xout)` is coeffs -> image
+(Psi.hdot), `prox` is accepted and unused (the dual update is hard-wired to the
+sum-over-band dual_update_numba, primal_dual.py:136), x and v are updated in
+place and returned.  The pdb traps of the reference become FloatingPointError.
+
+Device-resident loop, per iteration (nlevel = L):
+    L   launches  Psi.dot(xp) -> v
+    1   launch    fused dual update + `vp = 2v - vp`
+    L   launches  Psi.hdot(vp) -> xout
+    3   launches  grad: psf_convolve(xp)          (when grad is a Grad21)
+    2   launches  fused `xout += conv - data; x = P+(xp - tau*xout)` + eps terms
+and one 16-byte device->host read for the convergence test.  The reference's
+`xp[...] = x`, `vp[...] = v` copies are buffer swaps.  With
+pfb_b200.parallel enabled the bands are sharded over ranks: the dual update is
+split around an all-reduce of the band-sum slab and the eps terms are
+all-reduced.
+"""
+import math
+
+import numpy as np
+import torch
+
+from .. import _dev, _lib, parallel
+from ..operators.psi import Psi
+from ..prox import _common as _prox
+from ..utils.misc import norm_diff_terms
+from . import _vec
+
+
+class Grad21:
+    """grad21 = lambda x: psf_convolve(x) - data  (pfb/workers/spotless.py:260)
+    as an object, so the solver can fuse the subtraction into the primal
+    update instead of materialising the gradient."""
+
+    def __init__(self, psf_convolve, data):
+        self.psf_convolve = psf_convolve
+        self.data = data
+        self._data_dev = None
+
+    def data_dev(self):
+        if self._data_dev is None:
+            self._data_dev = _dev.to_dev(self.data)
+        return self._data_dev
+
+    def __call__(self, x):
+        conv = self.psf_convolve(x)
+        if isinstance(conv, np.ndarray):
+            return conv - (self.data if isinstance(self.data, np.ndarray) else self.data.cpu().numpy())
+        return conv - self.data_dev()
+
+
+def _is_psi_pair(psi, psiH):
+    a, b = getattr(psi, "__self__", None), getattr(psiH, "__self__", None)
+    return (isinstance(a, Psi) and a is b and getattr(psi, "__func__", None) is Psi.dot
+            and getattr(psiH, "__func__", None) is Psi.hdot)
+
+
+def _dual_step(vp, v, lam, sigma, w, n, bsum):
+    """v <- dual update(vp, v); vp <- 2 v - vp.  Sharded: split around the
+    all-reduce of the band-sum slab."""
+    L = _lib.lib()
+    nb = v.shape[0]
+    if parallel.active():
+        _lib.check(L.pfb_dual_partial(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(bsum), nb, n, float(sigma),
+                                      _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
+        parallel.allreduce_sum(bsum)
+        _lib.check(L.pfb_dual_apply(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(bsum), _dev.ptr(w), _dev.ptr(vp),
+                                    nb, n, float(lam), float(sigma), _lib.BAND_SUM, _dev.dcode(v),
+                                    _dev.stream()))
+    else:
+        _lib.check(L.pfb_dual_update(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(w), _dev.ptr(vp), nb, n,
+                                     float(lam), float(sigma), _lib.BAND_SUM, _dev.dcode(v),
+                                     _dev.stream()))
+
+
+def _gap_index(psi_obj, device):
+    """Flat indices (into nbasis*Nymax*Nxmax) of the slab cells Psi.dot never
+    writes.  Found by running a 1-band analysis over a NaN-filled slab once."""
+    idx = getattr(psi_obj, "_gap_idx", None)
+    if idx is None:
+        one = Psi(1, psi_obj.nx, psi_obj.ny, psi_obj.bases, psi_obj.nlevel, 1)
+        a = torch.full((1, one.nbasis, one.Nymax, one.Nxmax), float("nan"), dtype=torch.float64,
+                       device=device)
+        one.dot(torch.zeros((1, one.nx, one.ny), dtype=torch.float64, device=device), a)
+        idx = torch.nonzero(torch.isnan(a.view(-1))).view(-1)
+        psi_obj._gap_idx = idx
+    return idx
+
+
+def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, grad,
+                          nu=1.0, sigma=None, mask=None, tol=1e-5, maxit=1000,
+                          positivity=1, report_freq=10, gamma=1.0, verbosity=1,
+                          maxreweight=50):
+    xa = _dev.to_dev(x, copy=_dev._EMULATED and isinstance(x, np.ndarray))
+    va = _dev.to_dev(v, copy=_dev._EMULATED and isinstance(v, np.ndarray))
+    if xa.dtype != va.dtype:
+        raise TypeError("x and v must have the same precision")
+    xcur, xprev = xa, xa.clone()
+    vcur, vprev = va, va.clone()
+    xout = torch.zeros_like(xa)
+    n = va.numel() // va.shape[0]
+    w = _prox._weight_dev(l1weight, va, tuple(va.shape[1:]))
+    bsum = torch.empty(va.shape[1:], dtype=va.dtype, device=va.device) if parallel.active() else None
+    terms = _dev.scalars(2)
+
+    if sigma is None:
+        sigma = L / (2.0 * gamma) / nu
+    tau = 0.9 / (L / (2.0 * gamma) + sigma * nu**2)
+
+    # buffer swap instead of `vp[...] = v` needs the never-written slab cells of
+    # both dual buffers to agree; they do whenever they are zero (always, for a
+    # dual that started at zero).  Otherwise they are patched after each swap.
+    fast = _is_psi_pair(psi, psiH)
+    gap_idx = None
+    if fast:
+        gi = _gap_index(psi.__self__, va.device)
+        if gi.numel() and bool(torch.any(va.view(va.shape[0], -1)[:, gi] != 0)):
+            gap_idx = gi
+    fused_grad = isinstance(grad, Grad21)
+    data = grad.data_dev() if fused_grad else None
+    if data is not None and data.dtype != xa.dtype:
+        data = data.to(xa.dtype)
+    pos_kernel = positivity if not (positivity == 2 and parallel.active()) else 0
+
+    eps = 1.0
+    numreweight = 0
+    k = -1
+    broke = False
+    for k in range(maxit):
+        psi(xprev, vcur)
+        _dual_step(vprev, vcur, lam, sigma, w, n, bsum)          # vprev now holds 2v - vp
+        psiH(vprev, xout)
+        g = _dev.to_dev(grad.psf_convolve(xprev) if fused_grad else grad(xprev))
+        if g.dtype != xa.dtype:
+            g = g.to(xa.dtype)
+        _vec.pd_primal(xcur, xprev, xout, g, data, tau, pos_kernel, terms)
+        if pos_kernel != positivity:   # positivity 2 across band-sharded ranks
+            neg = (xcur <= 0).any(dim=0).to(torch.int32)
+            parallel.allreduce_max(neg)
+            xcur[:, neg.bool()] = 0
+            norm_diff_terms(xcur, xprev, out=terms)
+        num, den = parallel.allreduce_sum(terms).tolist()
+        if den == 0.0:
+            raise FloatingPointError("primal_dual: model is identically zero "
+                                     "(the reference drops into pdb here)")
+        eps = math.sqrt(num / (1e-12 + den))
+        if eps < tol:
+            if reweighter is not None and numreweight < maxreweight:
+                w = _prox._weight_dev(reweighter(xcur), va, tuple(va.shape[1:]))
+                numreweight += 1
+            else:
+                if numreweight >= maxreweight and verbosity:
+                    print("Maximum reweighting steps reached")
+                broke = True
+                break
+        # xp <- x, vp <- v  (pfb/opt/primal_dual.py:164-165) as swaps
+        xcur, xprev = xprev, xcur
+        if fast:
+            vcur, vprev = vprev, vcur
+            if gap_idx is not None:
+                vcur.view(vcur.shape[0], -1)[:, gap_idx] = vprev.view(vprev.shape[0], -1)[:, gap_idx]
+        else:
+            vprev.copy_(vcur)
+        if math.isnan(eps) or math.isinf(eps):
+            raise FloatingPointError("primal_dual: eps is NaN/Inf")
+        if not k % report_freq and verbosity > 1:
+            print(f"At iteration {k} eps = {eps:.3e}")
+
+    if verbosity:
+        if k == maxit - 1 and not broke:
+            print(f"Max iters reached. eps = {eps:.3e}")
+        else:
+            print(f"Success, converged after {k} iterations")
+    xfin = xcur if broke else xprev
+    vfin = vcur if (broke or not fast) else vprev
+    return _dev.to_out(xfin, x), _dev.to_out(vfin, v)
+
+
+def primal_dual(x, v, lam, psi, psiH, L, prox, grad, nu=1.0, sigma=None, mask=None,
+                tol=1e-5, maxit=1000, minit=10, positivity=1, report_freq=10, gamma=1.0,
+                verbosity=1):
+    """pfb/opt/primal_dual.py:12-87, functional form: psiH(x) RETURNS coeffs,
+    psi(v) RETURNS an image, prox(v, thr) RETURNS an array.  Kept literal (the
+    operators it is given own the kernels); single rank only."""
+    xd = _dev.to_dev(x, copy=True)
+    vd = _dev.to_dev(v, copy=True)
+    xp, vp = xd.clone(), vd.clone()
+    if sigma is None:
+        sigma = L / (2.0 * gamma) / nu
+    tau = 0.9 / (L / (2.0 * gamma) + sigma * nu**2)
+    eps = 1.0
+    k = 0
+    terms = _dev.scalars(2)
+    while (eps > tol or k < minit) and k < maxit:
+        vtilde = vd + sigma * _dev.to_dev(psiH(xp))
+        vd = vtilde - sigma * _dev.to_dev(prox(vtilde / sigma, lam / sigma))
+        xd = xp - tau * (_dev.to_dev(psi(2 * vd - vp)) + _dev.to_dev(grad(xp)))
+        if positivity == 1:
+            xd = torch.clamp_min(xd, 0.0)
+        elif positivity == 2:
+            xd[:, (xd <= 0).any(dim=0)] = 0.0
+        # eps = ||x - xp|| / ||x||
+        num, den = norm_diff_terms(xd, xp, out=terms).tolist()
+        eps = math.sqrt(num) / math.sqrt(den) if den > 0 else float("nan")
+        xp.copy_(xd)
+        vp.copy_(vd)
+        if math.isnan(eps) or math.isinf(eps):
+            raise FloatingPointError("primal_dual: eps is NaN/Inf")
+        if not k % report_freq and verbosity > 1:
+            print(f"At iteration {k} eps = {eps:.3e}")
+        k += 1
+    if verbosity:
+        if k == maxit:
+            print(f"Max iters reached. eps = {eps:.3e}")
+        else:
+            print(f"Success, converged after {k} iterations")
+    return _dev.like(x, xd), _dev.like(v, vd)

@@ -20,3 +20,18 @@ def golden(name):
 @pytest.fixture(scope="session")
 def golden_loader():
     return golden
+
+
+@pytest.fixture()
+def emu_backend(monkeypatch):
+    """Route the product's Python host layer to the CPU execution-model
+    emulator build of the kernel sources (tests only; see tests/emu)."""
+    import pfb_b200._lib as L
+    import pfb_b200._dev as D
+    from emu.emulib import emu
+    import pfb_b200.operators.psf as psf
+    monkeypatch.setattr(L, "_LIB", emu())
+    monkeypatch.setattr(D, "_EMULATED", True)
+    psf.clear_plan_cache()
+    yield
+    psf.clear_plan_cache()
