@@ -1,0 +1,326 @@
+"""GPU parity tests proper: libpfb_b200.so on a B200, driven through the Python
+host layer (ctypes -> C-ABI of include/pfb_b200.h), against the oracle on the
+same seeded inputs, plus size-independent properties at BASELINE.json's full
+sizes.  Tolerances are the north-star's: operators 1e-6 relative L2 in fp32,
+1e-11 in fp64; final model after a fixed iteration count 1e-5."""
+from functools import partial
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref
+
+pytestmark = pytest.mark.gpu
+pmp = pytest.mark.parametrize
+
+TOL = {np.float32: 1e-6, np.float64: 1e-11}
+BASES = ["self", "db1", "db2", "db3", "db4"]
+
+
+def rel(a, b):
+    a = a.cpu().numpy() if isinstance(a, torch.Tensor) else a
+    b = b.cpu().numpy() if isinstance(b, torch.Tensor) else b
+    return np.linalg.norm((a.astype(np.float64) - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300)
+
+
+@pytest.fixture(autouse=True)
+def _cuda_lib():
+    import pfb_b200._lib as L
+    import pfb_b200.operators.psf as psf
+    assert torch.cuda.is_available()
+    L.lib()
+    psf.clear_plan_cache()
+    yield
+    psf.clear_plan_cache()
+
+
+# ------------------------------------------------------------------ prox
+@pmp("dtype", [np.float32, np.float64])
+@pmp("nband,shape", [(1, (1, 5, 7)), (3, (2, 9, 12)), (8, (5, 67, 130)), (10, (2, 16, 16)),
+                      (4, (5, 268, 268))])
+@pmp("mode", [0, 1])
+def test_prox_dual_vs_oracle(dtype, nband, shape, mode):
+    from pfb_b200.prox import prox_21m as P, prox_21 as P2
+    rng = np.random.default_rng(1)
+    v = rng.standard_normal((nband,) + shape).astype(dtype)
+    v[:, 0, 1, 2] = 0
+    vp = rng.standard_normal(v.shape).astype(dtype)
+    w = rng.random(shape).astype(dtype)
+    tol = 1e-14 if dtype == np.float64 else 3e-7
+    for lam, sigma in [(1.0, 1.0), (0.1, 75.0), (1e-3, 1e-3)]:
+        res = np.full(v.shape, np.nan, dtype)
+        (P2.prox_21_numba if mode else P.prox_21m_numba)(v, res, lam, sigma=sigma, weight=w)
+        exp = np.zeros_like(v)
+        (ref.prox_21_numba if mode else ref.prox_21m_numba)(v, exp, lam, sigma=sigma, weight=w)
+        assert rel(res, exp) < tol
+        v2 = v.copy()
+        (P2.dual_update_numba if mode else P.dual_update_numba)(vp, v2, lam, sigma=sigma, weight=w)
+        exp = v.copy()
+        (ref.dual_update_numba_l2 if mode else ref.dual_update_numba)(vp, exp, lam, sigma=sigma, weight=w)
+        assert rel(v2, exp) < tol
+
+
+def test_prox_zero_threshold_identity():
+    """tests/test_psi_operator.py:92-129 (test_prox21m): prox with lam = 0 is the identity."""
+    from pfb_b200.prox.prox_21m import prox_21m_numba
+    rng = np.random.default_rng(5)
+    v = rng.standard_normal((3, 2, 30, 40))
+    res = np.empty_like(v)
+    prox_21m_numba(v, res, 0.0, sigma=1.0, weight=np.ones(v.shape[1:]))
+    assert rel(res, v) < 1e-15
+
+
+# ------------------------------------------------------------------- psi
+@pmp("dtype", [np.float32, np.float64])
+@pmp("nx,ny,bases,nlevel", [
+    (128, 256, ["self", "db1", "db4", "db5"], 3),     # tests/test_psi_operator.py shapes
+    (512, 128, ["db1", "db2", "db3"], 2),
+    (64, 64, ["self", "db2"], 1),
+    (250, 198, BASES, 3),                              # even, not multiples of the tile
+    (512, 512, BASES, 3),                              # config 1
+])
+def test_psi_vs_oracle(dtype, nx, ny, bases, nlevel):
+    from pfb_b200.operators.psi import Psi
+    rng = np.random.default_rng(420)
+    nband = 2
+    x = rng.standard_normal((nband, nx, ny)).astype(dtype)
+    psi = Psi(nband, nx, ny, bases, nlevel, 1)
+    opsi = ref.Psi(nband, nx, ny, bases, nlevel)
+    assert (psi.Nxmax, psi.Nymax) == (opsi.Nxmax, opsi.Nymax)
+    fill = rng.standard_normal((nband, len(bases), psi.Nymax, psi.Nxmax)).astype(dtype)
+    a, oa = fill.copy(), fill.copy()
+    psi.dot(x, a)
+    opsi.dot(x, oa)
+    assert rel(a, oa) < TOL[dtype]
+    # never-written cells keep the caller's content, bit for bit
+    gaps = oa == fill
+    assert np.array_equal(a[gaps], fill[gaps])
+    xr, oxr = np.full(x.shape, np.nan, dtype), np.zeros(x.shape, dtype)
+    psi.hdot(fill, xr)
+    opsi.hdot(fill, oxr)
+    assert rel(xr, oxr) < TOL[dtype]
+    # perfect reconstruction: hdot(dot(x)) = nbasis * x  (tests/test_psi_operator.py:48)
+    a0 = np.zeros_like(fill)
+    psi.dot(x, a0)
+    psi.hdot(a0, xr)
+    assert rel(xr, len(bases) * x) < (1e-12 if dtype == np.float64 else 2e-6)
+
+
+def test_psi_errors():
+    from pfb_b200.operators.psi import Psi
+    with pytest.raises(ValueError):
+        Psi(1, 32, 32, ["self", "db5"], 3, 1)      # nlevel too large (psi.py:43-46)
+    with pytest.raises(ValueError):
+        Psi(1, 33, 32, ["db1"], 1, 1)              # odd sizes are unsupported by the reference
+
+
+# --------------------------------------------------------------- hessian
+@pmp("dtype", [np.float32, np.float64])
+@pmp("nx,ny,nxp,nyp", [(8, 6, 16, 32), (20, 40, 64, 128), (100, 64, 256, 128), (30, 200, 32, 512),
+                        (6, 10, 4096, 64), (4, 10, 16, 8192), (512, 512, 1024, 1024),
+                        (300, 500, 1024, 1024)])
+def test_hess_vs_oracle(dtype, nx, ny, nxp, nyp):
+    from pfb_b200.operators.psf import psf_convolve_cube
+    from pfb_b200.operators.hessian import hessian_psf_cube
+    rng = np.random.default_rng(11)
+    nband = 2
+    cdt = np.complex64 if dtype == np.float32 else np.complex128
+    psf = rng.standard_normal((nband, nxp, nyp))
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2)).astype(cdt)
+    x = rng.standard_normal((nband, nx, ny)).astype(dtype)
+    beam = (0.5 + rng.random(x.shape)).astype(dtype)
+    xpad, xhat = np.empty((nband, nxp, nyp), dtype), np.empty(psfhat.shape, cdt)
+    xo = np.empty(x.shape, dtype)
+    exp = ref.psf_convolve_cube(xpad, xhat, xo, psfhat, nyp, x).copy()
+    out = np.full(x.shape, np.nan, dtype)
+    res = psf_convolve_cube(None, None, out, psfhat, nyp, x)
+    assert res is out
+    assert rel(out, exp) < TOL[dtype]
+    exp2 = ref.hessian_psf_cube(xpad, xhat, xo, beam, psfhat, nyp, x, sigmainv=0.25, wsum=3.5)
+    got2 = hessian_psf_cube(None, None, None, beam, psfhat, nyp, x, sigmainv=0.25, wsum=3.5)
+    assert rel(got2, exp2) < TOL[dtype]
+
+
+def test_hess_delta_kat_full_size():
+    """Config-3 band at full size: x = delta at (p,q) => out = shifted PSF crop
+    (SURVEY 8c); exercises the 8192-point column and 4096-point row FFTs."""
+    from pfb_b200.operators.psf import psf_convolve_cube
+    dev = torch.device("cuda")
+    nx = ny = 4096
+    nxp = nyp = 8192
+    g = torch.Generator(device="cpu").manual_seed(7)
+    psf = torch.randn((1, nxp, nyp), generator=g, dtype=torch.float32)
+    psfhat = torch.fft.rfft2(torch.fft.ifftshift(psf.to(dev).double(), dim=(1, 2)), dim=(1, 2)).to(torch.complex64)
+    x = torch.zeros((1, nx, ny), dtype=torch.float32, device=dev)
+    p, q = 1234, 4001
+    x[0, p, q] = 1.0
+    out = torch.empty_like(x)
+    psf_convolve_cube(None, None, out, psfhat, nyp, x)
+    exp = psf[0, nxp // 2 - p: nxp // 2 - p + nx, nyp // 2 - q: nyp // 2 - q + ny]
+    assert rel(out[0], exp.numpy()) < 1e-6
+
+
+@pmp("dtype", [torch.float32, torch.float64])
+def test_hess_linearity_full_size(dtype):
+    """H(a x + b y) = a H(x) + b H(y) at config-2 band size."""
+    from pfb_b200.operators.psf import psf_convolve_cube
+    dev = torch.device("cuda")
+    nband, nx, nxp = 2, 2048, 4096
+    g = torch.Generator(device=dev).manual_seed(3)
+    cdt = torch.complex64 if dtype == torch.float32 else torch.complex128
+    psf = torch.randn((nband, nxp, nxp), generator=g, dtype=torch.float64, device=dev)
+    psfhat = torch.fft.rfft2(torch.fft.ifftshift(psf, dim=(1, 2)), dim=(1, 2)).to(cdt)
+    del psf
+    x = torch.randn((nband, nx, nx), generator=g, dtype=dtype, device=dev)
+    y = torch.randn((nband, nx, nx), generator=g, dtype=dtype, device=dev)
+    hx, hy, hz = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
+    psf_convolve_cube(None, None, hx, psfhat, nxp, x)
+    psf_convolve_cube(None, None, hy, psfhat, nxp, y)
+    psf_convolve_cube(None, None, hz, psfhat, nxp, 2.0 * x - 0.5 * y)
+    tol = 2e-6 if dtype == torch.float32 else 1e-12
+    assert rel(hz, (2.0 * hx - 0.5 * hy)) < tol
+    # against the library FFT definition (cross-check only, never the product path)
+    xp = torch.zeros((nband, nxp, nxp), dtype=dtype, device=dev)
+    xp[:, :nx, :nx] = x
+    exp = torch.fft.irfft2(torch.fft.rfft2(xp.double()) * psfhat.to(torch.complex128), s=(nxp, nxp))[:, :nx, :nx]
+    assert rel(hx, exp) < (1e-6 if dtype == torch.float32 else 1e-11)
+
+
+@pmp("dtype", [torch.float32, torch.float64])
+def test_psi_roundtrip_full_size(dtype):
+    """hdot(dot(x)) = nbasis * x at 4096^2, self+db1..db4, 3 levels (config 3 band)."""
+    from pfb_b200.operators.psi import Psi
+    dev = torch.device("cuda")
+    nx = ny = 4096
+    psi = Psi(1, nx, ny, BASES, 3, 1)
+    assert (psi.Nxmax, psi.Nymax) == (4116, 4116)
+    g = torch.Generator(device=dev).manual_seed(9)
+    x = torch.randn((1, nx, ny), generator=g, dtype=dtype, device=dev)
+    a = torch.zeros((1, 5, psi.Nymax, psi.Nxmax), dtype=dtype, device=dev)
+    psi.dot(x, a)
+    # zero-mode isometry per basis: ||dwt(x)|| = ||x|| for every orthonormal bank
+    nrm = torch.linalg.vector_norm(x.double())
+    for b in range(5):
+        r = float(torch.linalg.vector_norm(a[0, b].double()) / nrm)
+        assert abs(r - 1) < (1e-6 if dtype == torch.float32 else 1e-11), (b, r)
+    xr = torch.empty_like(x)
+    psi.hdot(a, xr)
+    assert rel(xr, 5 * x) < (2e-6 if dtype == torch.float32 else 1e-12)
+
+
+def test_psi_full_size_one_band_vs_oracle():
+    """One full-size band (2048^2, config 2) against the C oracle."""
+    from pfb_b200.operators.psi import Psi
+    rng = np.random.default_rng(2)
+    nx = ny = 2048
+    x = rng.standard_normal((1, nx, ny)).astype(np.float32)
+    psi = Psi(1, nx, ny, BASES, 3, 1)
+    opsi = ref.Psi(1, nx, ny, BASES, 3)
+    a = np.zeros((1, 5, psi.Nymax, psi.Nxmax), np.float32)
+    oa = np.zeros_like(a)
+    psi.dot(x, a)
+    opsi.dot(x, oa)
+    assert rel(a, oa) < 1e-6
+    xr, oxr = np.empty_like(x), np.empty_like(x)
+    psi.hdot(oa, xr)
+    opsi.hdot(oa, oxr)
+    assert rel(xr, oxr) < 1e-6
+
+
+# ------------------------------------------------------- vector kernels
+@pmp("dtype", [np.float32, np.float64])
+@pmp("n", [1, 255, 4096 + 3, 1 << 20])
+def test_vector_ops(dtype, n):
+    from pfb_b200.opt import _vec
+    from pfb_b200.utils.misc import norm_diff
+    rng = np.random.default_rng(2)
+    a, b = (rng.standard_normal(n).astype(dtype) for _ in range(2))
+    ta, tb = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    out = torch.empty_like(ta)
+    _vec.axpby(out, 2.0, ta, -1.0, tb)
+    assert np.array_equal(out.cpu().numpy(), (2 * a - b).astype(dtype))
+    r = _vec.vdot2(ta, tb, ta, ta).tolist()
+    assert abs(r[0] - np.vdot(a.astype(np.float64), b.astype(np.float64))) < 1e-12 * n
+    assert abs(r[1] - np.vdot(a.astype(np.float64), a.astype(np.float64))) < 1e-12 * n
+    e = norm_diff(a.reshape(1, -1), b.reshape(1, -1))
+    assert abs(e / ref.norm_diff(a, b) - 1) < (1e-12 if dtype == np.float64 else 1e-6)
+    # reductions are deterministic (fixed order): bitwise identical on repeat
+    assert _vec.vdot2(ta, tb, ta, ta).tolist() == r
+
+
+# ---------------------------------------------------------------- solvers
+def _problem(nband, nx, dtype, seed=420):
+    rng = np.random.default_rng(seed)
+    nxp = 2 * nx
+    cdt = np.complex64 if dtype == np.float32 else np.complex128
+    r2 = ((np.arange(nxp) - nxp // 2)[:, None] ** 2 + (np.arange(nxp) - nxp // 2)[None, :] ** 2)
+    psf = np.stack([np.exp(-0.5 * r2 / (2.0 * (1 + 0.05 * b)) ** 2) for b in range(nband)])
+    psf += 0.02 * rng.standard_normal(psf.shape) * np.exp(-0.5 * r2 / (0.2 * nx) ** 2)
+    psf /= psf.max(axis=(1, 2)).sum()
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2)).astype(cdt)
+    model = np.zeros((nband, nx, nx))
+    for _ in range(30):
+        i, j = rng.integers(nx // 8, 7 * nx // 8, 2)
+        model[:, i, j] = (1 + np.exp(rng.standard_normal())) * (1 + 0.1 * np.arange(nband)) ** -0.7
+    model = model.astype(dtype)
+    xpad, xhat = np.empty((nband, nxp, nxp), dtype), np.empty(psfhat.shape, cdt)
+    xo = np.empty_like(model)
+    oconv = partial(ref.psf_convolve_cube, xpad, xhat, xo, psfhat, nxp)
+    dirty = oconv(model).copy()
+    dirty += (1e-3 * dirty.max() * rng.standard_normal(dirty.shape)).astype(dtype)
+    return psfhat, dirty, oconv, (xpad, xhat, xo)
+
+
+@pmp("dtype", [np.float32, np.float64])
+@pmp("nband,nx", [(1, 512), (3, 256)])
+def test_minor_cycle_vs_oracle(dtype, nband, nx):
+    """Config 1 (1 band 512^2, pcg + primal_dual 10 iters) and a 3-band case:
+    final model after a fixed iteration count within 1e-5 relative L2."""
+    from pfb_b200.operators.psf import psf_convolve_cube
+    from pfb_b200.operators.hessian import hessian_psf_cube
+    from pfb_b200.operators.psi import Psi
+    from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
+    from pfb_b200.opt.power_method import power_method
+    from pfb_b200.opt.pcg import pcg
+    psfhat, dirty, oconv, (xpad, xhat, xo) = _problem(nband, nx, dtype)
+    nxp = 2 * nx
+    psi = Psi(nband, nx, nx, BASES, 3, 1)
+    opsi = ref.Psi(nband, nx, nx, BASES, 3)
+    xout = np.empty_like(dirty)
+    conv = partial(psf_convolve_cube, None, None, xout, psfhat, nxp)
+    b0 = np.random.default_rng(1).standard_normal(dirty.shape).astype(dtype)
+    beta, _ = power_method(conv, dirty.shape, b0=b0.copy(), tol=1e-3, maxit=30, verbosity=0)
+    obeta, _ = ref.power_method(lambda z: oconv(z).copy(), dirty.shape, b0=b0.copy(), tol=1e-3, maxit=30)
+    assert abs(beta / obeta - 1) < (1e-10 if dtype == np.float64 else 1e-4)
+    hessnorm = 1.05 * float(obeta)
+    lam = 0.5 * float(np.std(dirty.sum(axis=0)))
+    shape_v = (nband, 5, psi.Nymax, psi.Nxmax)
+    w = np.ones(shape_v[1:], dtype)
+    x, v = np.zeros_like(dirty), np.zeros(shape_v, dtype)
+    primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, w, None, Grad21(conv, dirty),
+                          nu=5, tol=0.0, maxit=10, verbosity=0)
+    ox, ov = np.zeros_like(dirty), np.zeros(shape_v, dtype)
+    ref.primal_dual_optimised(ox, ov, lam, opsi.hdot, opsi.dot, hessnorm, None, w, None,
+                              lambda z: oconv(z) - dirty, nu=5, tol=0.0, maxit=10)
+    assert ox.any()
+    assert rel(x, ox) < (1e-11 if dtype == np.float64 else 1e-5)
+    assert rel(v, ov) < (1e-11 if dtype == np.float64 else 1e-5)
+    A = partial(hessian_psf_cube, None, None, None, None, psfhat, nxp, sigmainv=1e-3)
+    oA = partial(ref.hessian_psf_cube, xpad, xhat, xo, None, psfhat, nxp, sigmainv=1e-3)
+    xs = pcg(A, dirty, np.zeros_like(dirty), tol=0.0, maxit=10, minit=10, verbosity=0)
+    oxs = ref.pcg(oA, dirty, np.zeros_like(dirty), tol=0.0, maxit=10, minit=10)
+    assert rel(xs, oxs) < (1e-10 if dtype == np.float64 else 1e-5)
+
+
+def test_library_is_the_one_loaded():
+    """The GPU tests must run on libpfb_b200.so (no silent fallback)."""
+    import pfb_b200._lib as L
+    import pfb_b200._dev as D
+    assert not D._EMULATED
+    assert L.lib()._name.endswith("libpfb_b200.so")
+    n0 = L.lib().pfb_launch_count()
+    from pfb_b200.opt import _vec
+    t = torch.ones(1000, device="cuda")
+    _vec.axpby(t, 1.0, t, 1.0, t)
+    assert L.lib().pfb_launch_count() == n0 + 1

@@ -18,7 +18,7 @@ def rel(a, b):
 
 
 @pmp("tag", ["psi_f64_a", "psi_f32_a"])
-def test_psi_api(emu_backend, tag):
+def test_psi_api(backend, tag):
     from pfb_b200.operators.psi import Psi
     g = golden(tag)
     x = g["x"]
@@ -46,7 +46,7 @@ def test_psi_api(emu_backend, tag):
 
 
 @pmp("tag", ["hess_f64", "hess_f32"])
-def test_hess_api(emu_backend, tag):
+def test_hess_api(backend, tag):
     from pfb_b200.operators.psf import psf_convolve_cube, psf_convolve_slice
     from pfb_b200.operators.hessian import hessian_psf_cube, _hessian_psf_slice
     g = golden(tag)
@@ -64,7 +64,7 @@ def test_hess_api(emu_backend, tag):
 
 
 @pmp("tag", ["prox_f64", "prox_f32"])
-def test_prox_api(emu_backend, tag):
+def test_prox_api(backend, tag):
     from pfb_b200.prox.prox_21m import prox_21m, prox_21m_numba, dual_update_numba
     from pfb_b200.prox import prox_21 as p21
     g = golden(tag)
@@ -85,7 +85,7 @@ def test_prox_api(emu_backend, tag):
     assert rel(p21.prox_21(v, 0.3, weight=w), g["prox21_numpy"]) < tol
 
 
-def test_norm_diff_api(emu_backend):
+def test_norm_diff_api(backend):
     from pfb_b200.utils.misc import norm_diff
     g = golden("misc")
     for t, tol in (("f64", 1e-13), ("f32", 1e-6)):
@@ -93,7 +93,7 @@ def test_norm_diff_api(emu_backend):
 
 
 @pmp("tag", ["solve_f64", "solve_f32"])
-def test_solvers_api(emu_backend, tag):
+def test_solvers_api(backend, tag):
     from pfb_b200.operators.psf import psf_convolve_cube
     from pfb_b200.operators.hessian import hessian_psf_cube
     from pfb_b200.operators.psi import Psi
@@ -178,7 +178,7 @@ def test_solvers_api(emu_backend, tag):
     assert rel(xb, g["pcgpsf_x"]) < (1e-10 if f64 else 2e-4)
 
 
-def test_nonzero_gap_dual(emu_backend):
+def test_nonzero_gap_dual(backend):
     """A dual variable whose never-written slab cells are non-zero must evolve
     exactly as in the reference even though vp <- v is a buffer swap."""
     from oracle import ref
