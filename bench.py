@@ -1,0 +1,525 @@
+#!/usr/bin/env python
+"""bench.py -- PFB minor iterations / second (BASELINE.json metric).
+
+A "step" is ONE primal-dual minor iteration (body of primal_dual_optimised,
+pfb/opt/primal_dual.py:134-171 of the reference: Psi.dot -> dual update ->
+2v-vp -> Psi.hdot -> PSF Hessian -> primal update -> eps) over the WHOLE cube.
+Default workload = BASELINE.json configs[2]: 8 bands x 4096^2, PSF 8192^2,
+bases self+db1..db4, 3 levels, fp32 -- it fits one B200 (about 14 GB).  With
+--gpus N (torchrun) the 8 bands are sharded over the ranks (strong scaling) and
+the band-sum slab of the dual update plus the eps scalars are all-reduced (NCCL).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Prints ONE JSON line (rank 0).  `value` = K / device time of K iterations with
+every input resident in HBM; `e2e` = the same K iterations through the
+reference-facing call primal_dual_optimised(x, v, ...) with HOST (pinned numpy)
+buffers, host<->device copies inside the timed region.  `--impl reference`
+times the CPU path (the oracle port of the reference, all host threads) on a
+bounded sample of the same workload.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BASES = ["self", "db1", "db2", "db3", "db4"]
+NLEVEL = 3
+METRIC = "pfb_minor_iters_per_sec"
+UNIT = "iter/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--nband", type=int, default=8)
+    ap.add_argument("--nx", type=int, default=4096)
+    ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-bands", type=int, default=1)
+    ap.add_argument("--ncu-step", action="store_true",
+                    help="profiling aid: run ONE iteration between cudaProfilerStart/Stop and exit "
+                         "(use with ncu --profile-from-start off); prints no bench line")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"{a.nband} bands {a.nx}x{a.nx}, PSF {2 * a.nx}x{2 * a.nx} (psf-oversize 2), "
+            f"bases {'+'.join(BASES)}, {NLEVEL} levels, primal-dual minor cycle")
+
+
+# ------------------------------------------------------------ synthetic data
+def make_band_inputs(torch, band, nband, nx, rdt, dev, seed=420):
+    """MeerKAT-like PSF (core-dominated, thinned uv density) and a
+    sky of Gaussians + point sources for one band, built on `dev` with torch
+    (input generation only -- not the product path).
+    Returns psfhat (nxp, nyo2) complex, model (nx, nx)."""
+    nxp = 2 * nx
+    cdt = torch.complex64 if rdt == torch.float32 else torch.complex128
+    g = torch.Generator(device="cpu").manual_seed(seed)        # band independent part
+    nu = 1.0 + 0.1 * band
+    u = torch.fft.fftfreq(nxp, device=dev, dtype=torch.float64)[:, None] * nxp
+    vv = torch.fft.rfftfreq(nxp, device=dev, dtype=torch.float64)[None, :] * nxp
+    r = torch.sqrt(u * u + vv * vv) / nu
+    W = (1.0 + (r / (0.05 * nxp)) ** 2) ** -1.5
+    gd = torch.Generator(device=dev).manual_seed(seed + 17)
+    W = W * (torch.rand(W.shape, generator=gd, device=dev, dtype=torch.float64) < 0.3)
+    psf = torch.fft.irfft2(W, s=(nxp, nxp))                   # peak at (0,0): already ifftshift-ed
+    psf = psf / (psf[0, 0] * nband)                           # sum_b psf_b.max() = 1
+    psfhat = torch.fft.rfft2(psf).to(cdt)                     # = r2c(ifftshift(psf_centred))
+    del W, psf, r
+    # sky
+    model = torch.zeros((nx, nx), dtype=torch.float64, device=dev)
+    ii = torch.arange(nx, device=dev, dtype=torch.float64)
+    ngauss, npoint = 25, 50
+    cen = 0.15 * nx + 0.7 * nx * torch.rand((ngauss + npoint, 2), generator=g, dtype=torch.float64)
+    flux = 1.0 + torch.exp(torch.randn(ngauss + npoint, generator=g, dtype=torch.float64))
+    alpha = -0.7 + 0.1 * torch.randn(ngauss + npoint, generator=g, dtype=torch.float64)
+    fwhm = 3.0 + (0.02 * nx - 3.0) * torch.rand(ngauss, generator=g, dtype=torch.float64)
+    for k in range(ngauss):
+        s = float(fwhm[k]) / 2.355
+        gx = torch.exp(-0.5 * ((ii - float(cen[k, 0])) / s) ** 2)
+        gy = torch.exp(-0.5 * ((ii - float(cen[k, 1])) / (1.5 * s)) ** 2)
+        model += float(flux[k]) * nu ** float(alpha[k]) * gx[:, None] * gy[None, :]
+    for k in range(ngauss, ngauss + npoint):
+        model[int(cen[k, 0]), int(cen[k, 1])] += float(flux[k]) * nu ** float(alpha[k])
+    return psfhat, model.to(rdt)
+
+
+def clock_sampler(idx, stop, rows):
+    """nvidia-smi clocks/throttle reasons during the timed region."""
+    q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+    try:
+        p = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                              "-lms", "100", "-i", str(idx)], stdout=subprocess.PIPE, text=True)
+    except OSError:
+        return
+    def pump():
+        for line in p.stdout:
+            rows.append(line.strip())
+    t = threading.Thread(target=pump, daemon=True)
+    t.start()
+    stop.wait()
+    p.terminate()
+    t.join(timeout=2)
+
+
+def summarise_clocks(rows):
+    sm, mx, reasons = [], 0.0, set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for r in rows:
+        f = [c.strip() for c in r.split(",")]
+        if len(f) < 7:
+            continue
+        try:
+            sm.append(float(f[0]))
+            mx = max(mx, float(f[1]))
+        except ValueError:
+            continue
+        for n, val in zip(names, f[3:7]):
+            if val.lower().startswith("active"):
+                reasons.add(n)
+    sm.sort()
+    med = sm[len(sm) // 2] if sm else None
+    return {"sm_mhz": med, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# -------------------------------------------------------- algorithmic bytes
+def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
+    """Algorithmic (compulsory) bytes, SURVEY.md 8(d) / DESIGN.md, for the bands
+    on ONE GPU.  s = bytes per real."""
+    nxp = 2 * nx
+    nyo2 = nxp // 2 + 1
+    P1 = nx * nx * s
+    C1 = nbasis * Nmax * Nmax * s
+    psfhat = 2 * s * nxp * nyo2
+    S = 2 * s * nx * nyo2                      # pruned half spectrum (pipeline intermediate)
+    per_kernel = {                              # inputs + outputs of each kernel, counted once
+        "k_dwt_level": None, "k_idwt_level": None,   # per-op figure used instead (3 launches each)
+        "k_dual": nb_local * 4 * C1 + C1,       # read vp,v ; write v,u ; weight once
+        "k_dual_partial": nb_local * 3 * C1 + C1,
+        "k_dual_apply": nb_local * 4 * C1 + 2 * C1,
+        "k_hess_rows_fwd": nb_local * (P1 + S),
+        "k_hess_cols": nb_local * (2 * S + psfhat),
+        "k_hess_rows_inv": nb_local * (S + P1),
+        "k_pd_primal": nb_local * 5 * P1,       # read xp,xout,conv,data ; write x
+    }
+    per_op = {                                  # SURVEY 8(d) table, x nb_local
+        "psi_dot": nb_local * (P1 + C1),
+        "psi_hdot": nb_local * (C1 + P1),
+        "psf_convolve": nb_local * (2 * P1 + psfhat),
+        "dual_update+2v-vp": nb_local * 4 * C1 + C1,
+        "primal_update+eps": nb_local * 5 * P1,
+    }
+    fused_iter = nb_local * (3 * P1 + psfhat + 2 * C1) + C1     # SURVEY 8(d) headline lower bound
+    return per_kernel, per_op, fused_iter
+
+
+def short_kernel_name(mangled):
+    for k in ("k_dwt_level", "k_idwt_level", "k_dual_partial", "k_dual_apply", "k_dual",
+              "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv", "k_pd_primal", "k_red_final",
+              "k_norm_diff", "k_axpby", "k_dot", "k_prox21", "k_psfhat_prepare"):
+        if k in mangled:
+            return k
+    return mangled[:40]
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ----------------------------------------------------------------- our arm
+def run_ours(a):
+    import ctypes
+    from functools import partial
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus:
+        raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}: launch with torchrun for N>1")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    import pfb_b200  # noqa: F401
+    from pfb_b200 import _lib, parallel
+    from pfb_b200.operators.psf import psf_convolve_cube
+    from pfb_b200.operators.psi import Psi
+    from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
+    from pfb_b200.opt.power_method import power_method
+    L = _lib.lib()          # raises if libpfb_b200.so is missing: no fallback
+    if world > 1:
+        parallel.enable()
+
+    rdt = torch.float32 if a.dtype == "f32" else torch.float64
+    s = 4 if a.dtype == "f32" else 8
+    nb, nx = a.nband, a.nx
+    nxp = 2 * nx
+    if nb % world:
+        raise SystemExit("nband must be divisible by the number of GPUs")
+    nbl = nb // world
+    bands = range(rank * nbl, (rank + 1) * nbl)
+
+    # ---- inputs (synthetic, seeded; generated per band to bound memory)
+    psfhat = torch.empty((nbl, nxp, nxp // 2 + 1), dtype=torch.complex64 if s == 4 else torch.complex128, device=dev)
+    model = torch.empty((nbl, nx, nx), dtype=rdt, device=dev)
+    for i, b in enumerate(bands):
+        psfhat[i], model[i] = make_band_inputs(torch, b, nb, nx, rdt, dev)
+    torch.cuda.empty_cache()
+    xout = torch.empty_like(model)
+    conv = partial(psf_convolve_cube, None, None, xout, psfhat, nxp)
+    dirty = conv(model).clone()
+    gn = torch.Generator(device=dev).manual_seed(1000 + rank)
+    dmax = dirty.max()
+    if world > 1:
+        dist.all_reduce(dmax, op=dist.ReduceOp.MAX)
+    dirty += 1e-3 * dmax * torch.randn(dirty.shape, generator=gn, device=dev, dtype=rdt)
+    del model
+
+    psi = Psi(nbl, nx, nx, BASES, NLEVEL, 1, dtype=np.float32 if s == 4 else np.float64)
+    nbasis = len(BASES)
+    shape_v = (nbl, nbasis, psi.Nymax, psi.Nxmax)
+    # hessnorm = 1.05 * power_method(psf_convolve)  (pfb/workers/spotless.py:187-193)
+    gb = torch.Generator(device=dev).manual_seed(7 + rank)
+    b0 = torch.randn(dirty.shape, generator=gb, device=dev, dtype=rdt)
+    beta, _ = power_method(conv, dirty.shape, b0=b0, tol=1e-3, maxit=100, verbosity=0)
+    del b0
+    hessnorm = 1.05 * float(beta)
+    mfs = dirty.sum(dim=0)
+    if world > 1:
+        dist.all_reduce(mfs)
+    lam = 0.5 * float(mfs.std())
+    del mfs
+    w = torch.ones(shape_v[1:], dtype=rdt, device=dev)
+    grad = Grad21(conv, dirty)
+
+    def pd(x, v, nit):
+        return primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, w, None, grad,
+                                     nu=nbasis, tol=0.0, maxit=nit, positivity=1, verbosity=0)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident timing (`value`)
+    x = torch.zeros_like(dirty)
+    v = torch.zeros(shape_v, dtype=rdt, device=dev)
+    pd(x, v, max(a.warmup, 3))                       # warm-up iterations (untimed)
+    if a.ncu_step:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        pd(x, v, 1)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return None
+    rows, stop = [], threading.Event()
+    th = threading.Thread(target=clock_sampler, args=(local, stop, rows), daemon=True)
+    if rank == 0:
+        th.start()
+        time.sleep(0.3)
+    barrier()
+    L.pfb_profile_enable(1)
+    n0 = L.pfb_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    pd(x, v, a.steps)
+    e1.record()
+    barrier()
+    launches = L.pfb_launch_count() - n0
+    L.pfb_profile_enable(0)
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms)
+    stop.set()
+    buf = ctypes.create_string_buffer(1 << 16)
+    _lib.check(L.pfb_profile_report(buf, len(buf)))
+    kern = {}
+    for line in buf.value.decode().splitlines():
+        nm, n, t = line.split("\t")
+        k = short_kernel_name(nm)
+        c = kern.setdefault(k, [0, 0.0])
+        c[0] += int(n)
+        c[1] += float(t)
+    return finish_ours(a, locals())
+
+
+def finish_ours(a, env):
+    """e2e leg, CPU baseline leg and the JSON line (split from run_ours only to
+    keep the functions short; `env` is run_ours' namespace)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    g = env
+    world, rank, dev, rdt, s = g["world"], g["rank"], g["dev"], g["rdt"], g["s"]
+    nb, nbl, nx, psi, nbasis = g["nb"], g["nbl"], g["nx"], g["psi"], g["nbasis"]
+    pd, barrier, shape_v, dirty = g["pd"], g["barrier"], g["shape_v"], g["dirty"]
+    ms_total, kern, launches = g["ms_total"], g["kern"], g["launches"]
+    K = a.steps
+    value = K / (ms_total * 1e-3)
+
+    # ---- e2e: same K iterations through the public call with HOST buffers
+    e2e = None
+    if not a.no_e2e:
+        from pfb_b200.opt.primal_dual import Grad21
+        from functools import partial
+        from pfb_b200.operators.psf import psf_convolve_cube
+        del g["x"], g["v"]
+        torch.cuda.empty_cache()
+        hx = torch.zeros(dirty.shape, dtype=rdt).pin_memory()
+        hv = torch.zeros(shape_v, dtype=rdt).pin_memory()
+        hd = dirty.cpu().pin_memory()
+        hw = torch.ones(shape_v[1:], dtype=rdt).pin_memory()
+        hxo = torch.empty(dirty.shape, dtype=rdt).pin_memory()
+        # psfhat stays with the operator (uploaded once when the plan is bound,
+        # like the reference's one-off PSFHAT set-up): not a per-call input
+        hconv = partial(psf_convolve_cube, None, None, hxo.numpy(), g["psfhat"], 2 * nx)
+
+        def pd_host(nit):
+            from pfb_b200.opt.primal_dual import primal_dual_optimised
+            return primal_dual_optimised(hx.numpy(), hv.numpy(), g["lam"], psi.hdot, psi.dot,
+                                         g["hessnorm"], None, hw.numpy(), None,
+                                         Grad21(hconv, hd.numpy()), nu=nbasis, tol=0.0, maxit=nit,
+                                         positivity=1, verbosity=0)
+        pd_host(2)                                    # warm-up of the host path
+        hx.zero_(); hv.zero_()
+        barrier()
+        t0 = time.perf_counter()
+        pd_host(K)
+        torch.cuda.synchronize()
+        dt_ = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt_, op=dist.ReduceOp.MAX)
+        h2d = (hx.numel() + hv.numel() + hd.numel() + hw.numel()) * s * world
+        d2h = (hx.numel() + hv.numel()) * s * world + 16 * K * world
+        e2e = {"value": K / float(dt_), "unit": UNIT,
+               "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K,
+               "note": (f"one primal_dual_optimised(x, v, ...) call of {K} iterations with pinned "
+                        "numpy x, v, data, l1weight: H2D of all four and D2H of x, v inside the "
+                        "timed region (bytes are per call / K); psfhat is operator state bound "
+                        "before the call")}
+
+    if rank != 0:
+        return None
+    hbm, peak_src = peaks()
+    per_kernel, per_op, fused_iter = byte_model(nbl, nx, s, psi.Nxmax, nbasis, world > 1)
+    # dominant kernel = largest total device time in the timed region
+    tot_k = sum(t for _, t in kern.values())
+    dom = max(kern.items(), key=lambda kv: kv[1][1])
+    dname, (dn, dt_ms) = dom[0], dom[1]
+    if per_kernel.get(dname) is not None:
+        balg = per_kernel[dname]
+        what = f"{dname}: inputs+outputs of this kernel once"
+    else:   # wavelet level kernels: op-level bytes over the op's launches
+        op = "psi_dot" if dname == "k_dwt_level" else "psi_hdot"
+        balg = per_op[op] / NLEVEL
+        what = f"{dname}: {op} algorithmic bytes / {NLEVEL} level launches"
+    avg_s = dt_ms * 1e-3 / dn
+    ach = balg / avg_s / 1e9
+    roofline = {"bound": "hbm", "kernel": dname, "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
+                "frac": round(ach / hbm, 4), "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": balg, "avg_launch_ms": round(avg_s * 1e3, 4),
+                "share_of_step": round(dt_ms / tot_k, 4), "basis": what}
+    kernels = {k: {"launches": n, "ms_per_step": round(t / K, 4), "share": round(t / tot_k, 4)}
+               for k, (n, t) in sorted(kern.items(), key=lambda kv: -kv[1][1])}
+    for k, d in kernels.items():
+        if per_kernel.get(k) is not None:
+            d["GBps"] = round(per_kernel[k] / (d["ms_per_step"] * 1e-3) / 1e9 / (kern[k][0] / K), 1)
+            d["frac"] = round(d["GBps"] / hbm, 4)
+    ops = {}
+    groups = {"psi_dot": ["k_dwt_level"], "psi_hdot": ["k_idwt_level"],
+              "psf_convolve": ["k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv"],
+              "dual_update+2v-vp": ["k_dual", "k_dual_partial", "k_dual_apply"],
+              "primal_update+eps": ["k_pd_primal"]}
+    for op, ks in groups.items():
+        t = sum(kern[k][1] for k in ks if k in kern) / K
+        if t > 0:
+            ops[op] = {"ms_per_step": round(t, 4), "alg_GBps": round(per_op[op] / (t * 1e-3) / 1e9, 1),
+                       "frac": round(per_op[op] / (t * 1e-3) / 1e9 / hbm, 4)}
+    step_frac = fused_iter / (ms_total * 1e-3 / K) / 1e9 / hbm
+
+    cpu = None
+    if not a.no_cpu_baseline and world == 1:
+        cpu = cpu_reference(a, steps=2, warmup=1)
+
+    clocks = summarise_clocks(g["rows"])
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": K,
+        "warmup": max(a.warmup, 3), "ms_per_step": round(ms_total / K, 4), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+        "config": {"workload": workload_name(a), "nband": nb, "nx": nx, "ny": nx, "nxp": 2 * nx,
+                   "nyp": 2 * nx, "bases": BASES, "nlevels": NLEVEL, "positivity": 1,
+                   "bands_per_gpu": nbl, "parallelism": f"band-sharded x{world}",
+                   "l2_policy": "inputs larger than L2 (per-iteration working set > 10 GB)",
+                   "init": "x0=0, v0=0, l1weight=1, tol=0 (fixed iteration count)"},
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+        "step_roofline": {"fused_compulsory_bytes_per_step_per_gpu": fused_iter,
+                          "frac_of_hbm_peak": round(step_frac, 4)},
+        "kernels": kernels, "ops": ops, "cpu_baseline": cpu,
+    }
+    return line
+
+
+# ------------------------------------------------------- CPU reference arm
+def cpu_reference(a, steps, warmup):
+    """The reference's CPU algorithm for the same minor iteration, timed on the
+    host cores: oracle/ref.py (numpy + OpenMP C restatement of the numba
+    kernels, scipy.fft/pocketfft standing in for ducc0.fft) with every host
+    thread.  Bounded sample: `cpu_sample_bands` band(s) of the workload, scaled
+    by nband/sample (bands are independent apart from the cross-band sum)."""
+    from functools import partial
+    import numpy as np
+    import scipy.fft as sfft
+    from oracle import ref
+    ncores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(ncores))
+    nbs = max(1, min(a.cpu_sample_bands, a.nband))
+    nx, nxp = a.nx, 2 * a.nx
+    dt = np.float32 if a.dtype == "f32" else np.float64
+    cdt = np.complex64 if a.dtype == "f32" else np.complex128
+    rng = np.random.default_rng(420)
+    u = sfft.fftfreq(nxp)[:, None] * nxp
+    vv = sfft.rfftfreq(nxp)[None, :] * nxp
+    psfhat = np.empty((nbs, nxp, nxp // 2 + 1), cdt)
+    for b in range(nbs):
+        W = (1.0 + (np.sqrt(u * u + vv * vv) / (1 + 0.1 * b) / (0.05 * nxp)) ** 2) ** -1.5
+        W *= rng.random(W.shape) < 0.3
+        psf = sfft.irfft2(W, s=(nxp, nxp), workers=ncores)
+        psf /= psf[0, 0] * a.nband
+        psfhat[b] = sfft.rfft2(psf, workers=ncores)
+    del W, psf
+    model = np.zeros((nbs, nx, nx), dt)
+    idx = rng.integers(nx // 8, 7 * nx // 8, (75, 2))
+    model[:, idx[:, 0], idx[:, 1]] = (1 + np.exp(rng.standard_normal(75))).astype(dt)
+    xpad, xhat = np.empty((nbs, nxp, nxp), dt), np.empty(psfhat.shape, cdt)
+    xo = np.empty_like(model)
+    conv = partial(ref.psf_convolve_cube, xpad, xhat, xo, psfhat, nxp, nthreads=ncores)
+    dirty = conv(model).copy()
+    dirty += (1e-3 * dirty.max() * rng.standard_normal(dirty.shape)).astype(dt)
+    psi = ref.Psi(nbs, nx, nx, BASES, NLEVEL, nthreads=ncores)
+    shape_v = (nbs, len(BASES), psi.Nymax, psi.Nxmax)
+    x, v = np.zeros_like(dirty), np.zeros(shape_v, dt)
+    w = np.ones(shape_v[1:], dt)
+    lam = 0.5 * float(np.std(dirty.sum(axis=0)))
+
+    def run(nit):
+        ref.primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, 1.05 * nbs / a.nband, None, w, None,
+                                  lambda z: conv(z) - dirty, nu=len(BASES), tol=0.0, maxit=nit)
+    run(max(1, warmup))
+    t0 = time.perf_counter()
+    run(steps)
+    dt_s = (time.perf_counter() - t0) / steps
+    val = 1.0 / (dt_s * a.nband / nbs)
+    try:
+        nthr = int(ref.lib().orc_num_threads())
+    except Exception:
+        nthr = ncores
+    return {"value": round(val, 5), "unit": UNIT, "cores": nthr, "kind": "port",
+            "sample": (f"{steps} timed primal-dual iterations (after {max(1, warmup)} warm-up) on {nbs} of the "
+                       f"{a.nband} bands at full size {nx}x{nx}/PSF {nxp}x{nxp}, scaled x{nbs}/{a.nband}; "
+                       f"{dt_s:.2f} s per sampled iteration; oracle port (OpenMP C wavelets/prox, "
+                       f"scipy.fft workers={ncores} for ducc0.fft), host has {ncores} logical cores"),
+            "sec_per_sample_iter": round(dt_s, 3)}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    steps = max(1, min(a.steps, 3))
+    warm = max(1, min(a.warmup, 1))
+    cpu = cpu_reference(a, steps=steps, warmup=warm)
+    return {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT,
+            "n_gpus": a.gpus, "steps": steps, "warmup": warm,
+            "ms_per_step": round(1e3 / cpu["value"], 2), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "config": {"workload": workload_name(a), "nband": a.nband, "nx": a.nx, "ny": a.nx,
+                       "nxp": 2 * a.nx, "nyp": 2 * a.nx, "bases": BASES, "nlevels": NLEVEL,
+                       "note": "steps/warmup capped at 3/1: one CPU iteration of the full cube takes tens of seconds"},
+            "cpu_baseline": cpu,
+            "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+
+
+def main():
+    a = parse_args()
+    line = run_reference(a) if a.impl == "reference" else run_ours(a)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    try:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.barrier()
+            dist.destroy_process_group()
+    except Exception:
+        pass
+
+
+if __name__ == "__main__":
+    main()

@@ -47,6 +47,14 @@ const char *pfb_last_error(void);
  * gpu_launches is the difference around the timed region) */
 long long pfb_launch_count(void);
 
+/* Per-kernel device timing for bench.py's roofline: while enabled every kernel
+ * launch of the library is bracketed by CUDA events on its own stream.
+ * pfb_profile_report synchronises the device and writes one line per kernel
+ * symbol, "mangled_name\tlaunches\ttotal_ms\n", into buf (host memory).
+ * Enabling clears the previous records. */
+int pfb_profile_enable(int on);
+int pfb_profile_report(char *buf_host, long long buflen);
+
 /* ------------------------------------------------------------------ prox --
  * Coefficient arrays are (nband, n) with n = nbasis*Nymax*Nxmax flattened;
  * weight is (n).  Scalar math is fp64 as in the reference's numba kernels.   */

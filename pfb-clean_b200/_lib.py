@@ -29,6 +29,8 @@ _SIGS = {
     "pfb_version": (c_int, []),
     "pfb_last_error": (c_char_p, []),
     "pfb_launch_count": (c_longlong, []),
+    "pfb_profile_enable": (c_int, [c_int]),
+    "pfb_profile_report": (c_int, [c_char_p, c_longlong]),
     "pfb_prox21": (c_int, [_P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
     "pfb_dual_update": (c_int, [_P, _P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
     "pfb_dual_partial": (c_int, [_P, _P, _P, c_int, c_longlong, c_double, c_int, c_int, _P]),

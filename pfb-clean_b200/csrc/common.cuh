@@ -29,12 +29,25 @@ static inline void pfb_launch(void (*k)(KA...), dim3 g, dim3 b, size_t smem,
 using ::pfb_launch;
 #endif
 
+// Optional per-kernel timing (pfb_profile_*): when enabled, every launch is
+// bracketed by two CUDA events recorded on the launching stream; the report
+// groups them by kernel symbol.  Off by default (zero overhead).
+extern int g_profile_on;
+void profile_begin(const void *func, cudaStream_t st);
+void profile_end(cudaStream_t st);
+
 // every kernel launch of the library goes through here (counted)
 template <class... KA, class... A>
 static inline void launch(void (*k)(KA...), dim3 g, dim3 b, size_t smem,
                           cudaStream_t st, A... a) {
     ++g_launch_count;
+#ifndef PFB_EMU
+    if (g_profile_on) profile_begin((const void *)k, st);
+#endif
     pfb_launch(k, g, b, smem, st, a...);
+#ifndef PFB_EMU
+    if (g_profile_on) profile_end(st);
+#endif
 }
 
 #define PFB_CUDA_OK(expr)                                                      \

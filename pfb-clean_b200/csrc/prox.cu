@@ -8,11 +8,31 @@
 // (pfb/prox/prox_21m.py:30-61, 75-103; pfb/prox/prox_21.py:25-91).
 #include "common.cuh"
 #include <cstdarg>
+#include <map>
+#include <vector>
 
 namespace pfb {
 
 thread_local std::string g_last_error;
 long long g_launch_count = 0;
+
+int g_profile_on = 0;
+
+#ifndef PFB_EMU
+// one record per launch while profiling is on
+struct ProfRec { const void *func; cudaEvent_t e0, e1; };
+static std::vector<ProfRec> g_prof;
+
+void profile_begin(const void *func, cudaStream_t st) {
+    ProfRec r;
+    r.func = func;
+    cudaEventCreate(&r.e0);
+    cudaEventCreate(&r.e1);
+    cudaEventRecord(r.e0, st);
+    g_prof.push_back(r);
+}
+void profile_end(cudaStream_t st) { cudaEventRecord(g_prof.back().e1, st); }
+#endif
 
 int fail(int status, const char *fmt, ...) {
     char buf[512];
@@ -552,6 +572,48 @@ extern "C" {
 int pfb_version(void) { return 100; }
 const char *pfb_last_error(void) { return g_last_error.c_str(); }
 long long pfb_launch_count(void) { return g_launch_count; }
+
+/* profiling: see include/pfb_b200.h */
+int pfb_profile_enable(int on) {
+#ifndef PFB_EMU
+    if (on && !g_profile_on) {
+        for (auto &r : g_prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+        g_prof.clear();
+    }
+#endif
+    g_profile_on = on ? 1 : 0;
+    return PFB_OK;
+}
+
+int pfb_profile_report(char *buf, long long buflen) {
+    if (!buf || buflen < 2) return fail(PFB_ERR_BAD_ARG, "pfb_profile_report: bad buffer");
+    std::string out;
+#ifndef PFB_EMU
+    if (cudaDeviceSynchronize() != cudaSuccess)
+        return fail(PFB_ERR_CUDA, "pfb_profile_report: device synchronise failed");
+    struct Acc { long n; double ms; };
+    std::map<std::string, Acc> acc;
+    std::vector<std::string> order;
+    for (auto &r : g_prof) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.e0, r.e1);
+        const char *nm = nullptr;
+        std::string key = "?";
+        if (cudaFuncGetName(&nm, r.func) == cudaSuccess && nm) key = nm;
+        auto it = acc.find(key);
+        if (it == acc.end()) { acc[key] = Acc{1, (double)ms}; order.push_back(key); }
+        else { it->second.n += 1; it->second.ms += ms; }
+    }
+    char line[1024];
+    for (auto &k : order) {
+        snprintf(line, sizeof line, "%s\t%ld\t%.6f\n", k.c_str(), acc[k].n, acc[k].ms);
+        out += line;
+    }
+#endif
+    if ((long long)out.size() + 1 > buflen) return fail(PFB_ERR_BAD_ARG, "pfb_profile_report: buffer too small (%zu needed)", out.size() + 1);
+    memcpy(buf, out.c_str(), out.size() + 1);
+    return PFB_OK;
+}
 
 int pfb_prox21(const void *v, void *result, const void *weight, int nband, long long n,
                double lam, double sigma, int mode, int dtype, void *stream) {

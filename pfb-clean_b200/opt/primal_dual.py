@@ -26,6 +26,7 @@ import torch
 
 from .. import _dev, _lib, parallel
 from ..operators.psi import Psi
+from ..operators.psf import _convolve
 from ..prox import _common as _prox
 from ..utils.misc import norm_diff_terms
 from . import _vec
@@ -45,6 +46,20 @@ class Grad21:
         if self._data_dev is None:
             self._data_dev = _dev.to_dev(self.data)
         return self._data_dev
+
+    def bound_psf(self):
+        """(psfhat, lastsize) when psf_convolve is the usual
+        partial(psf_convolve_cube, xpad, xhat, xout, psfhat, lastsize) of
+        pfb/workers/spotless.py:182 over THIS package's operator, else None.
+        Lets the solver convolve straight into its own device buffer instead
+        of bouncing through the caller's (possibly host) xout every iteration."""
+        from functools import partial as _partial
+        from ..operators import psf as _psf
+        f = self.psf_convolve
+        if (isinstance(f, _partial) and f.func in (_psf.psf_convolve_cube, _psf.psf_convolve_slice)
+                and len(f.args) == 5 and not f.keywords.get("x")):
+            return f.args[3], f.args[4]
+        return None
 
     def __call__(self, x):
         conv = self.psf_convolve(x)
@@ -121,6 +136,8 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         if gi.numel() and bool(torch.any(va.view(va.shape[0], -1)[:, gi] != 0)):
             gap_idx = gi
     fused_grad = isinstance(grad, Grad21)
+    bound = grad.bound_psf() if fused_grad else None
+    conv_buf = torch.empty_like(xa) if bound is not None else None
     data = grad.data_dev() if fused_grad else None
     if data is not None and data.dtype != xa.dtype:
         data = data.to(xa.dtype)
@@ -134,7 +151,10 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         psi(xprev, vcur)
         _dual_step(vprev, vcur, lam, sigma, w, n, bsum)          # vprev now holds 2v - vp
         psiH(vprev, xout)
-        g = _dev.to_dev(grad.psf_convolve(xprev) if fused_grad else grad(xprev))
+        if bound is not None:
+            g = _convolve(bound[0], bound[1], xprev, conv_buf)
+        else:
+            g = _dev.to_dev(grad.psf_convolve(xprev) if fused_grad else grad(xprev))
         if g.dtype != xa.dtype:
             g = g.to(xa.dtype)
         _vec.pd_primal(xcur, xprev, xout, g, data, tau, pos_kernel, terms)
