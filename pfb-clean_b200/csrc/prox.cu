@@ -57,8 +57,10 @@ __device__ __forceinline__ void st(T *p, const Pack<T, V> &x) {
 
 // ---------------------------------------------------------------------------
 // prox_21m_numba / prox_21_numba:  result = v * soft(|S|)/|S| / sigma
-// MAXB > 0: bands cached in registers (nband <= MAXB); MAXB == 0: re-read.
-template <class T, int V, int MAXB>
+// NB > 0: band count known at compile time -> all NB loads of a thread are
+// issued back to back (no per-band branch), which is what keeps enough bytes
+// in flight to saturate HBM; NB == 0: generic loop for nband > 8.
+template <class T, int V, int NB>
 __global__ void __launch_bounds__(256)
 k_prox21(const T *__restrict__ v, T *__restrict__ res, const T *__restrict__ w,
          int nband, long n, double lam, double sigma, int mode) {
@@ -66,20 +68,19 @@ k_prox21(const T *__restrict__ v, T *__restrict__ res, const T *__restrict__ w,
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long)gridDim.x * blockDim.x) {
         long k = i * V;
-        Pack<T, V> c[MAXB > 0 ? MAXB : 1];
+        Pack<T, V> c[NB > 0 ? NB : 1];
         double s[V];
 #pragma unroll
         for (int e = 0; e < V; ++e) s[e] = 0.0;
-        if (MAXB > 0) {
+        if (NB > 0) {
 #pragma unroll
-            for (int b = 0; b < MAXB; ++b)
-                if (b < nband) {
-                    c[b] = ld<T, V>(v + b * n + k);
+            for (int b = 0; b < NB; ++b) c[b] = ld<T, V>(v + b * n + k);
 #pragma unroll
-                    for (int e = 0; e < V; ++e) {
-                        double x = (double)c[b].v[e];
-                        s[e] += mode ? x * x : x;
-                    }
+            for (int b = 0; b < NB; ++b)
+#pragma unroll
+                for (int e = 0; e < V; ++e) {
+                    double x = (double)c[b].v[e];
+                    s[e] += mode ? x * x : x;
                 }
         } else {
             for (int b = 0; b < nband; ++b) {
@@ -104,15 +105,14 @@ k_prox21(const T *__restrict__ v, T *__restrict__ res, const T *__restrict__ w,
                 f[e] = soft / absv / sigma;
             }
         }
-        if (MAXB > 0) {
+        if (NB > 0) {
 #pragma unroll
-            for (int b = 0; b < MAXB; ++b)
-                if (b < nband) {
-                    Pack<T, V> o;
+            for (int b = 0; b < NB; ++b) {
+                Pack<T, V> o;
 #pragma unroll
-                    for (int e = 0; e < V; ++e) o.v[e] = (T)((double)c[b].v[e] * f[e]);
-                    st<T, V>(res + b * n + k, o);
-                }
+                for (int e = 0; e < V; ++e) o.v[e] = (T)((double)c[b].v[e] * f[e]);
+                st<T, V>(res + b * n + k, o);
+            }
         } else {
             for (int b = 0; b < nband; ++b) {
                 Pack<T, V> t = ld<T, V>(v + b * n + k), o;
@@ -129,9 +129,9 @@ k_prox21(const T *__restrict__ v, T *__restrict__ res, const T *__restrict__ w,
 // in primal_dual_optimised (pfb/opt/primal_dual.py:136-137).
 //   vt = vp + sigma*v;  a = |red(vt)|/sigma;  v = vt * (1 - max(a - lam w/sigma,0)/a)
 //   u  = 2 v - vp   (written to `u` when non-null; u may alias vp)
-// `bsum` (optional, n doubles... stored as T2=double) supports the band-sharded
-// multi-GPU path: see k_dual_partial / k_dual_apply below.
-template <class T, int V, int MAXB>
+// The raw vp/v packs stay in registers (vt is recomputed for the store instead
+// of being kept in fp64) so a thread has 2*NB 16-byte loads in flight.
+template <class T, int V, int NB>
 __global__ void __launch_bounds__(256)
 k_dual(const T *vp, T *v, const T *__restrict__ w, T *u, int nband, long n,
        double lam, double sigma, int mode) {
@@ -139,21 +139,22 @@ k_dual(const T *vp, T *v, const T *__restrict__ w, T *u, int nband, long n,
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long)gridDim.x * blockDim.x) {
         long k = i * V;
-        double vt[MAXB > 0 ? MAXB : 1][V];
+        Pack<T, V> pa[NB > 0 ? NB : 1], pc[NB > 0 ? NB : 1];
         double s[V];
 #pragma unroll
         for (int e = 0; e < V; ++e) s[e] = 0.0;
-        if (MAXB > 0) {
+        if (NB > 0) {
 #pragma unroll
-            for (int b = 0; b < MAXB; ++b)
-                if (b < nband) {
-                    Pack<T, V> a = ld<T, V>(vp + b * n + k), c = ld<T, V>(v + b * n + k);
+            for (int b = 0; b < NB; ++b) {
+                pa[b] = ld<T, V>(vp + b * n + k);
+                pc[b] = ld<T, V>(v + b * n + k);
+            }
 #pragma unroll
-                    for (int e = 0; e < V; ++e) {
-                        double x = (double)a.v[e] + sigma * (double)c.v[e];
-                        vt[b][e] = x;
-                        s[e] += mode ? x * x : x;
-                    }
+            for (int b = 0; b < NB; ++b)
+#pragma unroll
+                for (int e = 0; e < V; ++e) {
+                    double x = (double)pa[b].v[e] + sigma * (double)pc[b].v[e];
+                    s[e] += mode ? x * x : x;
                 }
         } else {
             for (int b = 0; b < nband; ++b) {
@@ -173,20 +174,19 @@ k_dual(const T *vp, T *v, const T *__restrict__ w, T *u, int nband, long n,
             f[e] = 1.0;
             if (a != 0.0) f[e] = 1.0 - fmax(a - lam * (double)wk.v[e] / sigma, 0.0) / a;
         }
-        if (MAXB > 0) {
+        if (NB > 0) {
 #pragma unroll
-            for (int b = 0; b < MAXB; ++b)
-                if (b < nband) {
-                    Pack<T, V> o, uo, a;
-                    if (u) a = ld<T, V>(vp + b * n + k);
+            for (int b = 0; b < NB; ++b) {
+                Pack<T, V> o, uo;
 #pragma unroll
-                    for (int e = 0; e < V; ++e) {
-                        o.v[e] = (T)(vt[b][e] * f[e]);
-                        if (u) uo.v[e] = (T)2 * o.v[e] - a.v[e];
-                    }
-                    st<T, V>(v + b * n + k, o);
-                    if (u) st<T, V>(u + b * n + k, uo);
+                for (int e = 0; e < V; ++e) {
+                    double x = (double)pa[b].v[e] + sigma * (double)pc[b].v[e];
+                    o.v[e] = (T)(x * f[e]);
+                    uo.v[e] = (T)2 * o.v[e] - pa[b].v[e];
                 }
+                st<T, V>(v + b * n + k, o);
+                if (u) st<T, V>(u + b * n + k, uo);
+            }
         } else {
             for (int b = 0; b < nband; ++b) {
                 Pack<T, V> a = ld<T, V>(vp + b * n + k), c = ld<T, V>(v + b * n + k), o, uo;
@@ -415,6 +415,41 @@ k_pd_primal(T *x, const T *__restrict__ xp, const T *__restrict__ xout,
     block_store<2>(acc, part);
 }
 
+// Flat, 128-bit vectorised form for positivity 0/1 (no cross-band coupling):
+// one thread handles V consecutive elements of the (nband*npix) cube.
+template <class T, int V>
+__global__ void __launch_bounds__(256)
+k_pd_primal_vec(T *x, const T *__restrict__ xp, const T *__restrict__ xout,
+                const T *__restrict__ conv, const T *__restrict__ data, T tau,
+                int positivity, long n, double *part) {
+    double acc[2] = {0.0, 0.0};
+    long nv = n / V;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+         i += (long)gridDim.x * blockDim.x) {
+        long k = i * V;
+        Pack<T, V> g = ld<T, V>(xout + k), p = ld<T, V>(xp + k), c, d, o;
+        if (conv) c = ld<T, V>(conv + k);
+        if (data) d = ld<T, V>(data + k);
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            T ge = g.v[e];
+            if (conv) {
+                T gr = c.v[e];
+                if (data) gr = gr - d.v[e];
+                ge = ge + gr;
+            }
+            T xi = p.v[e] - tau * ge;
+            if (positivity == 1 && xi < (T)0) xi = (T)0;
+            o.v[e] = xi;
+            T df = xi - p.v[e];
+            acc[0] += (double)(df * df);
+            acc[1] += (double)(xi * xi);
+        }
+        st<T, V>(x + k, o);
+    }
+    block_store<2>(acc, part);
+}
+
 // ---------------------------------------------------------------------------
 // PCG line update (pfb/opt/pcg.py:92-95, 97-101):
 //   x = xp + alpha*p;  r = rp + alpha*Ap;  y = M(r) with M(r) = minv*r
@@ -478,6 +513,14 @@ template <class T> static inline bool aligned16(const void *p) {
     return ((uintptr_t)p & 15) == 0;
 }
 
+// dispatch the band count to a compile-time constant (1..8), else generic
+#define PFB_NB_SWITCH(nband, CALL)                                            \
+    switch (nband) {                                                           \
+    case 1: CALL(1); break; case 2: CALL(2); break; case 3: CALL(3); break;    \
+    case 4: CALL(4); break; case 5: CALL(5); break; case 6: CALL(6); break;    \
+    case 7: CALL(7); break; case 8: CALL(8); break; default: CALL(0); break;   \
+    }
+
 template <class T>
 static int prox21_t(const T *v, T *res, const T *w, int nband, long n, double lam,
                     double sigma, int mode, cudaStream_t st) {
@@ -486,12 +529,12 @@ static int prox21_t(const T *v, T *res, const T *w, int nband, long n, double la
     dim3 b(256);
     if (vec) {
         dim3 g(stream_grid(n / V));
-        if (nband <= 8) launch(&k_prox21<T, V, 8>, g, b, 0, st, v, res, w, nband, n, lam, sigma, mode);
-        else launch(&k_prox21<T, V, 0>, g, b, 0, st, v, res, w, nband, n, lam, sigma, mode);
+#define PFB_CALL(NB) launch(&k_prox21<T, V, NB>, g, b, 0, st, v, res, w, nband, n, lam, sigma, mode)
+        PFB_NB_SWITCH(nband, PFB_CALL)
+#undef PFB_CALL
     } else {
         dim3 g(stream_grid(n));
-        if (nband <= 8) launch(&k_prox21<T, 1, 8>, g, b, 0, st, v, res, w, nband, n, lam, sigma, mode);
-        else launch(&k_prox21<T, 1, 0>, g, b, 0, st, v, res, w, nband, n, lam, sigma, mode);
+        launch(&k_prox21<T, 1, 0>, g, b, 0, st, v, res, w, nband, n, lam, sigma, mode);
     }
     PFB_CHECK_LAUNCH();
     return PFB_OK;
@@ -506,12 +549,12 @@ static int dual_t(const T *vp, T *v, const T *w, T *u, int nband, long n, double
     dim3 b(256);
     if (vec) {
         dim3 g(stream_grid(n / V));
-        if (nband <= 8) launch(&k_dual<T, V, 8>, g, b, 0, st, vp, v, w, u, nband, n, lam, sigma, mode);
-        else launch(&k_dual<T, V, 0>, g, b, 0, st, vp, v, w, u, nband, n, lam, sigma, mode);
+#define PFB_CALL(NB) launch(&k_dual<T, V, NB>, g, b, 0, st, vp, v, w, u, nband, n, lam, sigma, mode)
+        PFB_NB_SWITCH(nband, PFB_CALL)
+#undef PFB_CALL
     } else {
         dim3 g(stream_grid(n));
-        if (nband <= 8) launch(&k_dual<T, 1, 8>, g, b, 0, st, vp, v, w, u, nband, n, lam, sigma, mode);
-        else launch(&k_dual<T, 1, 0>, g, b, 0, st, vp, v, w, u, nband, n, lam, sigma, mode);
+        launch(&k_dual<T, 1, 0>, g, b, 0, st, vp, v, w, u, nband, n, lam, sigma, mode);
     }
     PFB_CHECK_LAUNCH();
     return PFB_OK;
@@ -710,7 +753,13 @@ int pfb_pd_primal(void *x, const void *xp, const void *xout, const void *conv,
     int rc = ensure_part();
     if (rc) return rc;
     cudaStream_t st = as_stream(stream);
-    if (dtype == PFB_F32)
+    long ntot = (long)nband * (long)npix;
+    bool al = (((uintptr_t)x | (uintptr_t)xp | (uintptr_t)xout | (uintptr_t)conv | (uintptr_t)data) & 15) == 0;
+    if (positivity != 2 && al && dtype == PFB_F32 && ntot % 4 == 0)
+        launch(&k_pd_primal_vec<float, 4>, dim3(kRedBlocks), dim3(256), 0, st, (float *)x, (const float *)xp, (const float *)xout, (const float *)conv, (const float *)data, (float)tau, positivity, ntot, g_part);
+    else if (positivity != 2 && al && dtype == PFB_F64 && ntot % 2 == 0)
+        launch(&k_pd_primal_vec<double, 2>, dim3(kRedBlocks), dim3(256), 0, st, (double *)x, (const double *)xp, (const double *)xout, (const double *)conv, (const double *)data, tau, positivity, ntot, g_part);
+    else if (dtype == PFB_F32)
         launch(&k_pd_primal<float>, dim3(kRedBlocks), dim3(256), 0, st, (float *)x, (const float *)xp, (const float *)xout, (const float *)conv, (const float *)data, (float)tau, positivity, nband, (long)npix, g_part);
     else if (dtype == PFB_F64)
         launch(&k_pd_primal<double>, dim3(kRedBlocks), dim3(256), 0, st, (double *)x, (const double *)xp, (const double *)xout, (const double *)conv, (const double *)data, tau, positivity, nband, (long)npix, g_part);
