@@ -19,25 +19,11 @@
 //                  (beam, /wsum, + sigmainv*x) fused into the store.
 // HBM traffic per band: x + out + psfhat^T + 4 x (nx x nyo2 complex) instead
 // of the reference's ~5 passes over the 4x larger padded arrays.
-#include "fft.cuh"
+#include "hess_fast.cuh"
 #include <cmath>
 #include <vector>
 
 namespace pfb {
-
-template <class T> struct Epilogue {
-    const T *beam;   // nullable, (nband, nx, ny)
-    const T *x;      // nullable: adds sigmainv * x
-    T wsum;          // used if has_wsum
-    T sigmainv;
-    int has_wsum;
-};
-
-struct HessDims {
-    int nband, nx, ny, nxp, nyp, nyo2, M;   // M = nyp/2
-    int twN;                                 // twiddle table length
-    int R;                                   // rows (or columns) per CTA
-};
 
 // ------------------------------------------------------------------ pass A
 template <class T, int MAXT>
@@ -180,7 +166,7 @@ __global__ void __launch_bounds__(MAXT) k_hess_rows_inv(const Cx<T> *__restrict_
 // psfhat (nband, nxp, nyo2) -> psfT (nband, nyo2, nxp) * scale
 template <class T>
 __global__ void k_psfhat_prepare(const Cx<T> *__restrict__ in, Cx<T> *__restrict__ out,
-                                 int nxp, int nyo2, T scale) {
+                                 int nxp, int nyo2, T scale, int deint) {
     __shared__ Cx<T> tile[32][33];
     int band = blockIdx.z;
     const Cx<T> *src = in + (long)band * nxp * nyo2;
@@ -195,7 +181,9 @@ __global__ void k_psfhat_prepare(const Cx<T> *__restrict__ in, Cx<T> *__restrict
         int c = c0 + i, r = r0 + threadIdx.x;
         if (r < nxp && c < nyo2) {
             Cx<T> v = tile[threadIdx.x][i];
-            dst[(long)c * nxp + r] = cx<T>(v.x * scale, v.y * scale);
+            // fast path: rows de-interleaved per column, [even rows | odd rows]
+            int rr = deint ? ((r & 1) * (nxp >> 1) + (r >> 1)) : r;
+            dst[(long)c * nxp + rr] = cx<T>(v.x * scale, v.y * scale);
         }
     }
 }
@@ -211,11 +199,17 @@ struct pfb_hess_plan {
     void *S;                 // (nband, nyo2, nx) complex scratch
     void *psfT;              // (nband, nyo2, nxp) complex, scaled
     int have_psf;
+    // fast path (hess_fast.cuh): nxp = 2H >= 2nx, nyp = 2M >= 2ny, H, M in [512, 4096]
+    int fast, RB, nsm;
+    void *tabM, *tabH;       // ct_fft stage tables for lengths M and H
+    void *twr;               // exp(-2 pi i k / nyp), k = 0..M
+    void *modg;              // exp(-2 pi i n / nxp), n = 0..H-1
 };
 
 namespace pfb {
 
 static const size_t kMaxSmem = 200 * 1024;
+static const size_t kMaxSmemFast = 224 * 1024;
 
 // kernels are compiled for several block-size caps so that the register
 // allocation always fits (1024 threads -> 64 regs, 512 -> 128, <= 256 -> 255)
@@ -238,10 +232,101 @@ static int hess_set_psf_t(pfb_hess_plan *p, const void *psfhat, cudaStream_t st)
     dim3 grid(cdiv(h.nyo2, 32), cdiv(h.nxp, 32), h.nband), block(32, 8);
     T scale = (T)(1.0 / ((double)h.nxp * (double)h.nyp));
     launch(&k_psfhat_prepare<T>, grid, block, 0, st, (const Cx<T> *)psfhat, (Cx<T> *)p->psfT,
-           h.nxp, h.nyo2, scale);
+           h.nxp, h.nyo2, scale, p->fast);
     PFB_CHECK_LAUNCH();
     p->have_psf = 1;
     return PFB_OK;
+}
+
+
+// ---------------------------------------------------------------- fast path
+static int persistent_grid(const void *func, int threads, size_t smem, int total, int nsm) {
+#ifdef PFB_EMU
+    (void)func; (void)threads; (void)smem; (void)nsm;
+    return total < 2 ? total : 2;
+#else
+    int per = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, func, threads, smem) != cudaSuccess || per < 1)
+        per = 1;
+    long g = (long)per * nsm;
+    return (int)(g < total ? g : total);
+#endif
+}
+
+template <class T, int M, int RB>
+static int fast_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
+    const HessDims &h = p->h;
+    size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
+    auto kern = &k_hessf_rows_fwd<T, M, RB>;
+    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int nbb = cdiv(h.nx, RB);
+    int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
+    launch(kern, dim3(grid), dim3(M / 8), smem, st, x, beam, (Cx<T> *)p->S, (const Cx<T> *)p->tabM,
+           (const Cx<T> *)p->twr, h, nbb);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+template <class T, int M, int RB>
+static int fast_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
+    const HessDims &h = p->h;
+    size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
+    auto kern = &k_hessf_rows_inv<T, M, RB>;
+    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int nbb = cdiv(h.nx, RB);
+    int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
+    launch(kern, dim3(grid), dim3(M / 8), smem, st, (const Cx<T> *)p->S, out, (const Cx<T> *)p->tabM,
+           (const Cx<T> *)p->twr, h, nbb, ep);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+template <class T, int H>
+static int fast_cols(pfb_hess_plan *p, cudaStream_t st) {
+    const HessDims &h = p->h;
+    size_t smem = sizeof(Cx<T>) * ((size_t)2 * ct_stride(H) + ct_tab_size(H));
+    auto kern = &k_hessf_cols<T, H>;
+    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = persistent_grid((const void *)kern, H / 8, smem, h.nyo2 * h.nband, p->nsm);
+    launch(kern, dim3(grid), dim3(H / 8), smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
+           (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+#define PFB_SIZE_SWITCH(n, CALL)                         \
+    switch (n) {                                         \
+    case 512: return CALL(512);                          \
+    case 1024: return CALL(1024);                        \
+    case 2048: return CALL(2048);                        \
+    case 4096: return CALL(4096);                        \
+    default: return fail(PFB_ERR_FFT_SIZE, "fast path: unsupported length %d", (int)(n)); \
+    }
+
+template <class T> static int fast_rows_fwd_d(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
+    if (p->RB == 4) {
+#define PFB_C(N) fast_rows_fwd<T, N, 4>(p, x, beam, st)
+        PFB_SIZE_SWITCH(p->h.M, PFB_C)
+#undef PFB_C
+    }
+#define PFB_C(N) fast_rows_fwd<T, N, 2>(p, x, beam, st)
+    PFB_SIZE_SWITCH(p->h.M, PFB_C)
+#undef PFB_C
+}
+template <class T> static int fast_rows_inv_d(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
+    if (p->RB == 4) {
+#define PFB_C(N) fast_rows_inv<T, N, 4>(p, out, ep, st)
+        PFB_SIZE_SWITCH(p->h.M, PFB_C)
+#undef PFB_C
+    }
+#define PFB_C(N) fast_rows_inv<T, N, 2>(p, out, ep, st)
+    PFB_SIZE_SWITCH(p->h.M, PFB_C)
+#undef PFB_C
+}
+template <class T> static int fast_cols_d(pfb_hess_plan *p, cudaStream_t st) {
+#define PFB_C(N) fast_cols<T, N>(p, st)
+    PFB_SIZE_SWITCH(p->h.nxp / 2, PFB_C)
+#undef PFB_C
 }
 
 template <class T>
@@ -251,7 +336,19 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
     const HessDims &h0 = p->h;
     const Cx<T> *tw = (const Cx<T> *)p->tw;
     Cx<T> *S = (Cx<T> *)p->S;
-    {
+    // the fast row passes use 2-element vector accesses on x / out / beam
+    const uintptr_t al = 2 * sizeof(T) - 1;
+    const bool fast_rows = p->fast && !(((uintptr_t)x | (uintptr_t)out | (uintptr_t)beam_in |
+                                         (uintptr_t)beam_out | (uintptr_t)addx) & al);
+    Epilogue<T> ep;
+    ep.beam = beam_out;
+    ep.x = addx;
+    ep.wsum = (T)wsum;
+    ep.sigmainv = (T)sigmainv;
+    ep.has_wsum = has_wsum;
+    if (fast_rows) {
+        if (int rc = fast_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
+    } else {
         HessDims h = h0;
         h.R = p->Rrow;
         size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.M) * h.R;
@@ -259,7 +356,9 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
         PFB_BY_THREADS(nthr, k_hess_rows_fwd, smem, dim3(cdiv(h.nx, h.R), h.nband), st,
                        x, beam_in, S, tw, p->drow, h);
     }
-    {
+    if (p->fast) {
+        if (int rc = fast_cols_d<T>(p, st)) return rc;
+    } else {
         HessDims h = h0;
         h.R = p->Rcol;
         size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.nxp) * h.R;
@@ -267,16 +366,12 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
         PFB_BY_THREADS(nthr, k_hess_cols, smem, dim3(cdiv(h.nyo2, h.R), h.nband), st,
                        S, (const Cx<T> *)p->psfT, tw, p->dcol, h);
     }
-    {
+    if (fast_rows) {
+        if (int rc = fast_rows_inv_d<T>(p, out, ep, st)) return rc;
+    } else {
         HessDims h = h0;
         h.R = p->Rrow;
         size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.M) * h.R;
-        Epilogue<T> ep;
-        ep.beam = beam_out;
-        ep.x = addx;
-        ep.wsum = (T)wsum;
-        ep.sigmainv = (T)sigmainv;
-        ep.has_wsum = has_wsum;
         int nthr = p->drow.NT * h.R;
         PFB_BY_THREADS(nthr, k_hess_rows_inv, smem, dim3(cdiv(h.nx, h.R), h.nband), st,
                        (const Cx<T> *)S, out, tw, p->drow, h, ep);
@@ -345,12 +440,63 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
         delete p;
         return fail(PFB_ERR_CUDA, "twiddle upload failed");
     }
+    // ---- fast path set-up (hess_fast.cuh)
+    {
+        int H = nxp / 2;
+        auto okN = [](int n) { return n == 512 || n == 1024 || n == 2048 || n == 4096; };
+        p->nsm = kNumSM;
+#ifndef PFB_EMU
+        int dev = 0, nsm = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && nsm > 0)
+            p->nsm = nsm;
+#endif
+        bool fast = okN(M) && okN(H) && nx <= H && ny <= M && (ny % 2 == 0) && !getenv("PFB_HESS_GENERIC");
+        if (fast) {
+            p->RB = 4;
+            while (p->RB > 2 && cs * ((size_t)p->RB * ct_stride(M) + ct_tab_size(M)) > kMaxSmemFast) p->RB >>= 1;
+            if (cs * ((size_t)p->RB * ct_stride(M) + ct_tab_size(M)) > kMaxSmemFast ||
+                cs * ((size_t)2 * ct_stride(H) + ct_tab_size(H)) > kMaxSmemFast)
+                fast = false;
+        }
+        if (fast) {
+            auto upload = [&](void **dst, int n, auto gen) -> bool {
+                std::vector<char> hbuf(cs * (size_t)n);
+                gen([&](int i, double c, double sn) {
+                    if (dtype == PFB_F32) { ((float *)hbuf.data())[2 * i] = (float)c; ((float *)hbuf.data())[2 * i + 1] = (float)sn; }
+                    else { ((double *)hbuf.data())[2 * i] = c; ((double *)hbuf.data())[2 * i + 1] = sn; }
+                });
+                return cudaMalloc(dst, hbuf.size()) == cudaSuccess &&
+                       cudaMemcpy(*dst, hbuf.data(), hbuf.size(), cudaMemcpyHostToDevice) == cudaSuccess;
+            };
+            auto lin = [](int n, int N) {
+                return [n, N](auto put) {
+                    for (int i = 0; i < n; ++i) {
+                        long double a = -2.0L * 3.14159265358979323846264338327950288L * (long double)i / (long double)N;
+                        put(i, (double)cosl(a), (double)sinl(a));
+                    }
+                };
+            };
+            bool ok2 = upload(&p->tabM, ct_tab_size(M), [&](auto put) { ct_fill_table(M, put); }) &&
+                       upload(&p->tabH, ct_tab_size(H), [&](auto put) { ct_fill_table(H, put); }) &&
+                       upload(&p->twr, M + 1, lin(M + 1, nyp)) && upload(&p->modg, H, lin(H, nxp));
+            if (!ok2) {
+                pfb_hess_plan_destroy(p);
+                return fail(PFB_ERR_ALLOC, "hessian plan (fast path tables) allocation failed");
+            }
+        }
+        p->fast = fast ? 1 : 0;
+    }
     *out = p;
     return PFB_OK;
 }
 
 int pfb_hess_plan_destroy(pfb_hess_plan *p) {
     if (!p) return PFB_OK;
+    if (p->tabM) cudaFree(p->tabM);
+    if (p->tabH) cudaFree(p->tabH);
+    if (p->twr) cudaFree(p->twr);
+    if (p->modg) cudaFree(p->modg);
     cudaFree(p->tw); cudaFree(p->S); cudaFree(p->psfT);
     delete p;
     return PFB_OK;

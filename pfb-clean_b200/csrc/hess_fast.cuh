@@ -1,0 +1,236 @@
+// Fast path of the PSF Hessian for the standard geometry nxp = 2H >= 2 nx,
+// nyp = 2M >= 2 ny (psf-oversize 2, pfb/parser/grid.yaml:65-67) with H, M
+// powers of two in [512, 8192].  Same three passes and the same scratch layout
+// S[band][k][row] as hess.cu, on the compile-time FFT core of fft_ct.cuh:
+//
+//  pass A  k_hessf_rows_fwd : persistent CTAs of two transform groups; a batch
+//          of RB (2 or 4) image rows is transformed two at a time, the real-FFT
+//          post-processing and the transposed store then run CTA-wide so that
+//          S is written in RB*sizeof(complex) runs.
+//  pass B  k_hessf_cols     : one column per CTA iteration.  Because only the
+//          first H = nxp/2 inputs are non-zero and only the first H outputs are
+//          needed, the length-2H transform pair is replaced by TWO independent
+//          length-H pairs on the even / odd spectrum:
+//              X[2j]   = FFT_H(a)[j]           X[2j+1] = FFT_H(a . w_2H^n)[j]
+//              y[n<H]  = IFFT_H(Y_even)[n] + conj(w_2H^n) IFFT_H(Y_odd)[n]
+//          Group 0 does the even half, group 1 the odd half, each with its own
+//          named barrier; psfhat is stored de-interleaved ([even | odd] per
+//          column) by pfb_hess_plan_set_psfhat so the multiply is coalesced.
+//  pass C  k_hessf_rows_inv : mirror of pass A (transposed gather, real-FFT
+//          pre-processing, inverse transform, crop + epilogue).
+#pragma once
+#include "fft_ct.cuh"
+
+namespace pfb {
+
+template <class T> struct Epilogue {
+    const T *beam;   // nullable, (nband, nx, ny)
+    const T *x;      // nullable: adds sigmainv * x
+    T wsum;          // used if has_wsum
+    T sigmainv;
+    int has_wsum;
+};
+
+struct HessDims {
+    int nband, nx, ny, nxp, nyp, nyo2, M;   // M = nyp/2
+    int twN;                                 // twiddle table length
+    int R;                                   // rows (or columns) per CTA
+};
+
+template <class T> struct V2;
+template <> struct V2<float> { typedef float2 type; };
+template <> struct V2<double> { typedef double2 type; };
+
+template <class T, int N>
+__device__ __forceinline__ void ct_load_table(Cx<T> *dst, const Cx<T> *__restrict__ src) {
+    for (int i = threadIdx.x; i < ct_tab_size(N); i += blockDim.x) dst[i] = src[i];
+}
+
+// ------------------------------------------------------------------ pass A
+// twr[k] = exp(-2 pi i k / nyp), k = 0..M
+template <class T, int M, int RB>
+__global__ void __launch_bounds__(M / 8, 1)
+k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__restrict__ S,
+                 const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twr, HessDims h,
+                 int nbatch_band) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
+    Cx<T> *tab = bufs + RB * ct_stride(M);
+    constexpr int NT = M / 16;
+    const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
+    const GroupBar bar{1 + g, NT};
+    ct_load_table<T, M>(tab, tabg);
+    __syncthreads();
+    typedef typename V2<T>::type T2;
+    const int total = nbatch_band * h.nband;
+    for (int batch = blockIdx.x; batch < total; batch += gridDim.x) {
+        const int band = batch / nbatch_band;
+        const int row0 = (batch - band * nbatch_band) * RB;
+#pragma unroll 1
+        for (int ph = 0; ph < RB / 2; ++ph) {
+            const int l = 2 * ph + g, row = row0 + l;
+            Cx<T> *buf = bufs + l * ct_stride(M);
+            Cx<T> v[16];
+            const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                const int c0 = 2 * (t + e * NT);
+                T2 a;
+                a.x = (T)0; a.y = (T)0;
+                if (row < h.nx && c0 < h.ny) {
+                    a = *reinterpret_cast<const T2 *>(x + ro + c0);
+                    if (beam) {
+                        T2 bm = *reinterpret_cast<const T2 *>(beam + ro + c0);
+                        a.x *= bm.x; a.y *= bm.y;
+                    }
+                }
+                v[e] = cx<T>(a.x, a.y);
+            }
+            ct_fft<T, M, -1>(v, t, buf, tab, bar);
+            bar();
+            Cx<T> *q = buf + ct_pad(t);
+#pragma unroll
+            for (int e = 0; e < 16; ++e) q[e * (NT + NT / 16)] = v[e];
+        }
+        __syncthreads();
+        // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
+        for (int i = threadIdx.x; i < (M + 1) * RB; i += 2 * NT) {
+            const int l = i & (RB - 1), k = i / RB;
+            const Cx<T> *b2 = bufs + l * ct_stride(M);
+            const Cx<T> zk = b2[ct_pad(k & (M - 1))], zm = cconj(b2[ct_pad((M - k) & (M - 1))]);
+            const Cx<T> E = cx<T>((T)0.5 * (zk.x + zm.x), (T)0.5 * (zk.y + zm.y));
+            const Cx<T> D = cx<T>((T)0.5 * (zk.x - zm.x), (T)0.5 * (zk.y - zm.y));
+            const Cx<T> O = cx<T>(D.y, -D.x);
+            const Cx<T> X = E + cmul(twr[k], O);
+            if (row0 + l < h.nx) S[((long)band * h.nyo2 + k) * h.nx + row0 + l] = X;
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ pass B
+// psfE: (nband, nyo2, 2H) de-interleaved [even rows | odd rows], pre-scaled.
+// modg[n] = exp(-2 pi i n / (2H)), n < H.
+template <class T, int H>
+__global__ void __launch_bounds__(H / 8, 1)
+k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__ tabg,
+             const Cx<T> *__restrict__ modg, HessDims h) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
+    Cx<T> *tab = bufs + 2 * ct_stride(H);
+    constexpr int NT = H / 16;
+    const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
+    const GroupBar bar{1 + g, NT};
+    ct_load_table<T, H>(tab, tabg);
+    __syncthreads();
+    Cx<T> *buf = bufs + g * ct_stride(H);
+    const int total = h.nyo2 * h.nband;
+    for (int col = blockIdx.x; col < total; col += gridDim.x) {
+        Cx<T> *line = S + (long)col * h.nx;
+        const Cx<T> *pl = psfE + (long)col * (2 * H) + g * H;
+        Cx<T> v[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            const int i = t + e * NT;
+            v[e] = i < h.nx ? line[i] : cx<T>((T)0, (T)0);
+        }
+        if (g == 1) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], modg[t + e * NT]);
+        }
+        ct_fft<T, H, -1>(v, t, buf, tab, bar);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], pl[t + e * NT]);
+        ct_fft<T, H, +1>(v, t, buf, tab, bar);
+        if (g == 1) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], cconj(modg[t + e * NT]));
+        }
+        bar();                                   // the group's last exchange reads are done
+        {
+            Cx<T> *q = buf + ct_pad(t);
+#pragma unroll
+            for (int e = 0; e < 16; ++e) q[e * (NT + NT / 16)] = v[e];
+        }
+        __syncthreads();
+        {   // y = even + odd; group g stores slots e in [8g, 8g+8)
+            const Cx<T> *q0 = bufs + ct_pad(t), *q1 = bufs + ct_stride(H) + ct_pad(t);
+#pragma unroll
+            for (int e8 = 0; e8 < 8; ++e8) {
+                const int e = 8 * g + e8, i = t + e * NT;
+                const Cx<T> y = q0[e * (NT + NT / 16)] + q1[e * (NT + NT / 16)];
+                if (i < h.nx) line[i] = y;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ pass C
+template <class T, int M, int RB>
+__global__ void __launch_bounds__(M / 8, 1)
+k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
+                 const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twr, HessDims h,
+                 int nbatch_band, Epilogue<T> ep) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
+    Cx<T> *tab = bufs + RB * ct_stride(M);
+    constexpr int NT = M / 16;
+    const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
+    const GroupBar bar{1 + g, NT};
+    ct_load_table<T, M>(tab, tabg);
+    __syncthreads();
+    typedef typename V2<T>::type T2;
+    const int total = nbatch_band * h.nband;
+    for (int batch = blockIdx.x; batch < total; batch += gridDim.x) {
+        const int band = batch / nbatch_band;
+        const int row0 = (batch - band * nbatch_band) * RB;
+        for (int i = threadIdx.x; i < (M + 1) * RB; i += 2 * NT) {
+            const int l = i & (RB - 1), k = i / RB;
+            Cx<T> X = cx<T>((T)0, (T)0);
+            if (row0 + l < h.nx) X = S[((long)band * h.nyo2 + k) * h.nx + row0 + l];
+            bufs[l * ct_stride(M) + ct_pad(k)] = X;
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (int ph = 0; ph < RB / 2; ++ph) {
+            const int l = 2 * ph + g, row = row0 + l;
+            Cx<T> *buf = bufs + l * ct_stride(M);
+            // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m])
+            Cx<T> v[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                const int m = t + e * NT;
+                const Cx<T> xm = buf[ct_pad(m)], xr = cconj(buf[ct_pad(M - m)]);
+                const Cx<T> A = xm + xr, B = xm - xr;
+                const Cx<T> wB = cmul(cconj(twr[m]), B);
+                v[e] = cx<T>(A.x - wB.y, A.y + wB.x);
+            }
+            ct_fft<T, M, +1>(v, t, buf, tab, bar);
+            if (row < h.nx) {
+                const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const int c0 = 2 * (t + e * NT);
+                    if (c0 < h.ny) {
+                        T2 o;
+                        o.x = v[e].x; o.y = v[e].y;
+                        if (ep.beam) {
+                            T2 bm = *reinterpret_cast<const T2 *>(ep.beam + ro + c0);
+                            o.x *= bm.x; o.y *= bm.y;
+                        }
+                        if (ep.has_wsum) { o.x /= ep.wsum; o.y /= ep.wsum; }
+                        if (ep.x) {
+                            T2 xx = *reinterpret_cast<const T2 *>(ep.x + ro + c0);
+                            o.x += xx.x * ep.sigmainv; o.y += xx.y * ep.sigmainv;
+                        }
+                        *reinterpret_cast<T2 *>(out + ro + c0) = o;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace pfb

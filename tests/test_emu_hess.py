@@ -54,7 +54,8 @@ def test_hess_golden(tag):
 
 @pmp("dtype", [np.float32, np.float64])
 @pmp("nx,ny,nxp,nyp", [(8, 6, 16, 32), (20, 40, 64, 128), (100, 64, 256, 128), (30, 200, 32, 512),
-                             (6, 10, 4096, 64), (4, 10, 16, 8192), (5, 4, 8192, 32)])
+                             (6, 10, 4096, 64), (4, 10, 16, 8192), (5, 4, 8192, 32),
+                             (10, 12, 1024, 1024), (7, 30, 2048, 1024)])   # fast path (hess_fast.cuh)
 def test_hess_oracle(dtype, nx, ny, nxp, nyp):
     rng = np.random.default_rng(11)
     nband = 2
