@@ -74,20 +74,22 @@ def _is_psi_pair(psi, psiH):
             and getattr(psiH, "__func__", None) is Psi.hdot)
 
 
-def _dual_step(vp, v, lam, sigma, w, n, bsum):
-    """v <- dual update(vp, v); vp <- 2 v - vp.  Sharded: split around the
-    all-reduce of the band-sum slab."""
+def _dual_step(vp, v, lam, sigma, w, n, bsum, write_u=True):
+    """v <- dual update(vp, v); if write_u: vp <- 2 v - vp (else the caller
+    fuses 2v - vp into the Psi.hdot loader and vp is left untouched).
+    Sharded: split around the all-reduce of the band-sum slab."""
     L = _lib.lib()
     nb = v.shape[0]
+    u = _dev.ptr(vp) if write_u else None
     if parallel.active():
         _lib.check(L.pfb_dual_partial(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(bsum), nb, n, float(sigma),
                                       _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
         parallel.allreduce_sum(bsum)
-        _lib.check(L.pfb_dual_apply(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(bsum), _dev.ptr(w), _dev.ptr(vp),
+        _lib.check(L.pfb_dual_apply(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(bsum), _dev.ptr(w), u,
                                     nb, n, float(lam), float(sigma), _lib.BAND_SUM, _dev.dcode(v),
                                     _dev.stream()))
     else:
-        _lib.check(L.pfb_dual_update(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(w), _dev.ptr(vp), nb, n,
+        _lib.check(L.pfb_dual_update(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(w), u, nb, n,
                                      float(lam), float(sigma), _lib.BAND_SUM, _dev.dcode(v),
                                      _dev.stream()))
 
@@ -149,8 +151,12 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     broke = False
     for k in range(maxit):
         psi(xprev, vcur)
-        _dual_step(vprev, vcur, lam, sigma, w, n, bsum)          # vprev now holds 2v - vp
-        psiH(vprev, xout)
+        if fast:   # `vp = 2v - vp` (primal_dual.py:137) is fused into the synthesis loader
+            _dual_step(vprev, vcur, lam, sigma, w, n, bsum, write_u=False)
+            psi.__self__.hdot(vcur, xout, alpha2=vprev)
+        else:
+            _dual_step(vprev, vcur, lam, sigma, w, n, bsum)      # vprev now holds 2v - vp
+            psiH(vprev, xout)
         if bound is not None:
             g = _convolve(bound[0], bound[1], xprev, conv_buf)
         else:
