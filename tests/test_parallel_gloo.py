@@ -1,0 +1,104 @@
+"""Band-sharded (multi-GPU) control flow on CPU: two gloo ranks, each holding
+one of the two bands of the reference's golden problem, run the sharded
+primal-dual / PCG / power-method code paths (pfb_b200.parallel) on the emulator
+build of the kernels and must reproduce the single-process golden vectors of the
+unmodified reference (tests/golden/solve_f64.npz)."""
+import os
+import sys
+from functools import partial
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+
+def rel(a, b):
+    return np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300)
+
+
+def _worker(rank, world, port, q):
+    try:
+        sys.path.insert(0, ROOT)
+        sys.path.insert(0, HERE)
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        import pfb_b200  # noqa: F401
+        import pfb_b200._lib as L
+        import pfb_b200._dev as D
+        from emu.emulib import emu
+        L._LIB = emu()
+        D._EMULATED = True
+        from pfb_b200 import parallel
+        from pfb_b200.operators.psf import psf_convolve_cube
+        from pfb_b200.operators.hessian import hessian_psf_cube
+        from pfb_b200.operators.psi import Psi
+        from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
+        from pfb_b200.opt.power_method import power_method
+        from pfb_b200.opt.pcg import pcg
+        parallel.enable()
+        g = np.load(os.path.join(HERE, "golden", "solve_f64.npz"))
+        nband = g["dirty"].shape[0]
+        sl = parallel.band_slice(nband)
+        psfhat, dirty = np.ascontiguousarray(g["psfhat"][sl]), np.ascontiguousarray(g["dirty"][sl])
+        nbl, nx, ny = dirty.shape
+        nyp = 2 * (psfhat.shape[2] - 1)
+        bases = [str(b) for b in g["bases"]]
+        res = {}
+        xout = np.empty_like(dirty)
+        conv = partial(psf_convolve_cube, None, None, xout, psfhat, nyp)
+        beta, b = power_method(conv, dirty.shape, b0=np.ascontiguousarray(g["pm_b0"][sl]), tol=1e-3,
+                               maxit=40, verbosity=0)
+        res["pm_beta"] = abs(beta / float(g["pm_beta"]) - 1)
+        res["pm_b"] = rel(b, g["pm_b"][sl])
+        psi = Psi(nbl, nx, ny, bases, int(g["nlevel"]), 1)
+        for pos in (1, 2):
+            x = np.zeros_like(dirty)
+            v = np.zeros((nbl, len(bases), psi.Nymax, psi.Nxmax))
+            w = np.ones(v.shape[1:])
+            primal_dual_optimised(x, v, float(g["lam"]), psi.hdot, psi.dot, float(g["hessnorm"]), None,
+                                  w, None, Grad21(conv, dirty), nu=len(bases), tol=0.0, maxit=10,
+                                  positivity=pos, verbosity=0)
+            res[f"pd_x{pos}"] = rel(x, g[f"pdo_x_pos{pos}"][sl])
+            res[f"pd_v{pos}"] = rel(v, g[f"pdo_v_pos{pos}"][sl])
+        A = partial(hessian_psf_cube, None, None, None, None, psfhat, nyp, sigmainv=1e-3, wsum=None)
+        xs = pcg(A, dirty, np.zeros_like(dirty), M=None, tol=0.0, maxit=10, minit=10, verbosity=0)
+        res["pcg_x"] = rel(xs, g["pcg_x"][sl])
+        q.put((rank, res))
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:   # pragma: no cover
+        import traceback
+        q.put((rank, {"error": traceback.format_exc() + str(e)}))
+
+
+def test_band_sharded_two_ranks():
+    sys.path.insert(0, HERE)
+    from emu.build_emu import build
+    build()                       # compile once in the parent, not in both ranks
+    from oracle import ref
+    ref.build()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = {}
+    for _ in range(2):
+        r, res = q.get(timeout=600)
+        out[r] = res
+    for p in procs:
+        p.join(timeout=60)
+    for r in range(2):
+        assert "error" not in out[r], out[r].get("error")
+        assert out[r]["pm_beta"] < 1e-12 and out[r]["pm_b"] < 1e-10, out[r]
+        for pos in (1, 2):
+            assert out[r][f"pd_x{pos}"] < 1e-11, out[r]
+            assert out[r][f"pd_v{pos}"] < 1e-11, out[r]
+        assert out[r]["pcg_x"] < 1e-10, out[r]
