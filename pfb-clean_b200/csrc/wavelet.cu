@@ -29,6 +29,12 @@ static const int TX = 32, TY = 32;   // tile of coefficient positions
 static const int NS = 4;             // outputs per thread along the filter axis
 
 __constant__ double c_taps[5][4][10] = PFB_TAPS_INIT;
+__constant__ float c_tapsf[5][4][10] = PFB_TAPS_INIT;   // same taps rounded once to fp32
+
+// tap as an operand of type T (compile-time indices fold into a constant-bank operand)
+template <class T> __device__ __forceinline__ T tapc(int n, int which, int k);
+template <> __device__ __forceinline__ float tapc<float>(int n, int which, int k) { return c_tapsf[n][which][k]; }
+template <> __device__ __forceinline__ double tapc<double>(int n, int which, int k) { return c_taps[n][which][k]; }
 
 // per-basis description of one level (device-visible, passed by value)
 struct LevelDesc {
@@ -213,6 +219,10 @@ k_dwt_level(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out,
     case 10: ana_tile<T, 10>(in, ld, d, slab, a.Nxmax, ll, a.last, tile0, tile1, smem); break;
     }
 }
+
+}  // namespace pfb
+#include "wavelet_stream.cuh"
+namespace pfb {
 
 // shared memory (elements of T) needed by k_dwt_level
 static const int kAnaSmemElems = 72 * 73 + 2 * TY * 73;
@@ -454,17 +464,23 @@ static int ensure_scratch(const pfb_psi_plan *cp) {
     return PFB_OK;
 }
 
+static inline int round4(int n) { return (n + 3) & ~3; }
+
 template <class T>
 static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t st) {
     if (int rc = ensure_scratch(p)) return rc;
     size_t smem = sizeof(T) * kAnaSmemElems;
     PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_level<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     T *A = (T *)p->scrA, *B = (T *)p->scrB;
+    // streaming kernel: 4-element vector loads of image rows, F <= 8
+    bool stream = (p->ny % 2 == 0) && (((uintptr_t)x & 15) == 0) && !getenv("PFB_DWT_TILE");
+    for (int b = 0; b < p->nbasis; ++b)
+        if (p->bp[b].F > 8) stream = false;
     for (int l = 0; l < p->nlevel; ++l) {
         LevelArgs a;
         memset(&a, 0, sizeof a);
         fill_common(p, a, l);
-        int maxC0 = 0, maxC1 = 0;
+        int maxC0 = 0, maxC1 = 0, wC0 = 0, wC1 = 0;
         for (int b = 0; b < p->nbasis; ++b) {
             const BasisPlan &bp = p->bp[b];
             LevelDesc &d = a.d[b];
@@ -482,17 +498,40 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t s
             d.C1 = bp.sy[l];
             d.lowx = bp.highx[l] - 2 * bp.sx[l];
             d.lowy = bp.highy[l] - 2 * bp.sy[l];
-            d.ld_in = d.n1;
-            d.ld_out = d.C1;
+            d.ld_in = round4(d.n1);      // scratch rows padded to 16 bytes (fp32)
+            d.ld_out = round4(d.C1);
             maxC0 = std::max(maxC0, d.C0);
             maxC1 = std::max(maxC1, d.C1);
+            wC0 = std::max(wC0, d.C0);
+            wC1 = std::max(wC1, d.C1);
         }
         if (maxC0 == 0) continue;
+        const T *in = (l % 2 == 1) ? A : B;   // level l reads what level l-1 wrote
+        T *out = (l % 2 == 0) ? A : B;
+        if (stream) {
+            if (l == 0) {
+                for (int b = 0; b < p->nbasis; ++b)
+                    if (p->bp[b].F == 0) {
+                        dim3 grid(cdiv(p->ny, 64), cdiv(p->nx, 64), p->nband);
+                        launch(&k_self_dot<T>, grid, dim3(256), sizeof(T) * 64 * 65, st, x, alpha, a, b);
+                        PFB_CHECK_LAUNCH();
+                    }
+            }
+            if (wC0 == 0) continue;
+            int NJ = wC0 >= 1024 ? 128 : (wC0 >= 256 ? 64 : 32);
+            int nstrip = cdiv(wC1, kStripOut), nchunk = cdiv(wC0, NJ);
+            long ntask = (long)p->nband * nstrip * nchunk;      // per basis
+            int dbg = getenv("PFB_DWT_DBG") ? atoi(getenv("PFB_DWT_DBG")) : 0;   // experiments only
+            size_t sm2 = sizeof(T) * (stream_smem_warp(a.last ? 4 : 3) + stream_ring_elems()) * kStreamWarps;
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_stream<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+            launch(&k_dwt_stream<T>, dim3((unsigned)(((ntask + kStreamWarps - 1) / kStreamWarps) * p->nbasis)),
+                   dim3(32 * kStreamWarps), sm2, st, x, in, out, alpha, a, nstrip, nchunk, NJ, ntask, dbg);
+            PFB_CHECK_LAUNCH();
+            continue;
+        }
         a.ntile0 = cdiv(maxC0, TX);
         a.ntile1 = cdiv(maxC1, TY);
         dim3 grid(a.ntile1 * p->nbasis, a.ntile0, p->nband);
-        const T *in = (l % 2 == 1) ? A : B;   // level l reads what level l-1 wrote
-        T *out = (l % 2 == 0) ? A : B;
         launch(&k_dwt_level<T>, grid, dim3(256), smem, st, x, in, out, alpha, a);
         PFB_CHECK_LAUNCH();
     }
@@ -592,7 +631,7 @@ int pfb_psi_plan_create(pfb_psi_plan **out, int nband, int nx, int ny, int nbasi
             bp.highx[k] = lowx + bp.sx[k]; bp.highy[k] = lowy + bp.sy[k];
             lowx += bp.sx[k]; lowy += bp.sy[k];
         }
-        scr = std::max(scr, (long)(bp.sx[0] + 2) * (bp.sy[0] + 2));
+        scr = std::max(scr, (((long)(bp.sx[0] + 2) * (bp.sy[0] + 6)) + 3) & ~3L);
     }
     if (p->Nxmax == 0) {   // bases == ['self'] only: the reference cannot run this either
         delete p;

@@ -1,0 +1,247 @@
+// Streaming, register-resident analysis (DWT) level: the "warp-shuffle stencil"
+// form of dwt2d_level (pfb/wavelets/wavelets.py:126-171).
+//
+// One WARP owns a strip of 29 coefficient columns jy (y = contiguous image
+// axis) and walks down the image rows (x axis) of a chunk of NJ coefficient
+// rows jx:
+//   * each lane loads one 2-element vector per image row (256 B coalesced per
+//     warp and row, straight from global memory -- no shared-memory staging of
+//     the input);
+//   * the row pass (filter along y) takes its 6 halo values from the three lower
+//     lanes with warp shuffles (lanes 0..2 only carry halo => 29 outputs/strip);
+//   * the column pass (filter along x) keeps the last F-2 row-pass results in
+//     registers (shifted by two rows per step); the inner loops are pure FFMA
+//     with the taps as constant-bank operands and the loop body is small enough
+//     for the L0 instruction cache;
+//   * the reference layout is transposed w.r.t. the image (slab rows = y), so
+//     the three detail sub-bands (and LL on the last level) are staged through a
+//     per-warp shared-memory block of 32 jx and written as 128-byte runs;
+//     LL of a non-final level goes straight from registers to the next level's
+//     natural-orientation scratch (coalesced).
+// The tile kernel k_dwt_level of wavelet.cu stays as the generic path (image
+// rows not a multiple of 4 elements, or unaligned pointers).
+#pragma once
+
+namespace pfb {
+
+// ---------------------------------------------------------------------------
+// Geometry.  A lane owns ONE coefficient column: it loads the image pair
+// in[2t], in[2t+1] of every row (256 B per warp and row) and takes the 6 halo
+// values of the 8-tap window from lanes l-1..l-3 => lanes 0..2 carry halo only
+// and a warp strip yields 29 columns.  The transposed write-out block is 32 jx
+// wide, i.e. every slab store instruction writes one 128-byte run (measured on
+// B200: 8-wide runs cost 2.7 ms per Psi.dot at 8x4096^2, 16-wide 1.4 ms,
+// 32-wide 0.9 ms -- profiles/dbg_dwt.sh), and with one column per lane its
+// shared-memory staging (3 x 32 x 29 values) is small enough for 16 warps/SM.
+static const int kStripOut = 29;     // coefficient columns per warp strip
+static const int kJB = 32;           // jx per transposed write-out block
+static const int kPitch = 31;        // staging pitch (odd: conflict-free transposed reads)
+static const int kStreamWarps = 4;   // warps (independent tasks) per CTA
+__host__ __device__ constexpr int stream_smem_warp(int nq) { return nq * kJB * kPitch; }
+
+static const int kPD = 8;            // prefetch distance (coefficient rows in flight per warp)
+// ring of kPD x 2 image-row pairs per warp, filled with cp.async (LDGSTS): no
+// registers are tied up by the loads in flight and rows/columns outside the
+// image are zero-filled by the copy itself (src-size operand).
+__host__ __device__ constexpr int stream_ring_elems() { return kPD * 2 * 32 * 2; }
+
+template <int BYTES>
+__device__ __forceinline__ void cp_async_zfill(void *smem_dst, const void *gsrc, int src_bytes) {
+#ifdef PFB_EMU
+    unsigned char tmp[BYTES];
+    for (int i = 0; i < BYTES; ++i) tmp[i] = i < src_bytes ? ((const unsigned char *)gsrc)[i] : 0;
+    for (int i = 0; i < BYTES; ++i) ((unsigned char *)smem_dst)[i] = tmp[i];
+#else
+    unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+    if (BYTES == 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
+#endif
+}
+__device__ __forceinline__ void cp_async_commit() {
+#ifndef PFB_EMU
+    asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
+}
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+#ifndef PFB_EMU
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+#endif
+}
+
+template <class T> struct Vec2 { T v[2]; };
+__device__ __forceinline__ Vec2<float> ldv2(const float *p) {
+    float2 q = *reinterpret_cast<const float2 *>(p);
+    Vec2<float> r; r.v[0] = q.x; r.v[1] = q.y; return r;
+}
+__device__ __forceinline__ Vec2<double> ldv2(const double *p) {
+    double2 q = *reinterpret_cast<const double2 *>(p);
+    Vec2<double> r; r.v[0] = q.x; r.v[1] = q.y; return r;
+}
+
+// row pass of one image row for the lane's column: m = {lo, hi}
+template <class T, int F>
+__device__ __forceinline__ void dwt_row_pass(const Vec2<T> &q, T (&m)[2]) {
+    // window w[j] = in[2t - 6 + j], j = 0..7
+    T w[8];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        w[2 * j] = __shfl_up_sync(0xffffffffu, q.v[0], 3 - j);
+        w[2 * j + 1] = __shfl_up_sync(0xffffffffu, q.v[1], 3 - j);
+    }
+    w[6] = q.v[0];
+    w[7] = q.v[1];
+    m[0] = m[1] = (T)0;
+#pragma unroll
+    for (int k = 0; k < F; ++k) {
+        m[0] += tapc<T>(F / 2 - 1, 0, k) * w[7 - k];
+        m[1] += tapc<T>(F / 2 - 1, 1, k) * w[7 - k];
+    }
+}
+
+// The loop body handles ONE coefficient row jx (two image rows) and is kept
+// small on purpose: the warps of an SM run this loop independently of each
+// other, so the body has to fit the ~6 KB L0 instruction cache (an 8-row
+// unrolled version with a static register ring was bound by instruction fetch:
+// icc hit rate 65 %, `no_instruction` the top stall in profiles/r01d).  The F-2
+// previous row-pass results are shifted in registers.
+template <class T, int F>
+__device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const int ld,
+                                                const LevelDesc &d, T *slab, const int ldslab,
+                                                T *ll_out, const bool last, const int strip,
+                                                const int chunk, const int NJ, T *s_out,
+                                                T *ring, const int dbg) {
+    const int lane = threadIdx.x & 31;
+    const int T0 = kStripOut * strip;
+    const int c = 2 * T0 - 6 + 2 * lane;             // first column of this lane's pair
+    const bool cvalid = c >= 0 && c < ld;            // ld, c even
+    const int tl = lane - 3;                         // local output column (lanes 0..2: halo only)
+    const int ta = T0 + tl;
+    const bool tval = lane >= 3 && ta < d.C1;
+    const int JX0 = chunk * NJ;
+    const int jx_end = JX0 + NJ < d.C0 ? JX0 + NJ : d.C0;
+    const int s0 = last ? 0 : 1;                     // first staged sub-band
+    constexpr int NH = F > 2 ? F - 2 : 1;
+    T hs[NH][2];                                     // row-pass results of rows 2jx-1, 2jx-2, ...
+#pragma unroll
+    for (int i = 0; i < NH; ++i) hs[i][0] = hs[i][1] = (T)0;
+    int tmax0 = d.C1 - T0;
+    tmax0 = tmax0 < kStripOut ? tmax0 : kStripOut;
+    // bytes of this lane's pair that lie inside the image row (0 => zero fill)
+    const int cbytes = (!cvalid || (dbg & 4)) ? 0 : (c + 1 < d.n1 ? 2 : (c < d.n1 ? 1 : 0)) * (int)sizeof(T);
+    T *myring = ring + 2 * lane;                     // slot layout [iter % kPD][row 0/1][lane][2]
+    auto prefetch = [&](const int j) {               // rows 2j, 2j+1 -> ring slot j mod kPD
+        T *dst = myring + (j & (kPD - 1)) * 128;
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+            const int r = 2 * j + rr;
+            const bool ok = (unsigned)r < (unsigned)d.n0 && j < jx_end;
+            cp_async_zfill<2 * sizeof(T)>(dst + rr * 64, ok ? in + (long)r * ld + c : in, ok ? cbytes : 0);
+        }
+        cp_async_commit();
+    };
+    const int jx_first = JX0 - (F - 2) / 2;
+#pragma unroll 1
+    for (int j = jx_first; j < jx_first + kPD; ++j) prefetch(j);
+
+#pragma unroll 1
+    for (int jx = jx_first; jx < jx_end; ++jx) {
+        cp_async_wait<kPD - 1>();                    // the oldest group (this jx) has landed
+        const T *slot = myring + (jx & (kPD - 1)) * 128;
+        Vec2<T> q0 = ldv2(slot), q1 = ldv2(slot + 64);
+        prefetch(jx + kPD);                          // refill the slot just consumed
+        T m0[2], m1[2];
+        dwt_row_pass<T, F>(q0, m0);
+        dwt_row_pass<T, F>(q1, m1);
+        // column pass: out[jx] = sum_k f[k] mid[2jx+1-k]; k=0 -> m1, k=1 -> m0, k>=2 -> hs[k-2]
+        T o[4] = {(T)0, (T)0, (T)0, (T)0};
+#pragma unroll
+        for (int k = 0; k < F; ++k) {
+            const T lo = tapc<T>(F / 2 - 1, 0, k), hi = tapc<T>(F / 2 - 1, 1, k);
+            const T *mm = k == 0 ? m1 : (k == 1 ? m0 : hs[k >= 2 ? k - 2 : 0]);
+            o[0] += lo * mm[0];       // x-lo of y-lo -> TL (LL)
+            o[1] += hi * mm[0];       // x-hi of y-lo -> TR
+            o[2] += lo * mm[1];       // x-lo of y-hi -> BL
+            o[3] += hi * mm[1];       // x-hi of y-hi -> BR
+        }
+        if (F > 2) {                                 // shift the history by two rows
+#pragma unroll
+            for (int i = NH - 1; i >= 2; --i) { hs[i][0] = hs[i - 2][0]; hs[i][1] = hs[i - 2][1]; }
+            hs[1][0] = m0[0]; hs[1][1] = m0[1];
+            hs[0][0] = m1[0]; hs[0][1] = m1[1];
+        }
+        // staging (warm-up rows hit cells that are overwritten before the flush)
+        const int jxl = (jx - JX0) & (kJB - 1);
+        if (lane >= 3) {
+#pragma unroll
+            for (int s = 0; s < 4; ++s)
+                if (s > 0 || last) s_out[((s - s0) * kJB + jxl) * kPitch + tl] = o[s];
+        }
+        if (!last && jx >= JX0 && tval && !(dbg & 2)) ll_out[(long)jx * d.ld_out + ta] = o[0];
+        // flush a completed block of 32 jx: one slab row (128 B) per store instruction
+        if (jx >= JX0 && (jxl == kJB - 1 || jx == jx_end - 1)) {
+            __syncwarp();
+            const int fj = jx - jxl + lane;
+            const int tmax = (fj < jx_end && !(dbg & 1)) ? tmax0 : 0;
+            for (int s = s0; s < 4; ++s) {
+                const int qx = s & 1, qy = s >> 1;
+                T *dst = slab + (long)(d.lowy + qy * d.C1 + T0) * ldslab + d.lowx + qx * d.C0 + fj;
+                const T *src = s_out + ((s - s0) * kJB + lane) * kPitch;
+#pragma unroll 4
+                for (int t = 0; t < tmax; ++t) dst[(long)t * ldslab] = src[t];
+            }
+            __syncwarp();
+        }
+    }
+    cp_async_wait<0>();
+}
+
+// grid.x = nbasis * ceil(ntask / kStreamWarps), ntask = nband*nstrip*nchunk per basis.
+template <class T>
+__global__ void __launch_bounds__(32 * kStreamWarps)
+k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out, T *alpha,
+             LevelArgs a, int nstrip, int nchunk, int NJ, long ntask, int dbg) {
+    PFB_DYN_SMEM(raw);
+    const int warp = threadIdx.x >> 5;
+    T *ring = reinterpret_cast<T *>(raw) + warp * stream_ring_elems();       // 16-byte aligned
+    T *s_out = reinterpret_cast<T *>(raw) + kStreamWarps * stream_ring_elems() +
+               warp * stream_smem_warp(a.last ? 4 : 3);
+    // Basis-major CTA order: the CTAs resident on an SM at any time run the same
+    // filter length (one code variant in the instruction cache at a time).
+    const int cpb = gridDim.x / a.nbasis;            // CTAs per basis
+    const int basis = blockIdx.x / cpb;
+    long task = (long)(blockIdx.x - basis * cpb) * kStreamWarps + warp;
+    if (task >= ntask) return;
+    const int chunk = (int)(task % nchunk); task /= nchunk;
+    const int strip = (int)(task % nstrip);
+    const int band = (int)(task / nstrip);
+    const LevelDesc &d = a.d[basis];
+    if (d.F == 0 || kStripOut * strip >= d.C1 || chunk * NJ >= d.C0) return;
+    const long slabsz = (long)a.Nymax * a.Nxmax;
+    T *slab = alpha + ((long)band * a.nbasis + basis) * slabsz;
+    const long so = ((long)band * a.nbasis + basis) * a.scr_stride;
+    const T *in = a.first ? img + band * a.img_band_stride : scr_in + so;
+    const int ld = a.first ? a.ny : d.ld_in;
+    T *ll = scr_out + so;
+    switch (d.F) {
+    case 2: dwt_stream_task<T, 2>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    case 4: dwt_stream_task<T, 4>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    case 6: dwt_stream_task<T, 6>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    case 8: dwt_stream_task<T, 8>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    default: break;   // F = 10 (db5) is routed to the tile kernel by the host
+    }
+}
+
+// 'self' basis alone: alphao[i, 0:ny, 0:nx] = x.T (pfb/operators/psi.py:196-199)
+template <class T>
+__global__ void __launch_bounds__(256)
+k_self_dot(const T *__restrict__ img, T *alpha, LevelArgs a, int basis) {
+    PFB_DYN_SMEM(raw);
+    T *smem = reinterpret_cast<T *>(raw);
+    const int band = blockIdx.z;
+    T *slab = alpha + ((long)band * a.nbasis + basis) * (long)a.Nymax * a.Nxmax;
+    self_tile<T>(img + band * a.img_band_stride, a.nx, a.ny, slab, a.Nxmax, blockIdx.y, blockIdx.x, smem);
+}
+
+}  // namespace pfb

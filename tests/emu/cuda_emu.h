@@ -117,6 +117,18 @@ template <class T> static inline T __shfl_up_sync(unsigned, T v, unsigned d, int
     return emu_shfl(v, src);
 }
 
+static inline int __any_sync(unsigned, int pred) {
+    int w = emu::S.cur / 32, lane = emu::S.cur % 32;
+    unsigned char *slots = emu::S.warp_slots.data() + (size_t)w * 32 * 16;
+    int p = pred ? 1 : 0;
+    std::memcpy(slots + lane * 16, &p, sizeof(int));
+    emu::warp_barrier();
+    int lanes = std::min(32, emu::S.nthreads - w * 32), r = 0;
+    for (int l = 0; l < lanes; ++l) { int v; std::memcpy(&v, slots + l * 16, sizeof(int)); r |= v; }
+    emu::warp_barrier();
+    return r;
+}
+
 template <class T> static inline T atomicAdd(T *p, T v) { T o = *p; *p = o + v; return o; }
 static inline unsigned atomicOr(unsigned *p, unsigned v) { unsigned o = *p; *p = o | v; return o; }
 static inline int atomicMax(int *p, int v) { int o = *p; *p = std::max(o, v); return o; }
