@@ -524,7 +524,7 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t s
             int dbg = getenv("PFB_DWT_DBG") ? atoi(getenv("PFB_DWT_DBG")) : 0;   // experiments only
             size_t sm2 = sizeof(T) * (stream_smem_warp(a.last ? 4 : 3) + stream_ring_elems()) * kStreamWarps;
             PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_stream<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-            launch(&k_dwt_stream<T>, dim3((unsigned)(((ntask + kStreamWarps - 1) / kStreamWarps) * p->nbasis)),
+            launch(&k_dwt_stream<T>, dim3((unsigned)((long)p->nbasis * p->nband * nchunk * cdiv(nstrip, kStreamWarps))),
                    dim3(32 * kStreamWarps), sm2, st, x, in, out, alpha, a, nstrip, nchunk, NJ, ntask, dbg);
             PFB_CHECK_LAUNCH();
             continue;

@@ -197,7 +197,7 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
     cp_async_wait<0>();
 }
 
-// grid.x = nbasis * ceil(ntask / kStreamWarps), ntask = nband*nstrip*nchunk per basis.
+// grid.x = nbasis * nband * nchunk * ceil(nstrip / kStreamWarps)
 template <class T>
 __global__ void __launch_bounds__(32 * kStreamWarps)
 k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out, T *alpha,
@@ -207,15 +207,18 @@ k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out
     T *ring = reinterpret_cast<T *>(raw) + warp * stream_ring_elems();       // 16-byte aligned
     T *s_out = reinterpret_cast<T *>(raw) + kStreamWarps * stream_ring_elems() +
                warp * stream_smem_warp(a.last ? 4 : 3);
-    // Basis-major CTA order: the CTAs resident on an SM at any time run the same
-    // filter length (one code variant in the instruction cache at a time).
-    const int cpb = gridDim.x / a.nbasis;            // CTAs per basis
-    const int basis = blockIdx.x / cpb;
-    long task = (long)(blockIdx.x - basis * cpb) * kStreamWarps + warp;
-    if (task >= ntask) return;
-    const int chunk = (int)(task % nchunk); task /= nchunk;
-    const int strip = (int)(task % nstrip);
-    const int band = (int)(task / nstrip);
+    // CTA order: basis fastest, so the four filter banks of one image region run
+    // at the same time on neighbouring SMs and the image is read from DRAM once
+    // (then from L2); the warps of a CTA take ADJACENT strips of the same rows so
+    // that a DRAM page / L2 line of an image row is consumed while it is open.
+    const int basis = blockIdx.x % a.nbasis;
+    long cta = blockIdx.x / a.nbasis;
+    const int nsg = (nstrip + kStreamWarps - 1) / kStreamWarps;      // strip groups
+    const int sg = (int)(cta % nsg); cta /= nsg;
+    const int chunk = (int)(cta % nchunk);
+    const int band = (int)(cta / nchunk);
+    const int strip = sg * kStreamWarps + warp;
+    if (band >= a.nband) return;
     const LevelDesc &d = a.d[basis];
     if (d.F == 0 || kStripOut * strip >= d.C1 || chunk * NJ >= d.C0) return;
     const long slabsz = (long)a.Nymax * a.Nxmax;
