@@ -150,9 +150,10 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
     S = 2 * s * nx * nyo2                      # pruned half spectrum (pipeline intermediate)
     per_kernel = {                              # inputs + outputs of each kernel, counted once
         "k_dwt_level": None, "k_idwt_level": None,   # per-op figure used instead (3 launches each)
-        "k_dual": nb_local * 4 * C1 + C1,       # read vp,v ; write v,u ; weight once
+        "k_dwt_stream": None, "k_idwt_stream": None,
+        "k_dual": nb_local * 3 * C1 + C1,       # read vp,v ; write v ; weight once (2v-vp is fused into hdot)
         "k_dual_partial": nb_local * 3 * C1 + C1,
-        "k_dual_apply": nb_local * 4 * C1 + 2 * C1,
+        "k_dual_apply": nb_local * 3 * C1 + 2 * C1,   # read vp,v,bsum,w ; write v
         "k_hess_rows_fwd": nb_local * (P1 + S),
         "k_hess_cols": nb_local * (2 * S + psfhat),
         "k_hess_rows_inv": nb_local * (S + P1),
@@ -162,9 +163,9 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
         per_kernel["k_hessf_" + k] = per_kernel["k_hess_" + k]
     per_op = {                                  # SURVEY 8(d) table, x nb_local
         "psi_dot": nb_local * (P1 + C1),
-        "psi_hdot": nb_local * (C1 + P1),
+        "psi_hdot": nb_local * (2 * C1 + P1),   # hdot(2v - vp): both dual arrays are read
         "psf_convolve": nb_local * (2 * P1 + psfhat),
-        "dual_update+2v-vp": nb_local * 4 * C1 + C1,
+        "dual_update": nb_local * 3 * C1 + C1,
         "primal_update+eps": nb_local * 5 * P1,
     }
     fused_iter = nb_local * (3 * P1 + psfhat + 2 * C1) + C1     # SURVEY 8(d) headline lower bound
@@ -172,7 +173,7 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
 
 
 def short_kernel_name(mangled):
-    for k in ("k_dwt_level", "k_idwt_level", "k_dual_partial", "k_dual_apply", "k_dual",
+    for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_dual_partial", "k_dual_apply", "k_dual",
               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
               "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv", "k_pd_primal", "k_red_final",
               "k_norm_diff", "k_axpby", "k_dot", "k_prox21", "k_psfhat_prepare"):
@@ -380,7 +381,7 @@ def finish_ours(a, env):
         balg = per_kernel[dname]
         what = f"{dname}: inputs+outputs of this kernel once"
     else:   # wavelet level kernels: op-level bytes over the op's launches
-        op = "psi_dot" if dname == "k_dwt_level" else "psi_hdot"
+        op = "psi_dot" if dname in ("k_dwt_level", "k_dwt_stream") else "psi_hdot"
         balg = per_op[op] / NLEVEL
         what = f"{dname}: {op} algorithmic bytes / {NLEVEL} level launches"
     avg_s = dt_ms * 1e-3 / dn
@@ -396,10 +397,10 @@ def finish_ours(a, env):
             d["GBps"] = round(per_kernel[k] / (d["ms_per_step"] * 1e-3) / 1e9 / (kern[k][0] / K), 1)
             d["frac"] = round(d["GBps"] / hbm, 4)
     ops = {}
-    groups = {"psi_dot": ["k_dwt_level"], "psi_hdot": ["k_idwt_level"],
+    groups = {"psi_dot": ["k_dwt_level", "k_dwt_stream", "k_self_dot"], "psi_hdot": ["k_idwt_level", "k_idwt_stream"],
               "psf_convolve": ["k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
                                "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv"],
-              "dual_update+2v-vp": ["k_dual", "k_dual_partial", "k_dual_apply"],
+              "dual_update": ["k_dual", "k_dual_partial", "k_dual_apply"],
               "primal_update+eps": ["k_pd_primal"]}
     for op, ks in groups.items():
         t = sum(kern[k][1] for k in ks if k in kern) / K
@@ -513,7 +514,14 @@ def run_reference(a):
 
 def main():
     a = parse_args()
+    # libraries (NCCL prints its version banner) must not pollute the one-line stdout contract:
+    # everything written to fd 1 during the run goes to stderr, the JSON line to the real stdout
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     line = run_reference(a) if a.impl == "reference" else run_ours(a)
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
     if line is not None:
         print(json.dumps(line), flush=True)
     try:

@@ -77,12 +77,16 @@ int pfb_dual_update(const void *vp, void *v, const void *weight, void *u,
  * is vtilde_update + get_ratio + update, pfb/opt/primal_dual.py:183-222):
  *   partial: v <- vp + sigma*v ; bsum[k] = sum (or sum of squares) over the
  *            LOCAL bands.  The caller all-reduces bsum (SUM) across ranks.
- *   apply  : v <- v * (1 - max(a - lam w/sigma, 0)/a), a from bsum; u as above */
+ *   apply  : v <- v * (1 - max(a - lam w/sigma, 0)/a), a from bsum; u as above
+ * band_stride = elements between consecutive bands of vp / v (0 => n); a value
+ * > n lets the caller run the split on one basis slab of a (nband, nbasis, ...)
+ * array at a time, so that the all-reduce of basis b overlaps the kernels of
+ * basis b+1. */
 int pfb_dual_partial(const void *vp, void *v, void *bsum, int nband, long long n,
-                     double sigma, int mode, int dtype, void *stream);
+                     long long band_stride, double sigma, int mode, int dtype, void *stream);
 int pfb_dual_apply(const void *vp, void *v, const void *bsum, const void *weight,
-                   void *u, int nband, long long n, double lam, double sigma,
-                   int mode, int dtype, void *stream);
+                   void *u, int nband, long long n, long long band_stride, double lam,
+                   double sigma, int mode, int dtype, void *stream);
 
 /* ------------------------------------------------- fused vector updates --
  * Reductions accumulate in fp64 in a fixed order (bitwise reproducible) and

@@ -211,7 +211,7 @@ k_dual(const T *vp, T *v, const T *__restrict__ w, T *u, int nband, long n,
 template <class T, int V>
 __global__ void __launch_bounds__(256)
 k_dual_partial(const T *__restrict__ vp, T *v, T *__restrict__ bsum, int nband,
-               long n, double sigma, int mode) {
+               long n, long bs, double sigma, int mode) {
     long nv = n / V;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long)gridDim.x * blockDim.x) {
@@ -220,14 +220,14 @@ k_dual_partial(const T *__restrict__ vp, T *v, T *__restrict__ bsum, int nband,
 #pragma unroll
         for (int e = 0; e < V; ++e) s[e] = 0.0;
         for (int b = 0; b < nband; ++b) {
-            Pack<T, V> a = ld<T, V>(vp + b * n + k), c = ld<T, V>(v + b * n + k), o;
+            Pack<T, V> a = ld<T, V>(vp + b * bs + k), c = ld<T, V>(v + b * bs + k), o;
 #pragma unroll
             for (int e = 0; e < V; ++e) {
                 double x = (double)a.v[e] + sigma * (double)c.v[e];
                 o.v[e] = (T)x;
                 s[e] += mode ? x * x : x;
             }
-            st<T, V>(v + b * n + k, o);
+            st<T, V>(v + b * bs + k, o);
         }
         Pack<T, V> so;
 #pragma unroll
@@ -239,7 +239,7 @@ k_dual_partial(const T *__restrict__ vp, T *v, T *__restrict__ bsum, int nband,
 template <class T, int V>
 __global__ void __launch_bounds__(256)
 k_dual_apply(const T *vp, T *v, const T *__restrict__ bsum,
-             const T *__restrict__ w, T *u, int nband, long n, double lam,
+             const T *__restrict__ w, T *u, int nband, long n, long bs, double lam,
              double sigma, int mode) {
     long nv = n / V;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
@@ -255,15 +255,15 @@ k_dual_apply(const T *vp, T *v, const T *__restrict__ bsum,
             if (a != 0.0) f[e] = 1.0 - fmax(a - lam * (double)wk.v[e] / sigma, 0.0) / a;
         }
         for (int b = 0; b < nband; ++b) {
-            Pack<T, V> c = ld<T, V>(v + b * n + k), o, uo, a;
-            if (u) a = ld<T, V>(vp + b * n + k);
+            Pack<T, V> c = ld<T, V>(v + b * bs + k), o, uo, a;
+            if (u) a = ld<T, V>(vp + b * bs + k);
 #pragma unroll
             for (int e = 0; e < V; ++e) {
                 o.v[e] = (T)((double)c.v[e] * f[e]);
                 if (u) uo.v[e] = (T)2 * o.v[e] - a.v[e];
             }
-            st<T, V>(v + b * n + k, o);
-            if (u) st<T, V>(u + b * n + k, uo);
+            st<T, V>(v + b * bs + k, o);
+            if (u) st<T, V>(u + b * bs + k, uo);
         }
     }
 }
@@ -561,24 +561,24 @@ static int dual_t(const T *vp, T *v, const T *w, T *u, int nband, long n, double
 }
 
 template <class T>
-static int dual_partial_t(const T *vp, T *v, T *bsum, int nband, long n, double sigma,
+static int dual_partial_t(const T *vp, T *v, T *bsum, int nband, long n, long bs, double sigma,
                           int mode, cudaStream_t st) {
     const int V = 16 / sizeof(T);
-    bool vec = (n % V == 0) && aligned16<T>(v) && aligned16<T>(vp) && aligned16<T>(bsum);
-    if (vec) launch(&k_dual_partial<T, V>, dim3(stream_grid(n / V)), dim3(256), 0, st, vp, v, bsum, nband, n, sigma, mode);
-    else launch(&k_dual_partial<T, 1>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, bsum, nband, n, sigma, mode);
+    bool vec = (n % V == 0) && (bs % V == 0) && aligned16<T>(v) && aligned16<T>(vp) && aligned16<T>(bsum);
+    if (vec) launch(&k_dual_partial<T, V>, dim3(stream_grid(n / V)), dim3(256), 0, st, vp, v, bsum, nband, n, bs, sigma, mode);
+    else launch(&k_dual_partial<T, 1>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, bsum, nband, n, bs, sigma, mode);
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
 
 template <class T>
 static int dual_apply_t(const T *vp, T *v, const T *bsum, const T *w, T *u, int nband,
-                        long n, double lam, double sigma, int mode, cudaStream_t st) {
+                        long n, long bs, double lam, double sigma, int mode, cudaStream_t st) {
     const int V = 16 / sizeof(T);
-    bool vec = (n % V == 0) && aligned16<T>(v) && aligned16<T>(vp) && aligned16<T>(bsum) &&
+    bool vec = (n % V == 0) && (bs % V == 0) && aligned16<T>(v) && aligned16<T>(vp) && aligned16<T>(bsum) &&
                aligned16<T>(w) && aligned16<T>(u);
-    if (vec) launch(&k_dual_apply<T, V>, dim3(stream_grid(n / V)), dim3(256), 0, st, vp, v, bsum, w, u, nband, n, lam, sigma, mode);
-    else launch(&k_dual_apply<T, 1>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, bsum, w, u, nband, n, lam, sigma, mode);
+    if (vec) launch(&k_dual_apply<T, V>, dim3(stream_grid(n / V)), dim3(256), 0, st, vp, v, bsum, w, u, nband, n, bs, lam, sigma, mode);
+    else launch(&k_dual_apply<T, 1>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, bsum, w, u, nband, n, bs, lam, sigma, mode);
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
@@ -681,26 +681,28 @@ int pfb_dual_update(const void *vp, void *v, const void *weight, void *u, int nb
 }
 
 int pfb_dual_partial(const void *vp, void *v, void *bsum, int nband, long long n,
-                     double sigma, int mode, int dtype, void *stream) {
-    if (!vp || !v || !bsum || nband < 1 || n < 0)
+                     long long band_stride, double sigma, int mode, int dtype, void *stream) {
+    if (band_stride <= 0) band_stride = n;
+    if (!vp || !v || !bsum || nband < 1 || n < 0 || band_stride < n)
         return fail(PFB_ERR_BAD_ARG, "pfb_dual_partial: bad argument");
     if (n == 0) return PFB_OK;
     cudaStream_t st = as_stream(stream);
     PFB_DISPATCH(dtype,
-                 dual_partial_t<float>((const float *)vp, (float *)v, (float *)bsum, nband, n, sigma, mode, st),
-                 dual_partial_t<double>((const double *)vp, (double *)v, (double *)bsum, nband, n, sigma, mode, st));
+                 dual_partial_t<float>((const float *)vp, (float *)v, (float *)bsum, nband, n, band_stride, sigma, mode, st),
+                 dual_partial_t<double>((const double *)vp, (double *)v, (double *)bsum, nband, n, band_stride, sigma, mode, st));
 }
 
 int pfb_dual_apply(const void *vp, void *v, const void *bsum, const void *weight, void *u,
-                   int nband, long long n, double lam, double sigma, int mode, int dtype,
-                   void *stream) {
-    if (!vp || !v || !bsum || !weight || nband < 1 || n < 0)
+                   int nband, long long n, long long band_stride, double lam, double sigma,
+                   int mode, int dtype, void *stream) {
+    if (band_stride <= 0) band_stride = n;
+    if (!vp || !v || !bsum || !weight || nband < 1 || n < 0 || band_stride < n)
         return fail(PFB_ERR_BAD_ARG, "pfb_dual_apply: bad argument");
     if (n == 0) return PFB_OK;
     cudaStream_t st = as_stream(stream);
     PFB_DISPATCH(dtype,
-                 dual_apply_t<float>((const float *)vp, (float *)v, (const float *)bsum, (const float *)weight, (float *)u, nband, n, lam, sigma, mode, st),
-                 dual_apply_t<double>((const double *)vp, (double *)v, (const double *)bsum, (const double *)weight, (double *)u, nband, n, lam, sigma, mode, st));
+                 dual_apply_t<float>((const float *)vp, (float *)v, (const float *)bsum, (const float *)weight, (float *)u, nband, n, band_stride, lam, sigma, mode, st),
+                 dual_apply_t<double>((const double *)vp, (double *)v, (const double *)bsum, (const double *)weight, (double *)u, nband, n, band_stride, lam, sigma, mode, st));
 }
 
 int pfb_axpby(void *out, double a, const void *x, double b, const void *y, long long n,

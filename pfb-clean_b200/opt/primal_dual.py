@@ -74,6 +74,11 @@ def _is_psi_pair(psi, psiH):
             and getattr(psiH, "__func__", None) is Psi.hdot)
 
 
+def _off(t, nbytes):
+    import ctypes
+    return ctypes.c_void_p(t.data_ptr() + nbytes)
+
+
 def _dual_step(vp, v, lam, sigma, w, n, bsum, write_u=True):
     """v <- dual update(vp, v); if write_u: vp <- 2 v - vp (else the caller
     fuses 2v - vp into the Psi.hdot loader and vp is left untouched).
@@ -82,12 +87,24 @@ def _dual_step(vp, v, lam, sigma, w, n, bsum, write_u=True):
     nb = v.shape[0]
     u = _dev.ptr(vp) if write_u else None
     if parallel.active():
-        _lib.check(L.pfb_dual_partial(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(bsum), nb, n, float(sigma),
-                                      _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
-        parallel.allreduce_sum(bsum)
-        _lib.check(L.pfb_dual_apply(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(bsum), _dev.ptr(w), u,
-                                    nb, n, float(lam), float(sigma), _lib.BAND_SUM, _dev.dcode(v),
-                                    _dev.stream()))
+        # one basis slab at a time: the all-reduce of slab b (NCCL's own stream)
+        # overlaps the partial kernel of slab b+1 and the apply kernel of slab b-1
+        nbasis = v.shape[1]
+        nslab = n // nbasis
+        esz = v.element_size()
+        works = []
+        for b in range(nbasis):
+            off = b * nslab * esz
+            _lib.check(L.pfb_dual_partial(_off(vp, off), _off(v, off), _off(bsum, off), nb, nslab, n,
+                                          float(sigma), _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
+            works.append(parallel.allreduce_sum_async(bsum.view(nbasis, -1)[b]))
+        for b in range(nbasis):
+            off = b * nslab * esz
+            if works[b] is not None:
+                works[b].wait()
+            _lib.check(L.pfb_dual_apply(_off(vp, off), _off(v, off), _off(bsum, off), _off(w, off),
+                                        _off(vp, off) if write_u else None, nb, nslab, n, float(lam),
+                                        float(sigma), _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
     else:
         _lib.check(L.pfb_dual_update(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(w), u, nb, n,
                                      float(lam), float(sigma), _lib.BAND_SUM, _dev.dcode(v),

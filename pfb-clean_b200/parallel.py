@@ -48,6 +48,15 @@ def allreduce_sum(t):
     return t
 
 
+def allreduce_sum_async(t):
+    """SUM all-reduce issued asynchronously (NCCL runs it on its own stream after
+    the work already queued on the current stream); returns a work handle whose
+    .wait() makes the current stream wait for the result, or None when inactive."""
+    if not active():
+        return None
+    return dist.all_reduce(t, op=dist.ReduceOp.SUM, group=_STATE["group"], async_op=True)
+
+
 def allreduce_max(t):
     if active():
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=_STATE["group"])

@@ -48,12 +48,12 @@ def test_prox_dual(dtype, nband, shape, mode):
             h = nband // 2
             va, vb = v[:h].copy(), v[h:].copy()
             sa, sb = np.zeros(shape, dtype), np.zeros(shape, dtype)
-            ok(L.pfb_dual_partial(ptr(vp[:h].copy()), ptr(va), ptr(sa), h, n, sigma, mode, dt(v), None))
-            ok(L.pfb_dual_partial(ptr(vp[h:].copy()), ptr(vb), ptr(sb), nband - h, n, sigma, mode, dt(v), None))
+            ok(L.pfb_dual_partial(ptr(vp[:h].copy()), ptr(va), ptr(sa), h, n, 0, sigma, mode, dt(v), None))
+            ok(L.pfb_dual_partial(ptr(vp[h:].copy()), ptr(vb), ptr(sb), nband - h, n, 0, sigma, mode, dt(v), None))
             s = sa + sb
             ua, ub = np.zeros_like(va), np.zeros_like(vb)
-            ok(L.pfb_dual_apply(ptr(vp[:h].copy()), ptr(va), ptr(s), ptr(w), ptr(ua), h, n, lam, sigma, mode, dt(v), None))
-            ok(L.pfb_dual_apply(ptr(vp[h:].copy()), ptr(vb), ptr(s), ptr(w), ptr(ub), nband - h, n, lam, sigma, mode, dt(v), None))
+            ok(L.pfb_dual_apply(ptr(vp[:h].copy()), ptr(va), ptr(s), ptr(w), ptr(ua), h, n, 0, lam, sigma, mode, dt(v), None))
+            ok(L.pfb_dual_apply(ptr(vp[h:].copy()), ptr(vb), ptr(s), ptr(w), ptr(ub), nband - h, n, 0, lam, sigma, mode, dt(v), None))
             tol2 = tol if dtype == np.float64 else 5e-6   # fp32 slab sum
             assert rel(np.concatenate([va, vb]), exp) < tol2
             assert rel(np.concatenate([ua, ub]), 2 * exp - vp) < 10 * tol2
