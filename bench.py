@@ -173,7 +173,7 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
 
 
 def short_kernel_name(mangled):
-    for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_dual_partial", "k_dual_apply", "k_dual",
+    for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_slab_to_nat", "k_nat_to_slab", "k_dual_partial", "k_dual_apply", "k_dual",
               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
               "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv", "k_pd_primal", "k_red_final",
               "k_norm_diff", "k_axpby", "k_dot", "k_prox21", "k_psfhat_prepare"):
@@ -397,7 +397,7 @@ def finish_ours(a, env):
             d["GBps"] = round(per_kernel[k] / (d["ms_per_step"] * 1e-3) / 1e9 / (kern[k][0] / K), 1)
             d["frac"] = round(d["GBps"] / hbm, 4)
     ops = {}
-    groups = {"psi_dot": ["k_dwt_level", "k_dwt_stream", "k_self_dot"], "psi_hdot": ["k_idwt_level", "k_idwt_stream"],
+    groups = {"psi_dot": ["k_dwt_level", "k_dwt_stream", "k_self_dot"], "psi_hdot": ["k_idwt_level", "k_idwt_stream", "k_slab_to_nat"],
               "psf_convolve": ["k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
                                "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv"],
               "dual_update": ["k_dual", "k_dual_partial", "k_dual_apply"],

@@ -222,6 +222,7 @@ k_dwt_level(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out,
 
 }  // namespace pfb
 #include "wavelet_stream.cuh"
+#include "wavelet_syn_stream.cuh"
 namespace pfb {
 
 // shared memory (elements of T) needed by k_dwt_level
@@ -418,10 +419,19 @@ struct pfb_psi_plan {
     pfb::BasisPlan bp[pfb::kMaxBasis];
     long scr_stride;
     void *scrA, *scrB;
+    // natural-orientation coefficient scratch of the streaming synthesis
+    // (wavelet_syn_stream.cuh): per (band, basis) a block of cn_stride elements
+    int syn_ok;                                          // bases are distinct db1..db4 (+ one self)
+    long cn_stride;
+    long cn_off1[pfb::kMaxBasis][pfb::kMaxLevel];        // quadrant 1 of level l
+    int cn_ld[pfb::kMaxBasis][pfb::kMaxLevel];
+    void *cn;
 };
 
 namespace pfb {
 
+static inline int round4(int n) { return (n + 3) & ~3; }
+static inline int round32(int n) { return (n + 31) & ~31; }
 static int coeff_size(int n, int F) { return (n + F - 1) / 2; }
 static int signal_size(int c, int F) { return 2 * c - F + 2; }
 
@@ -463,8 +473,6 @@ static int ensure_scratch(const pfb_psi_plan *cp) {
     }
     return PFB_OK;
 }
-
-static inline int round4(int n) { return (n + 3) & ~3; }
 
 template <class T>
 static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t st) {
@@ -538,10 +546,107 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t s
     return PFB_OK;
 }
 
+static int ensure_cn(const pfb_psi_plan *cp) {
+    pfb_psi_plan *p = const_cast<pfb_psi_plan *>(cp);
+    if (p->cn) return PFB_OK;
+    size_t bytes = dtype_size(p->dtype) * (size_t)p->cn_stride * p->nband * p->nbasis;
+    if (cudaMalloc(&p->cn, bytes) != cudaSuccess) {
+        p->cn = nullptr;
+        return fail(PFB_ERR_ALLOC, "psi plan coefficient scratch allocation failed (%zu bytes)", bytes);
+    }
+    return PFB_OK;
+}
+
+// Streaming synthesis: slab -> natural orientation (fusing 2*alpha - alpha2),
+// then one k_idwt_stream launch per level (wavelet_syn_stream.cuh).
+template <class T>
+static int psi_hdot_stream(const pfb_psi_plan *p, const T *alpha, const T *alpha2, T *xo,
+                           cudaStream_t st) {
+    if (int rc = ensure_cn(p)) return rc;
+    T *cn = (T *)p->cn;
+    T *A = (T *)p->scrA, *B = (T *)p->scrB;
+    const int L = p->nlevel;
+    // step 1: transposes.  'self' on its own grid, then one launch per level.
+    for (int pass = -1; pass < L; ++pass) {
+        NatArgs na;
+        memset(&na, 0, sizeof na);
+        na.nbasis = p->nbasis; na.Nxmax = p->Nxmax; na.Nymax = p->Nymax; na.cn_stride = p->cn_stride;
+        int mr = 0, mc = 0;
+        for (int b = 0; b < p->nbasis; ++b) {
+            const BasisPlan &bp = p->bp[b];
+            if (pass < 0) {
+                if (bp.F != 0) continue;
+                NatBlk &k = na.b[na.nblk++];
+                k.basis = b; k.row0 = k.col0 = 0; k.nrow = p->ny; k.ncol = p->nx;
+                k.ldn = round32(p->ny); k.off = 0;
+                mr = std::max(mr, k.nrow); mc = std::max(mc, k.ncol);
+                continue;
+            }
+            if (bp.F == 0) continue;
+            const int l = pass, C0 = bp.sx[l], C1 = bp.sy[l], ldn = p->cn_ld[b][l];
+            const int lowx = bp.highx[l] - 2 * C0, lowy = bp.highy[l] - 2 * C1;
+            const long qsz = (long)C0 * ldn;
+            for (int q = (l == L - 1 ? 0 : 1); q < 4; ++q) {
+                NatBlk &k = na.b[na.nblk++];
+                k.basis = b;
+                k.row0 = lowy + (q >> 1) * C1; k.col0 = lowx + (q & 1) * C0;
+                k.nrow = C1; k.ncol = C0; k.ldn = ldn;
+                k.off = p->cn_off1[b][l] + (q - 1) * qsz;
+            }
+            mr = std::max(mr, C1); mc = std::max(mc, C0);
+        }
+        if (na.nblk == 0) continue;
+        dim3 grid(cdiv(mc, 32), cdiv(mr, 32), p->nband * na.nblk);
+        launch(&k_slab_to_nat<T>, grid, dim3(256), 0, st, alpha, alpha2, cn, na);
+        PFB_CHECK_LAUNCH();
+    }
+    // step 2: synthesis, coarsest level first
+    for (int l = L - 1; l >= 0; --l) {
+        SynArgs a;
+        memset(&a, 0, sizeof a);
+        a.nbasis = p->nbasis; a.nband = p->nband;
+        a.first = l == 0; a.last = l == L - 1;
+        a.n0 = p->nx; a.n1 = p->ny; a.ld_out = p->ny;
+        a.self_basis = -1; a.ld_self = round32(p->ny);
+        a.cn_stride = p->cn_stride; a.scr_stride = p->scr_stride;
+        a.img_band_stride = (long)p->nx * p->ny;
+        for (int s = 0; s < kSynSlots; ++s) a.s[s].basis = -1;
+        int mn0 = 0, mn1 = 0;
+        for (int b = 0; b < p->nbasis; ++b) {
+            const BasisPlan &bp = p->bp[b];
+            if (bp.F == 0) { if (l == 0) a.self_basis = b; continue; }
+            SynSlot &d = a.s[bp.F / 2 - 1];
+            d.basis = b;
+            d.C0 = bp.sx[l]; d.C1 = bp.sy[l];
+            d.ldn = p->cn_ld[b][l];
+            d.ld_ll = l + 1 < L ? round4(bp.spy[l + 1]) : 0;
+            d.n0 = bp.spx[l]; d.n1 = bp.spy[l];
+            d.ld_out = round4(bp.spy[l]);
+            d.qs = d.C0 * d.ldn;
+            d.off1 = p->cn_off1[b][l];
+            mn0 = std::max(mn0, d.n0); mn1 = std::max(mn1, d.n1);
+        }
+        if (l == 0) { mn0 = p->nx; mn1 = p->ny; }
+        const int h0 = mn0 / 2, h1 = mn1 / 2;
+        const int NJ = h0 >= 1024 ? 128 : (h0 >= 256 ? 64 : 32);
+        const int nstrip = cdiv(h1, kSynStrip), nchunk = cdiv(h0, NJ);
+        const int per_basis = l > 0;
+        const long nblk = (long)(per_basis ? kSynSlots : 1) * p->nband * nchunk * cdiv(nstrip, kSynWarps);
+        const T *in = ((L - 1 - l) % 2 == 1) ? A : B;
+        T *out = l == 0 ? xo : (((L - 1 - l) % 2 == 0) ? A : B);
+        launch(&k_idwt_stream<T>, dim3((unsigned)nblk), dim3(32 * kSynWarps), 0, st,
+               (const T *)cn, in, out, a, nstrip, nchunk, NJ, per_basis);
+        PFB_CHECK_LAUNCH();
+    }
+    return PFB_OK;
+}
+
 template <class T>
 static int psi_hdot_t(const pfb_psi_plan *p, const T *alpha, const T *alpha2, T *xo,
                       cudaStream_t st) {
     if (int rc = ensure_scratch(p)) return rc;
+    if (p->syn_ok && ((uintptr_t)xo % (2 * sizeof(T))) == 0 && !getenv("PFB_IDWT_TILE"))
+        return psi_hdot_stream<T>(p, alpha, alpha2, xo, st);
     size_t smem = sizeof(T) * kSynSmemElems;
     PFB_CUDA_OK(cudaFuncSetAttribute(&k_idwt_level<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     T *A = (T *)p->scrA, *B = (T *)p->scrB;
@@ -638,6 +743,29 @@ int pfb_psi_plan_create(pfb_psi_plan **out, int nband, int nx, int ny, int nbasi
         return fail(PFB_ERR_BAD_ARG, "at least one wavelet basis is required");
     }
     p->scr_stride = scr;   // scratch itself is allocated on first use
+    // natural-orientation layout for the streaming synthesis
+    p->syn_ok = 1;
+    int seen[6] = {0, 0, 0, 0, 0, 0};
+    for (int b = 0; b < nbasis; ++b) {
+        int id = p->basis_id[b];
+        if (id == 5 || seen[id]++) p->syn_ok = 0;
+        long tot = 0;
+        if (id == 0) {
+            tot = (long)nx * round32(ny);
+        } else {
+            const BasisPlan &bp = p->bp[b];
+            for (int l = 0; l < nlevel; ++l) {
+                int ldn = round32(bp.sy[l]);
+                long qsz = (long)bp.sx[l] * ldn;
+                if (qsz > (1L << 30)) p->syn_ok = 0;
+                if (l == nlevel - 1) tot += qsz;      // LL in front of quadrant 1
+                p->cn_off1[b][l] = tot;
+                p->cn_ld[b][l] = ldn;
+                tot += 3 * qsz;
+            }
+        }
+        p->cn_stride = std::max(p->cn_stride, tot);
+    }
     *out = p;
     return PFB_OK;
 }
@@ -646,6 +774,7 @@ int pfb_psi_plan_destroy(pfb_psi_plan *p) {
     if (!p) return PFB_OK;
     if (p->scrA) cudaFree(p->scrA);
     if (p->scrB) cudaFree(p->scrB);
+    if (p->cn) cudaFree(p->cn);
     delete p;
     return PFB_OK;
 }

@@ -80,6 +80,13 @@ __device__ __forceinline__ Vec2<double> ldv2(const double *p) {
     Vec2<double> r; r.v[0] = q.x; r.v[1] = q.y; return r;
 }
 
+__device__ __forceinline__ void stv2(float *p, const Vec2<float> &r) {
+    *reinterpret_cast<float2 *>(p) = make_float2(r.v[0], r.v[1]);
+}
+__device__ __forceinline__ void stv2(double *p, const Vec2<double> &r) {
+    *reinterpret_cast<double2 *>(p) = make_double2(r.v[0], r.v[1]);
+}
+
 // row pass of one image row for the lane's column: m = {lo, hi}
 template <class T, int F>
 __device__ __forceinline__ void dwt_row_pass(const Vec2<T> &q, T (&m)[2]) {

@@ -67,13 +67,15 @@ def test_psi_golden(tag):
 
 @pmp("dtype", [np.float32, np.float64])
 @pmp("nx,ny,nlevel", [(128, 78, 1), (250, 64, 2), (200, 136, 3)])
-def test_psi_roundtrip_and_oracle(dtype, nx, ny, nlevel):
+@pmp("bases", [['self', 'db1', 'db2', 'db3', 'db4', 'db5'],      # db5 -> tile kernels
+               ['self', 'db1', 'db2', 'db3', 'db4'],             # streaming kernels
+               ['db4', 'db2']], ids=["all6", "stream5", "db42"])
+def test_psi_roundtrip_and_oracle(dtype, nx, ny, nlevel, bases):
     """tests/test_psi_operator.py:18 of the reference: hdot(dot(x)) == nbasis*x,
     buffers pre-filled with random numbers; plus direct oracle comparison and
     the fused 2*alpha - alpha2 loader."""
     rng = np.random.default_rng(7)
     nband = 2
-    bases = ['self', 'db1', 'db2', 'db3', 'db4', 'db5']
     x = rng.standard_normal((nband, nx, ny)).astype(dtype)
     psi = EmuPsi(nband, nx, ny, bases, nlevel, dtype)
     opsi = ref.Psi(nband, nx, ny, bases, nlevel)
