@@ -145,6 +145,30 @@ int pfb_psi_dot(const pfb_psi_plan *plan, const void *x, void *alpha, void *stre
 int pfb_psi_hdot(const pfb_psi_plan *plan, const void *alpha, const void *alpha2,
                  void *xo, void *stream);
 
+/* Natural-orientation coefficient layout.  The reference stores every sub-band
+ * transposed w.r.t. the image (pfb/wavelets/wavelets.py:143-144, psi.py:200-218),
+ * which costs a transposition per Psi.dot and per Psi.hdot.  A solver that owns
+ * its dual variable for many iterations (primal_dual_optimised,
+ * pfb/opt/primal_dual.py:117-166) may keep it in this layout instead and convert
+ * on entry/exit: per (band, basis) one block of `stride` elements holding, for
+ * every level, the sub-bands as [jx][jy] arrays (rows padded to 32 elements,
+ * padding = 0), 'self' as the image itself.  Element-wise operators (dual
+ * update / prox with the weights converted the same way) are layout-agnostic.
+ * stride = 0: the plan's bases do not support it (db5, repeated bases). */
+int pfb_psi_nat_stride(const pfb_psi_plan *plan, long long *stride);
+/* slab cube (nband, nbasis, Nymax, Nxmax) -> natural layout (nband, nbasis, stride);
+ * nband is given explicitly so the (nbasis, Nymax, Nxmax) weights convert with 1 */
+int pfb_psi_to_nat(const pfb_psi_plan *plan, int nband, const void *alpha, void *nat,
+                   void *stream);
+/* natural layout -> pyramid cells of the slab cube (other cells untouched) */
+int pfb_psi_from_nat(const pfb_psi_plan *plan, int nband, const void *nat, void *alpha,
+                     void *stream);
+/* Psi.dot / Psi.hdot on the natural layout (same arithmetic, no transposition);
+ * nat2 != NULL: synthesis of 2*nat - nat2.  x must be 16-byte aligned. */
+int pfb_psi_dot_nat(const pfb_psi_plan *plan, const void *x, void *nat, void *stream);
+int pfb_psi_hdot_nat(const pfb_psi_plan *plan, const void *nat, const void *nat2,
+                     void *xo, void *stream);
+
 /* --------------------------------------------------------------- Hessian --
  * psf_convolve_cube / psf_convolve_slice  pfb/operators/psf.py:32-56, :11-29
  * hessian_psf_cube / _hessian_psf_slice   pfb/operators/hessian.py:254-281, :129-158

@@ -46,6 +46,11 @@ _SIGS = {
     "pfb_psi_plan_tables": (c_int, [_P, c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "pfb_psi_dot": (c_int, [_P, _P, _P, _P]),
     "pfb_psi_hdot": (c_int, [_P, _P, _P, _P, _P]),
+    "pfb_psi_nat_stride": (c_int, [_P, POINTER(c_longlong)]),
+    "pfb_psi_to_nat": (c_int, [_P, c_int, _P, _P, _P]),
+    "pfb_psi_from_nat": (c_int, [_P, c_int, _P, _P, _P]),
+    "pfb_psi_dot_nat": (c_int, [_P, _P, _P, _P]),
+    "pfb_psi_hdot_nat": (c_int, [_P, _P, _P, _P, _P]),
     "pfb_hess_plan_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_int, c_int, c_int]),
     "pfb_hess_plan_destroy": (c_int, [_P]),
     "pfb_hess_plan_set_psfhat": (c_int, [_P, _P, _P]),

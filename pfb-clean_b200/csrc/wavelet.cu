@@ -44,6 +44,8 @@ struct LevelDesc {
     int lowx, lowy;        // block origin in the slab (col, row)
     int ld_in;             // row stride of the natural-orientation scratch read
     int ld_out;            // row stride of the natural-orientation scratch written
+    int ldn, qs;           // natural-orientation coefficient layout (wavelet_syn_stream.cuh):
+    long off1;             //   row stride, elements per quadrant, offset of quadrant 1
 };
 
 struct LevelArgs {
@@ -53,6 +55,7 @@ struct LevelArgs {
     int Nxmax, Nymax;              // slab is (Nymax, Nxmax)
     long img_band_stride;          // nx*ny
     long scr_stride;               // elements per (band,basis) scratch image
+    long cn_stride;                // elements per (band,basis) block of the natural layout
     int first, last;               // level is the finest / the coarsest
     int nx, ny;
 };
@@ -450,6 +453,7 @@ static void fill_common(const pfb_psi_plan *p, LevelArgs &a, int level) {
     a.Nymax = p->Nymax;
     a.img_band_stride = (long)p->nx * p->ny;
     a.scr_stride = p->scr_stride;
+    a.cn_stride = p->cn_stride;
     a.first = level == 0;
     a.last = level == p->nlevel - 1;
     a.nx = p->nx;
@@ -474,8 +478,10 @@ static int ensure_scratch(const pfb_psi_plan *cp) {
     return PFB_OK;
 }
 
+// nat = false: alpha is the reference's slab cube; nat = true: alpha is the
+// natural-orientation layout (streaming kernels only).
 template <class T>
-static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t st) {
+static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, bool nat, cudaStream_t st) {
     if (int rc = ensure_scratch(p)) return rc;
     size_t smem = sizeof(T) * kAnaSmemElems;
     PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_level<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -484,6 +490,8 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t s
     bool stream = (p->ny % 2 == 0) && (((uintptr_t)x & 15) == 0) && !getenv("PFB_DWT_TILE");
     for (int b = 0; b < p->nbasis; ++b)
         if (p->bp[b].F > 8) stream = false;
+    if (nat && !(stream && p->syn_ok))
+        return fail(PFB_ERR_BAD_ARG, "natural-orientation layout needs distinct db1..db4 (+self) bases and a 16-byte aligned image");
     for (int l = 0; l < p->nlevel; ++l) {
         LevelArgs a;
         memset(&a, 0, sizeof a);
@@ -508,6 +516,9 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t s
             d.lowy = bp.highy[l] - 2 * bp.sy[l];
             d.ld_in = round4(d.n1);      // scratch rows padded to 16 bytes (fp32)
             d.ld_out = round4(d.C1);
+            d.ldn = p->cn_ld[b][l];
+            d.qs = d.C0 * d.ldn;
+            d.off1 = p->cn_off1[b][l];
             maxC0 = std::max(maxC0, d.C0);
             maxC1 = std::max(maxC1, d.C1);
             wC0 = std::max(wC0, d.C0);
@@ -519,7 +530,12 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t s
         if (stream) {
             if (l == 0) {
                 for (int b = 0; b < p->nbasis; ++b)
-                    if (p->bp[b].F == 0) {
+                    if (p->bp[b].F == 0 && nat) {
+                        long total = (long)p->nband * p->nx * (p->ny / 2);
+                        launch(&k_self_nat<T>, dim3((unsigned)std::min<long>(cdiv(total, 256), kNumSM * 16L)), dim3(256), 0, st,
+                               x, alpha, p->nx, p->ny, round32(p->ny), p->cn_stride, p->nbasis, b, total);
+                        PFB_CHECK_LAUNCH();
+                    } else if (p->bp[b].F == 0) {
                         dim3 grid(cdiv(p->ny, 64), cdiv(p->nx, 64), p->nband);
                         launch(&k_self_dot<T>, grid, dim3(256), sizeof(T) * 64 * 65, st, x, alpha, a, b);
                         PFB_CHECK_LAUNCH();
@@ -530,10 +546,17 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, cudaStream_t s
             int nstrip = cdiv(wC1, kStripOut), nchunk = cdiv(wC0, NJ);
             long ntask = (long)p->nband * nstrip * nchunk;      // per basis
             int dbg = getenv("PFB_DWT_DBG") ? atoi(getenv("PFB_DWT_DBG")) : 0;   // experiments only
-            size_t sm2 = sizeof(T) * (stream_smem_warp(a.last ? 4 : 3) + stream_ring_elems()) * kStreamWarps;
-            PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_stream<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-            launch(&k_dwt_stream<T>, dim3((unsigned)((long)p->nbasis * p->nband * nchunk * cdiv(nstrip, kStreamWarps))),
-                   dim3(32 * kStreamWarps), sm2, st, x, in, out, alpha, a, nstrip, nchunk, NJ, ntask, dbg);
+            dim3 sgrid((unsigned)((long)p->nbasis * p->nband * nchunk * cdiv(nstrip, kStreamWarps)));
+            if (nat) {
+                size_t sm2 = sizeof(T) * stream_ring_elems() * kStreamWarps;
+                launch(&k_dwt_stream<T, true>, sgrid, dim3(32 * kStreamWarps), sm2, st, x, in, out, alpha, a,
+                       nstrip, nchunk, NJ, ntask, dbg);
+            } else {
+                size_t sm2 = sizeof(T) * (stream_smem_warp(a.last ? 4 : 3) + stream_ring_elems()) * kStreamWarps;
+                PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_stream<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+                launch(&k_dwt_stream<T, false>, sgrid, dim3(32 * kStreamWarps), sm2, st, x, in, out, alpha, a,
+                       nstrip, nchunk, NJ, ntask, dbg);
+            }
             PFB_CHECK_LAUNCH();
             continue;
         }
@@ -557,16 +580,12 @@ static int ensure_cn(const pfb_psi_plan *cp) {
     return PFB_OK;
 }
 
-// Streaming synthesis: slab -> natural orientation (fusing 2*alpha - alpha2),
-// then one k_idwt_stream launch per level (wavelet_syn_stream.cuh).
+// slab <-> natural orientation for `nband` (band) cubes: 'self' on its own grid,
+// then one launch per level.  to_nat fuses 2*alpha - alpha2 when alpha2 != NULL.
 template <class T>
-static int psi_hdot_stream(const pfb_psi_plan *p, const T *alpha, const T *alpha2, T *xo,
-                           cudaStream_t st) {
-    if (int rc = ensure_cn(p)) return rc;
-    T *cn = (T *)p->cn;
-    T *A = (T *)p->scrA, *B = (T *)p->scrB;
+static int nat_transposes(const pfb_psi_plan *p, int nband, bool to_nat, const T *alpha,
+                          const T *alpha2, T *alpha_out, T *cn, cudaStream_t st) {
     const int L = p->nlevel;
-    // step 1: transposes.  'self' on its own grid, then one launch per level.
     for (int pass = -1; pass < L; ++pass) {
         NatArgs na;
         memset(&na, 0, sizeof na);
@@ -596,11 +615,21 @@ static int psi_hdot_stream(const pfb_psi_plan *p, const T *alpha, const T *alpha
             mr = std::max(mr, C1); mc = std::max(mc, C0);
         }
         if (na.nblk == 0) continue;
-        dim3 grid(cdiv(mc, 32), cdiv(mr, 32), p->nband * na.nblk);
-        launch(&k_slab_to_nat<T>, grid, dim3(256), 0, st, alpha, alpha2, cn, na);
+        dim3 grid(cdiv(mc, 32), cdiv(mr, 32), nband * na.nblk);
+        if (to_nat) launch(&k_slab_to_nat<T>, grid, dim3(256), 0, st, alpha, alpha2, cn, na);
+        else launch(&k_nat_to_slab<T>, grid, dim3(256), 0, st, (const T *)cn, alpha_out, na);
         PFB_CHECK_LAUNCH();
     }
-    // step 2: synthesis, coarsest level first
+    return PFB_OK;
+}
+
+// Streaming synthesis from the natural-orientation layout (optionally of
+// 2*cn - cn2): one k_idwt_stream launch per level (wavelet_syn_stream.cuh).
+template <class T>
+static int psi_hdot_nat_t(const pfb_psi_plan *p, const T *cn, const T *cn2, T *xo, cudaStream_t st) {
+    if (int rc = ensure_scratch(p)) return rc;
+    T *A = (T *)p->scrA, *B = (T *)p->scrB;
+    const int L = p->nlevel;
     for (int l = L - 1; l >= 0; --l) {
         SynArgs a;
         memset(&a, 0, sizeof a);
@@ -634,11 +663,31 @@ static int psi_hdot_stream(const pfb_psi_plan *p, const T *alpha, const T *alpha
         const long nblk = (long)(per_basis ? kSynSlots : 1) * p->nband * nchunk * cdiv(nstrip, kSynWarps);
         const T *in = ((L - 1 - l) % 2 == 1) ? A : B;
         T *out = l == 0 ? xo : (((L - 1 - l) % 2 == 0) ? A : B);
-        launch(&k_idwt_stream<T>, dim3((unsigned)nblk), dim3(32 * kSynWarps), 0, st,
-               (const T *)cn, in, out, a, nstrip, nchunk, NJ, per_basis);
+        const size_t sm1 = sizeof(T) * kSynWarps * kSynPD * syn_stage_elems(false);
+        const size_t sm2 = sizeof(T) * kSynWarps * kSynPD * syn_stage_elems(true);
+        if (cn2) {
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_idwt_stream<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+            launch(&k_idwt_stream<T, true>, dim3((unsigned)nblk), dim3(32 * kSynWarps), sm2, st,
+                   cn, cn2, in, out, a, nstrip, nchunk, NJ, per_basis);
+        } else {
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_idwt_stream<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+            launch(&k_idwt_stream<T, false>, dim3((unsigned)nblk), dim3(32 * kSynWarps), sm1, st,
+                   cn, cn, in, out, a, nstrip, nchunk, NJ, per_basis);
+        }
         PFB_CHECK_LAUNCH();
     }
     return PFB_OK;
+}
+
+// Reference-layout entry: slab -> plan scratch (fusing 2*alpha - alpha2), then
+// the streaming synthesis.
+template <class T>
+static int psi_hdot_stream(const pfb_psi_plan *p, const T *alpha, const T *alpha2, T *xo,
+                           cudaStream_t st) {
+    if (int rc = ensure_cn(p)) return rc;
+    T *cn = (T *)p->cn;
+    if (int rc = nat_transposes<T>(p, p->nband, true, alpha, alpha2, nullptr, cn, st)) return rc;
+    return psi_hdot_nat_t<T>(p, cn, (const T *)nullptr, xo, st);
 }
 
 template <class T>
@@ -802,8 +851,53 @@ int pfb_psi_plan_tables(const pfb_psi_plan *p, int basis, int *tabs, int *Ntotx,
 
 int pfb_psi_dot(const pfb_psi_plan *p, const void *x, void *alpha, void *stream) {
     if (!p || !x || !alpha) return fail(PFB_ERR_BAD_ARG, "pfb_psi_dot: null argument");
-    if (p->dtype == PFB_F32) return psi_dot_t<float>(p, (const float *)x, (float *)alpha, as_stream(stream));
-    return psi_dot_t<double>(p, (const double *)x, (double *)alpha, as_stream(stream));
+    if (p->dtype == PFB_F32) return psi_dot_t<float>(p, (const float *)x, (float *)alpha, false, as_stream(stream));
+    return psi_dot_t<double>(p, (const double *)x, (double *)alpha, false, as_stream(stream));
+}
+
+int pfb_psi_nat_stride(const pfb_psi_plan *p, long long *stride) {
+    if (!p || !stride) return fail(PFB_ERR_BAD_ARG, "pfb_psi_nat_stride: null argument");
+    *stride = p->syn_ok ? p->cn_stride : 0;
+    return PFB_OK;
+}
+
+static int nat_check(const pfb_psi_plan *p, const void *a, const void *b, int nband, const char *who) {
+    if (!p || !a || !b || nband < 1) return fail(PFB_ERR_BAD_ARG, "%s: bad argument", who);
+    if (!p->syn_ok) return fail(PFB_ERR_BAD_ARG, "%s: natural-orientation layout needs distinct db1..db4 (+self) bases", who);
+    return PFB_OK;
+}
+
+int pfb_psi_to_nat(const pfb_psi_plan *p, int nband, const void *alpha, void *nat, void *stream) {
+    if (int rc = nat_check(p, alpha, nat, nband, "pfb_psi_to_nat")) return rc;
+    cudaStream_t st = as_stream(stream);
+    size_t bytes = dtype_size(p->dtype) * (size_t)p->cn_stride * nband * p->nbasis;
+    PFB_CUDA_OK(cudaMemsetAsync(nat, 0, bytes, st));        // row / block padding stays zero
+    if (p->dtype == PFB_F32)
+        return nat_transposes<float>(p, nband, true, (const float *)alpha, nullptr, nullptr, (float *)nat, st);
+    return nat_transposes<double>(p, nband, true, (const double *)alpha, nullptr, nullptr, (double *)nat, st);
+}
+
+int pfb_psi_from_nat(const pfb_psi_plan *p, int nband, const void *nat, void *alpha, void *stream) {
+    if (int rc = nat_check(p, nat, alpha, nband, "pfb_psi_from_nat")) return rc;
+    cudaStream_t st = as_stream(stream);
+    if (p->dtype == PFB_F32)
+        return nat_transposes<float>(p, nband, false, nullptr, nullptr, (float *)alpha, (float *)nat, st);
+    return nat_transposes<double>(p, nband, false, nullptr, nullptr, (double *)alpha, (double *)nat, st);
+}
+
+int pfb_psi_dot_nat(const pfb_psi_plan *p, const void *x, void *nat, void *stream) {
+    if (int rc = nat_check(p, x, nat, 1, "pfb_psi_dot_nat")) return rc;
+    if (p->dtype == PFB_F32) return psi_dot_t<float>(p, (const float *)x, (float *)nat, true, as_stream(stream));
+    return psi_dot_t<double>(p, (const double *)x, (double *)nat, true, as_stream(stream));
+}
+
+int pfb_psi_hdot_nat(const pfb_psi_plan *p, const void *nat, const void *nat2, void *xo, void *stream) {
+    if (int rc = nat_check(p, nat, xo, 1, "pfb_psi_hdot_nat")) return rc;
+    if ((uintptr_t)xo % (2 * dtype_size(p->dtype)))
+        return fail(PFB_ERR_BAD_ARG, "pfb_psi_hdot_nat: output image must be aligned to two elements");
+    if (p->dtype == PFB_F32)
+        return psi_hdot_nat_t<float>(p, (const float *)nat, (const float *)nat2, (float *)xo, as_stream(stream));
+    return psi_hdot_nat_t<double>(p, (const double *)nat, (const double *)nat2, (double *)xo, as_stream(stream));
 }
 
 int pfb_psi_hdot(const pfb_psi_plan *p, const void *alpha, const void *alpha2, void *xo,

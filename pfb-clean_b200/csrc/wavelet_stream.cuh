@@ -55,6 +55,8 @@ __device__ __forceinline__ void cp_async_zfill(void *smem_dst, const void *gsrc,
     unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
     if (BYTES == 16)
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
+    else if (BYTES == 4)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
     else
         asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
 #endif
@@ -113,7 +115,11 @@ __device__ __forceinline__ void dwt_row_pass(const Vec2<T> &q, T (&m)[2]) {
 // unrolled version with a static register ring was bound by instruction fetch:
 // icc hit rate 65 %, `no_instruction` the top stall in profiles/r01d).  The F-2
 // previous row-pass results are shifted in registers.
-template <class T, int F>
+// NAT: the sub-bands go to the natural-orientation coefficient layout of the
+// streaming synthesis (rows = jx, 116-byte coalesced runs straight from
+// registers; `slab` then is the (band, basis) block of that layout) instead of
+// the reference's transposed slab.
+template <class T, int F, bool NAT>
 __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const int ld,
                                                 const LevelDesc &d, T *slab, const int ldslab,
                                                 T *ll_out, const bool last, const int strip,
@@ -178,6 +184,17 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
             hs[1][0] = m0[0]; hs[1][1] = m0[1];
             hs[0][0] = m1[0]; hs[0][1] = m1[1];
         }
+        if (NAT) {
+            if (jx >= JX0 && tval) {
+                T *dst = slab + d.off1 + (long)jx * d.ldn + ta;
+                if (last) dst[-(long)d.qs] = o[0];
+                else ll_out[(long)jx * d.ld_out + ta] = o[0];
+                dst[0] = o[1];
+                dst[d.qs] = o[2];
+                dst[2 * (long)d.qs] = o[3];
+            }
+            continue;
+        }
         // staging (warm-up rows hit cells that are overwritten before the flush)
         const int jxl = (jx - JX0) & (kJB - 1);
         if (lane >= 3) {
@@ -205,7 +222,7 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
 }
 
 // grid.x = nbasis * nband * nchunk * ceil(nstrip / kStreamWarps)
-template <class T>
+template <class T, bool NAT>
 __global__ void __launch_bounds__(32 * kStreamWarps)
 k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out, T *alpha,
              LevelArgs a, int nstrip, int nchunk, int NJ, long ntask, int dbg) {
@@ -229,16 +246,16 @@ k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out
     const LevelDesc &d = a.d[basis];
     if (d.F == 0 || kStripOut * strip >= d.C1 || chunk * NJ >= d.C0) return;
     const long slabsz = (long)a.Nymax * a.Nxmax;
-    T *slab = alpha + ((long)band * a.nbasis + basis) * slabsz;
+    T *slab = alpha + ((long)band * a.nbasis + basis) * (NAT ? a.cn_stride : slabsz);
     const long so = ((long)band * a.nbasis + basis) * a.scr_stride;
     const T *in = a.first ? img + band * a.img_band_stride : scr_in + so;
     const int ld = a.first ? a.ny : d.ld_in;
     T *ll = scr_out + so;
     switch (d.F) {
-    case 2: dwt_stream_task<T, 2>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
-    case 4: dwt_stream_task<T, 4>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
-    case 6: dwt_stream_task<T, 6>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
-    case 8: dwt_stream_task<T, 8>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    case 2: dwt_stream_task<T, 2, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    case 4: dwt_stream_task<T, 4, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    case 6: dwt_stream_task<T, 6, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    case 8: dwt_stream_task<T, 8, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
     default: break;   // F = 10 (db5) is routed to the tile kernel by the host
     }
 }
@@ -252,6 +269,23 @@ k_self_dot(const T *__restrict__ img, T *alpha, LevelArgs a, int basis) {
     const int band = blockIdx.z;
     T *slab = alpha + ((long)band * a.nbasis + basis) * (long)a.Nymax * a.Nxmax;
     self_tile<T>(img + band * a.img_band_stride, a.nx, a.ny, slab, a.Nxmax, blockIdx.y, blockIdx.x, smem);
+}
+
+
+// 'self' basis in the natural-orientation layout: its block is the image itself
+// (row stride ld_self).  One thread copies a pair of columns.
+template <class T>
+__global__ void __launch_bounds__(256)
+k_self_nat(const T *__restrict__ img, T *cn, int nx, int ny, int ld_self, long cn_stride,
+           int nbasis, int basis, long total) {
+    const int hy = ny / 2;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % hy);
+        const long r = i / hy;                 // band * nx + row
+        const long band = r / nx, row = r - band * nx;
+        stv2(cn + (band * nbasis + basis) * cn_stride + row * ld_self + 2 * c, ldv2(img + r * ny + 2 * c));
+    }
 }
 
 }  // namespace pfb

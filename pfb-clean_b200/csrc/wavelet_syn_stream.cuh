@@ -103,16 +103,46 @@ k_slab_to_nat(const T *__restrict__ alpha, const T *__restrict__ alpha2, T *__re
     }
 }
 
+// the way back (solver exit): natural orientation -> the pyramid cells of the slab
+template <class T>
+__global__ void __launch_bounds__(256)
+k_nat_to_slab(const T *__restrict__ cn, T *__restrict__ alpha, NatArgs a) {
+    __shared__ T tile[32][33];
+    const int band = blockIdx.z / a.nblk, blk = blockIdx.z - band * a.nblk;
+    const NatBlk &d = a.b[blk];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    if (c0 >= d.ncol || r0 >= d.nrow) return;
+    T *dst = alpha + ((long)band * a.nbasis + d.basis) * (long)a.Nymax * a.Nxmax;
+    const T *src = cn + ((long)band * a.nbasis + d.basis) * a.cn_stride + d.off;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = ty; i < 32; i += 8) {
+        const int c = c0 + i, r = r0 + tx;
+        tile[i][tx] = (c < d.ncol && r < d.nrow) ? src[(long)c * d.ldn + r] : (T)0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = ty; i < 32; i += 8) {
+        const int r = r0 + i, c = c0 + tx;
+        if (r < d.nrow && c < d.ncol) dst[(long)(d.row0 + r) * a.Nxmax + d.col0 + c] = tile[tx][i];
+    }
+}
+
 // ---------------------------------------------------------------------------
 // step 2: streaming synthesis.
 static const int kSynStrip = 29;      // output column PAIRS per warp (lanes 29..31: halo only)
 static const int kSynWarps = 4;       // warps (adjacent strips) per CTA
 static const int kSynHmax = 3;        // db4: F/2 - 1
 
-template <class T> struct SynRow {    // everything one walk step reads from memory
+template <class T> struct SynRow {    // everything one walk step consumes
     T c[kSynSlots][4];                // [slot][quadrant] at (ix = mx + H_slot, iy = MY0 + lane)
     Vec2<T> sf[2];                    // 'self' rows 2mx, 2mx+1 at columns 2my, 2my+1
 };
+// cp.async ring geometry (elements): one coefficient set of one walk step, and
+// a stage (one set, or two when the input is 2*cn - cn2)
+static const int kSynPD = 3;          // walk steps in flight per warp
+__host__ __device__ constexpr int syn_set_elems() { return kSynSlots * 4 * 32 + 2 * 64; }
+__host__ __device__ constexpr int syn_stage_elems(bool two) { return (two ? 2 : 1) * syn_set_elems(); }
 
 // One coefficient row of one filter bank: y synthesis across lanes, x synthesis
 // against the register history h[k-1] = U(row ix - k), accumulate into
@@ -162,10 +192,10 @@ __device__ __forceinline__ void syn_slot_step(const T (&c)[4], T (&h)[F > 2 ? F 
 // per_basis = 0 (finest level): a task sums every basis and writes the image;
 // per_basis = 1 (coarser levels): the task index also selects the slot and the
 // result is that basis' LL scratch for the next finer level.
-template <class T>
+template <class T, bool TWO>
 __global__ void __launch_bounds__(32 * kSynWarps)
-k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ scr_in, T *out, SynArgs a,
-              int nstrip, int nchunk, int NJ, int per_basis) {
+k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ cn2, const T *__restrict__ scr_in,
+              T *out, SynArgs a, int nstrip, int nchunk, int NJ, int per_basis) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     long idx = blockIdx.x;
     int sel = -1;
@@ -204,25 +234,77 @@ k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ scr_in, T *out, Sy
     if (has_self) pself = cn + ((long)band * a.nbasis + a.self_basis) * a.cn_stride + 2 * iy;
     const bool ocol = lane < kSynStrip && 2 * iy < n1;
 
-    auto load_row = [&](const int mx, SynRow<T> &r) {
+    // byte distance from a coefficient of cn to the same coefficient of cn2
+    const long d2 = TWO ? (long)((const char *)cn2 - (const char *)cn) : 0;
+    auto p2 = [&](const T *q) { return reinterpret_cast<const T *>(reinterpret_cast<const char *>(q) + d2); };
+
+    // cp.async ring: kSynPD walk steps of this warp's inputs in flight, no
+    // registers tied up, out-of-range rows / columns zero-filled by the copy.
+    // Stage layout per coefficient set: [slot][quadrant][lane], then self [row][lane][2].
+    PFB_DYN_SMEM(raw);
+    constexpr int SET = syn_set_elems();
+    T *ring = reinterpret_cast<T *>(raw) + warp * (kSynPD * syn_stage_elems(TWO));
+    auto prefetch = [&](const int mx) {
+        T *st = ring + ((mx - (MX0 - kSynHmax)) % kSynPD) * syn_stage_elems(TWO) + lane;
 #pragma unroll
         for (int s = 0; s < kSynSlots; ++s) {
+            if (!(mask >> s & 1)) continue;
             const SynSlot &d = a.s[s];
             const int ix = mx + s;                    // H of slot s is s
-            const bool ok = (mask >> s & 1) && ix >= MX0 && ix < d.C0 && iy < d.C1;
-            r.c[s][0] = r.c[s][1] = r.c[s][2] = r.c[s][3] = (T)0;
-            if (ok) {
-                const T *p = pq[s] + (long)ix * d.ldn;
-                r.c[s][0] = pl[s][(long)ix * ldl[s]];
-                r.c[s][1] = p[0];
-                r.c[s][2] = p[d.qs];
-                r.c[s][3] = p[2 * (long)d.qs];
+            const bool ok = ix >= MX0 && ix < d.C0 && iy < d.C1 && mx < mx_end;
+            const int nb = ok ? (int)sizeof(T) : 0;
+            const T *p = ok ? pq[s] + (long)ix * d.ldn : cn;
+            const T *l = ok ? pl[s] + (long)ix * ldl[s] : cn;
+            T *dq = st + s * 128;
+            cp_async_zfill<sizeof(T)>(dq, l, nb);
+            cp_async_zfill<sizeof(T)>(dq + 32, p, nb);
+            cp_async_zfill<sizeof(T)>(dq + 64, ok ? p + d.qs : cn, nb);
+            cp_async_zfill<sizeof(T)>(dq + 96, ok ? p + 2 * (long)d.qs : cn, nb);
+            if (TWO) {
+                if (a.last) cp_async_zfill<sizeof(T)>(dq + SET, ok ? p2(l) : cn, nb);
+                cp_async_zfill<sizeof(T)>(dq + SET + 32, ok ? p2(p) : cn, nb);
+                cp_async_zfill<sizeof(T)>(dq + SET + 64, ok ? p2(p + d.qs) : cn, nb);
+                cp_async_zfill<sizeof(T)>(dq + SET + 96, ok ? p2(p + 2 * (long)d.qs) : cn, nb);
             }
         }
-        r.sf[0].v[0] = r.sf[0].v[1] = r.sf[1].v[0] = r.sf[1].v[1] = (T)0;
-        if (has_self && ocol && mx >= MX0 && mx < mx_end) {
-            r.sf[0] = ldv2(pself + (long)(2 * mx) * a.ld_self);
-            r.sf[1] = ldv2(pself + (long)(2 * mx + 1) * a.ld_self);
+        if (has_self) {
+            const bool ok = ocol && mx >= MX0 && mx < mx_end;
+            const int nb = ok ? 2 * (int)sizeof(T) : 0;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const T *q = ok ? pself + (long)(2 * mx + k) * a.ld_self : cn;
+                T *dq = st + lane + kSynSlots * 128 + k * 64;      // (st already holds +lane)
+                cp_async_zfill<2 * sizeof(T)>(dq, q, nb);
+                if (TWO) cp_async_zfill<2 * sizeof(T)>(dq + SET, ok ? p2(q) : cn, nb);
+            }
+        }
+        cp_async_commit();
+    };
+    // On coarser levels LL comes from the scratch, which already holds the
+    // synthesis of the combined coefficients: only quadrants 1..3 are doubled.
+    auto consume = [&](const int mx, SynRow<T> &c) {
+        const T *st = ring + ((mx - (MX0 - kSynHmax)) % kSynPD) * syn_stage_elems(TWO) + lane;
+#pragma unroll
+        for (int s = 0; s < kSynSlots; ++s) {
+            if (!(mask >> s & 1)) continue;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                T v = st[s * 128 + q * 32];
+                if (TWO && (q > 0 || a.last)) v = (T)2 * v - st[SET + s * 128 + q * 32];
+                c.c[s][q] = v;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            c.sf[k].v[0] = c.sf[k].v[1] = (T)0;
+            if (has_self) {
+                c.sf[k] = ldv2(st + lane + kSynSlots * 128 + k * 64);
+                if (TWO) {
+                    const Vec2<T> o = ldv2(st + lane + kSynSlots * 128 + k * 64 + SET);
+                    c.sf[k].v[0] = (T)2 * c.sf[k].v[0] - o.v[0];
+                    c.sf[k].v[1] = (T)2 * c.sf[k].v[1] - o.v[1];
+                }
+            }
         }
     };
 
@@ -235,11 +317,16 @@ k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ scr_in, T *out, Sy
     }
     T *dst = out + (per_basis ? ((long)band * a.nbasis + a.s[sel].basis) * a.scr_stride
                               : band * a.img_band_stride) + 2 * iy;
-    SynRow<T> cur, nxt;
-    load_row(MX0 - kSynHmax, cur);
+    SynRow<T> cur;
+#pragma unroll
+    for (int s = 0; s < kSynSlots; ++s) cur.c[s][0] = cur.c[s][1] = cur.c[s][2] = cur.c[s][3] = (T)0;
+#pragma unroll 1
+    for (int j = 0; j < kSynPD; ++j) prefetch(MX0 - kSynHmax + j);
 #pragma unroll 1
     for (int mx = MX0 - kSynHmax; mx < mx_end; ++mx) {
-        load_row(mx + 1 < mx_end ? mx + 1 : mx, nxt);          // prefetch the next step
+        cp_async_wait<kSynPD - 1>();                           // the oldest group (this mx) has landed
+        consume(mx, cur);
+        prefetch(mx + kSynPD);                                 // refill the stage just read
         T acc[4] = {cur.sf[0].v[0], cur.sf[0].v[1], cur.sf[1].v[0], cur.sf[1].v[1]};
         T part[4] = {(T)0, (T)0, (T)0, (T)0};
         if (mask & 1u) syn_slot_step<T, 2>(cur.c[0], h0, part);
@@ -253,8 +340,8 @@ k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ scr_in, T *out, Sy
             stv2(dst + (long)(2 * mx) * ldo, r0);
             stv2(dst + (long)(2 * mx + 1) * ldo, r1);
         }
-        cur = nxt;
     }
+    cp_async_wait<0>();
 }
 
 }  // namespace pfb

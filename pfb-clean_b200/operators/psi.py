@@ -7,6 +7,7 @@ tiled DWT/IDWT kernels of csrc/wavelet.cu.  Coefficient layout, sizes
 import ctypes
 
 import numpy as np
+import torch
 
 from .. import _dev, _lib
 
@@ -95,6 +96,38 @@ class Psi(object):
         _lib.check(_lib.lib().pfb_psi_hdot(self._plan(_dev.dcode(ad)), _dev.ptr(ad), _dev.ptr(a2),
                                            _dev.ptr(od), _dev.stream()))
         _dev.to_out(od, xo)
+
+    # ---- natural-orientation layout (include/pfb_b200.h, pfb_psi_nat_stride) ----
+    # Device tensors only; used by primal_dual_optimised to keep its dual
+    # variable un-transposed between iterations.
+    def nat_stride(self, code=None):
+        """Elements per (band, basis) block, 0 when the bases do not support it."""
+        n = ctypes.c_longlong()
+        p = self._plan(code) if code is not None else next(iter(self._plans.values()))
+        _lib.check(_lib.lib().pfb_psi_nat_stride(p, ctypes.byref(n)))
+        return n.value
+
+    def to_nat(self, alpha):
+        """(nb, nbasis, Nymax, Nxmax) or (nbasis, Nymax, Nxmax) slab tensor -> natural layout."""
+        nb = alpha.shape[0] if alpha.dim() == 4 else 1
+        code = _dev.dcode(alpha)
+        out = torch.empty((nb, self.nbasis, self.nat_stride(code)), dtype=alpha.dtype, device=alpha.device)
+        _lib.check(_lib.lib().pfb_psi_to_nat(self._plan(code), nb, _dev.ptr(alpha), _dev.ptr(out), _dev.stream()))
+        return out if alpha.dim() == 4 else out[0]
+
+    def from_nat(self, nat, alpha):
+        nb = alpha.shape[0] if alpha.dim() == 4 else 1
+        _lib.check(_lib.lib().pfb_psi_from_nat(self._plan(_dev.dcode(alpha)), nb, _dev.ptr(nat),
+                                               _dev.ptr(alpha), _dev.stream()))
+        return alpha
+
+    def dot_nat(self, x, nat):
+        _lib.check(_lib.lib().pfb_psi_dot_nat(self._plan(_dev.dcode(x)), _dev.ptr(x), _dev.ptr(nat),
+                                              _dev.stream()))
+
+    def hdot_nat(self, nat, xo, nat2=None):
+        _lib.check(_lib.lib().pfb_psi_hdot_nat(self._plan(_dev.dcode(nat)), _dev.ptr(nat), _dev.ptr(nat2),
+                                               _dev.ptr(xo), _dev.stream()))
 
     def __del__(self):
         if self._destroy is not None:

@@ -20,6 +20,7 @@ split around an all-reduce of the band-sum slab and the eps terms are
 all-reduced.
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -134,7 +135,7 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     if xa.dtype != va.dtype:
         raise TypeError("x and v must have the same precision")
     xcur, xprev = xa, xa.clone()
-    vcur, vprev = va, va.clone()
+    vcur, vprev = va, None
     xout = torch.zeros_like(xa)
     n = va.numel() // va.shape[0]
     w = _prox._weight_dev(l1weight, va, tuple(va.shape[1:]))
@@ -154,6 +155,24 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         gi = _gap_index(psi.__self__, va.device)
         if gi.numel() and bool(torch.any(va.view(va.shape[0], -1)[:, gi] != 0)):
             gap_idx = gi
+    # Natural-orientation dual (include/pfb_b200.h): the solver owns v for the
+    # whole loop, so it is converted once here and once on exit, and neither
+    # Psi.dot nor Psi.hdot has to transpose.  The dual update is element-wise.
+    nat = (fast and gap_idx is None and psi.__self__.nat_stride(_dev.dcode(va)) > 0
+           and xa.data_ptr() % 16 == 0 and (xa[0].numel() * xa.element_size()) % 16 == 0
+           and not os.environ.get("PFB_PD_SLAB"))
+    # which loop ran, for the tests: "nat" | "slab" (fused loader) | "generic"
+    primal_dual_optimised.last_path = "nat" if nat else ("slab" if fast else "generic")
+    if nat:
+        P = psi.__self__
+        vcur = P.to_nat(va)
+        vprev = vcur.clone()
+        w = P.to_nat(w).contiguous()
+        n = vcur.numel() // vcur.shape[0]
+        if bsum is not None:
+            bsum = torch.empty(vcur.shape[1:], dtype=va.dtype, device=va.device)
+    else:
+        vprev = va.clone()
     fused_grad = isinstance(grad, Grad21)
     bound = grad.bound_psf() if fused_grad else None
     conv_buf = torch.empty_like(xa) if bound is not None else None
@@ -167,11 +186,16 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     k = -1
     broke = False
     for k in range(maxit):
-        psi(xprev, vcur)
-        if fast:   # `vp = 2v - vp` (primal_dual.py:137) is fused into the synthesis loader
+        if nat:
+            P.dot_nat(xprev, vcur)
+            _dual_step(vprev, vcur, lam, sigma, w, n, bsum, write_u=False)
+            P.hdot_nat(vcur, xout, vprev)
+        elif fast:   # `vp = 2v - vp` (primal_dual.py:137) is fused into the synthesis loader
+            psi(xprev, vcur)
             _dual_step(vprev, vcur, lam, sigma, w, n, bsum, write_u=False)
             psi.__self__.hdot(vcur, xout, alpha2=vprev)
         else:
+            psi(xprev, vcur)
             _dual_step(vprev, vcur, lam, sigma, w, n, bsum)      # vprev now holds 2v - vp
             psiH(vprev, xout)
         if bound is not None:
@@ -194,6 +218,8 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         if eps < tol:
             if reweighter is not None and numreweight < maxreweight:
                 w = _prox._weight_dev(reweighter(xcur), va, tuple(va.shape[1:]))
+                if nat:
+                    w = P.to_nat(w).contiguous()
                 numreweight += 1
             else:
                 if numreweight >= maxreweight and verbosity:
@@ -220,6 +246,8 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             print(f"Success, converged after {k} iterations")
     xfin = xcur if broke else xprev
     vfin = vcur if (broke or not fast) else vprev
+    if nat:
+        vfin = P.from_nat(vfin, va)
     return _dev.to_out(xfin, x), _dev.to_out(vfin, v)
 
 

@@ -104,3 +104,64 @@ def test_plan_errors():
     assert p.rc == 3       # nlevel too large (ValueError in the reference)
     with pytest.raises(ValueError):
         ref.Psi(1, 32, 32, ['self', 'db5'], 3)
+
+
+@pmp("dtype", [np.float32, np.float64])
+@pmp("nx,ny,nlevel", [(128, 78, 1), (250, 64, 2), (200, 136, 3)])
+@pmp("bases", [['self', 'db1', 'db2', 'db3', 'db4'], ['db3', 'db1']], ids=["stream5", "db31"])
+def test_psi_natural_layout(dtype, nx, ny, nlevel, bases):
+    """The natural-orientation layout (pfb_psi_nat_stride & co.) is a pure
+    re-arrangement: dot_nat == to_nat(dot), hdot_nat == hdot, from_nat inverts
+    to_nat on the pyramid cells and leaves every other slab cell alone."""
+    rng = np.random.default_rng(11)
+    nband = 2
+    L = emu()
+    psi = EmuPsi(nband, nx, ny, bases, nlevel, dtype)
+    stride = ctypes.c_longlong()
+    ok(L.pfb_psi_nat_stride(psi.plan, ctypes.byref(stride)))
+    assert stride.value > 0 and stride.value % 32 == 0
+    nb = len(bases)
+    x = rng.standard_normal((nband, nx, ny)).astype(dtype)
+    fill = rng.standard_normal((nband, nb, psi.Nymax, psi.Nxmax)).astype(dtype)
+    alpha = fill.copy()
+    psi.dot(x, alpha)
+    written = alpha != fill
+    # to_nat / from_nat
+    nat = np.full((nband, nb, stride.value), np.nan, dtype)
+    ok(L.pfb_psi_to_nat(psi.plan, nband, ptr(alpha), ptr(nat), None))
+    assert np.isfinite(nat).all()
+    assert np.count_nonzero(nat) == np.count_nonzero(alpha[written])
+    back = fill.copy()
+    ok(L.pfb_psi_from_nat(psi.plan, nband, ptr(nat), ptr(back), None))
+    assert np.array_equal(back, alpha)
+    # analysis straight into the layout (padding cells must stay as they are: zero)
+    nat2 = np.zeros_like(nat)
+    ok(L.pfb_psi_dot_nat(psi.plan, ptr(x), ptr(nat2), None))
+    assert np.array_equal(nat2, nat)
+    # synthesis from the layout, plain and with the fused 2a - a2
+    c1 = rng.standard_normal(fill.shape).astype(dtype)
+    c2 = rng.standard_normal(fill.shape).astype(dtype)
+    n1, n2 = np.empty_like(nat), np.empty_like(nat)
+    ok(L.pfb_psi_to_nat(psi.plan, nband, ptr(c1), ptr(n1), None))
+    ok(L.pfb_psi_to_nat(psi.plan, nband, ptr(c2), ptr(n2), None))
+    xa, xb = np.empty_like(x), np.empty_like(x)
+    psi.hdot(c1, xa)
+    ok(L.pfb_psi_hdot_nat(psi.plan, ptr(n1), None, ptr(xb), None))
+    assert np.array_equal(xa, xb)
+    psi.hdot(c1, xa, c2)
+    ok(L.pfb_psi_hdot_nat(psi.plan, ptr(n1), ptr(n2), ptr(xb), None))
+    assert np.array_equal(xa, xb)
+    # weights convert as a single "band"
+    wn = np.empty((nb, stride.value), dtype)
+    ok(L.pfb_psi_to_nat(psi.plan, 1, ptr(c1[1]), ptr(wn), None))
+    assert np.array_equal(wn, n1[1])
+
+
+def test_psi_natural_layout_unsupported():
+    L = emu()
+    psi = EmuPsi(1, 128, 128, ['db1', 'db5'], 2, np.float64)
+    stride = ctypes.c_longlong(-1)
+    ok(L.pfb_psi_nat_stride(psi.plan, ctypes.byref(stride)))
+    assert stride.value == 0
+    a = np.zeros((1, 2, psi.Nymax, psi.Nxmax))
+    assert L.pfb_psi_to_nat(psi.plan, 1, ptr(a), ptr(a), None) == 1   # PFB_ERR_BAD_ARG

@@ -3,6 +3,8 @@ against the emulated kernels and compared with the reference's golden vectors.
 Reads like the reference's own usage (spotless.py:175-281, fluxmop.py:166-199)."""
 from functools import partial
 
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -134,8 +136,22 @@ def test_solvers_api(backend, tag):
                                            w, None, grad, nu=nbasis, tol=0.0, maxit=10,
                                            positivity=pos, verbosity=0)
             assert xr is x and vr is v          # in place, like the reference
+            assert primal_dual_optimised.last_path == "nat"     # natural-orientation dual
             assert rel(x, g[f"pdo_x_pos{pos}"]) < tolx
             assert rel(v, g[f"pdo_v_pos{pos}"]) < tolx
+
+    # same solve with the dual kept in the reference's slab layout
+    os.environ["PFB_PD_SLAB"] = "1"
+    try:
+        x = np.zeros(dirty.shape, dt)
+        v = np.zeros((nband, nbasis, psi.Nymax, psi.Nxmax), dt)
+        primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, np.ones(v.shape[1:], dt), None,
+                              Grad21(psf_convolve, data), nu=nbasis, tol=0.0, maxit=10, positivity=1,
+                              verbosity=0)
+    finally:
+        del os.environ["PFB_PD_SLAB"]
+    assert primal_dual_optimised.last_path == "slab"
+    assert rel(x, g["pdo_x_pos1"]) < tolx and rel(v, g["pdo_v_pos1"]) < tolx
 
     # l1 reweighting branch
     outvar = np.zeros((nband, nbasis, psi.Nymax, psi.Nxmax), dt)
