@@ -893,8 +893,8 @@ int pfb_psi_dot_nat(const pfb_psi_plan *p, const void *x, void *nat, void *strea
 
 int pfb_psi_hdot_nat(const pfb_psi_plan *p, const void *nat, const void *nat2, void *xo, void *stream) {
     if (int rc = nat_check(p, nat, xo, 1, "pfb_psi_hdot_nat")) return rc;
-    if ((uintptr_t)xo % (2 * dtype_size(p->dtype)))
-        return fail(PFB_ERR_BAD_ARG, "pfb_psi_hdot_nat: output image must be aligned to two elements");
+    if ((uintptr_t)xo % (2 * dtype_size(p->dtype)) || (uintptr_t)nat % 16 || (uintptr_t)nat2 % 16)
+        return fail(PFB_ERR_BAD_ARG, "pfb_psi_hdot_nat: coefficients must be 16-byte aligned, the image to two elements");
     if (p->dtype == PFB_F32)
         return psi_hdot_nat_t<float>(p, (const float *)nat, (const float *)nat2, (float *)xo, as_stream(stream));
     return psi_hdot_nat_t<double>(p, (const double *)nat, (const double *)nat2, (double *)xo, as_stream(stream));

@@ -130,7 +130,8 @@ k_nat_to_slab(const T *__restrict__ cn, T *__restrict__ alpha, NatArgs a) {
 
 // ---------------------------------------------------------------------------
 // step 2: streaming synthesis.
-static const int kSynStrip = 29;      // output column PAIRS per warp (lanes 29..31: halo only)
+static const int kSynStrip = 28;      // output column PAIRS per warp (lanes 28..31: halo only);
+                                      // a multiple of 4 keeps every 16-byte load aligned
 static const int kSynWarps = 4;       // warps (adjacent strips) per CTA
 static const int kSynHmax = 3;        // db4: F/2 - 1
 
@@ -214,25 +215,56 @@ k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ cn2, const T *__re
     const int mx_end = (MX0 + NJ) * 2 < n0 ? MX0 + NJ : n0 / 2;
     const int iy = MY0 + lane;
 
+    // Loader geometry: every copy instruction moves 16 bytes per lane, i.e. a
+    // warp fetches RPI quadrant rows of 32 coefficients at once (fp32: all four
+    // quadrants of a slot in ONE LDGSTS).  Strips start at multiples of 28
+    // coefficients, rows are padded to 32 => every 16-byte piece is aligned.
+    constexpr int EPV = 16 / (int)sizeof(T);          // elements per vector
+    constexpr int SPR = 32 / EPV;                     // vectors per 32-coefficient row
+    constexpr int RPI = 32 / SPR;                     // rows per copy instruction
+    constexpr int NCI = 4 / RPI;                      // copy instructions per slot
+    const int seg = lane % SPR, rsub = lane / SPR;
+    const int vcol = MY0 + seg * EPV;                 // first coefficient column of this lane's vector
+
     unsigned mask = 0;
-    const T *pq[kSynSlots], *pl[kSynSlots];
-    int ldl[kSynSlots];
+    const T *pv[kSynSlots][NCI];                      // per-lane source of row 0
+    int ldv[kSynSlots][NCI], nbv[kSynSlots];
 #pragma unroll
     for (int s = 0; s < kSynSlots; ++s) {
         const SynSlot &d = a.s[s];
-        pq[s] = pl[s] = cn;
-        ldl[s] = 0;
+        nbv[s] = 0;
+#pragma unroll
+        for (int i = 0; i < NCI; ++i) { pv[s][i] = cn; ldv[s][i] = 0; }
         if (d.basis < 0 || (per_basis && s != sel)) continue;
         mask |= 1u << s;
         const long bb = (long)band * a.nbasis + d.basis;
-        pq[s] = cn + bb * a.cn_stride + d.off1 + iy;
-        if (a.last) { pl[s] = pq[s] - d.qs; ldl[s] = d.ldn; }
-        else { pl[s] = scr_in + bb * a.scr_stride + iy; ldl[s] = d.ld_ll; }
+        int left = (d.C1 - vcol) * (int)sizeof(T);
+        nbv[s] = left < 0 ? 0 : (left > 16 ? 16 : left);
+#pragma unroll
+        for (int i = 0; i < NCI; ++i) {
+            const int q = i * RPI + rsub;
+            if (q == 0 && !a.last) {                  // LL: what the coarser level wrote
+                pv[s][i] = scr_in + bb * a.scr_stride + vcol;
+                ldv[s][i] = d.ld_ll;
+            } else {
+                pv[s][i] = cn + bb * a.cn_stride + d.off1 + (long)(q - 1) * d.qs + vcol;
+                ldv[s][i] = d.ldn;
+            }
+        }
     }
     const bool has_self = !per_basis && a.self_basis >= 0;
-    const T *pself = cn;
-    if (has_self) pself = cn + ((long)band * a.nbasis + a.self_basis) * a.cn_stride + 2 * iy;
     const bool ocol = lane < kSynStrip && 2 * iy < n1;
+    // self rows: 2 * kSynStrip elements each, SSPR vectors reserved per row
+    constexpr int SSPR = 64 / EPV, SRPI = 32 / SSPR, SNCI = 2 / SRPI;
+    const int sseg = lane % SSPR, srow = lane / SSPR;
+    const int scol = 2 * MY0 + sseg * EPV;
+    const T *pself = cn;
+    int nbself = 0;
+    if (has_self) {
+        pself = cn + ((long)band * a.nbasis + a.self_basis) * a.cn_stride + scol;
+        int left = (n1 - scol) * (int)sizeof(T);
+        nbself = (sseg * EPV >= 2 * kSynStrip || left < 0) ? 0 : (left > 16 ? 16 : left);
+    }
 
     // byte distance from a coefficient of cn to the same coefficient of cn2
     const long d2 = TWO ? (long)((const char *)cn2 - (const char *)cn) : 0;
@@ -240,50 +272,45 @@ k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ cn2, const T *__re
 
     // cp.async ring: kSynPD walk steps of this warp's inputs in flight, no
     // registers tied up, out-of-range rows / columns zero-filled by the copy.
-    // Stage layout per coefficient set: [slot][quadrant][lane], then self [row][lane][2].
+    // Stage layout per coefficient set: [slot][quadrant][32], then self [row][64].
     PFB_DYN_SMEM(raw);
     constexpr int SET = syn_set_elems();
     T *ring = reinterpret_cast<T *>(raw) + warp * (kSynPD * syn_stage_elems(TWO));
     auto prefetch = [&](const int mx) {
-        T *st = ring + ((mx - (MX0 - kSynHmax)) % kSynPD) * syn_stage_elems(TWO) + lane;
+        T *st = ring + ((mx - (MX0 - kSynHmax)) % kSynPD) * syn_stage_elems(TWO);
 #pragma unroll
         for (int s = 0; s < kSynSlots; ++s) {
             if (!(mask >> s & 1)) continue;
             const SynSlot &d = a.s[s];
             const int ix = mx + s;                    // H of slot s is s
-            const bool ok = ix >= MX0 && ix < d.C0 && iy < d.C1 && mx < mx_end;
-            const int nb = ok ? (int)sizeof(T) : 0;
-            const T *p = ok ? pq[s] + (long)ix * d.ldn : cn;
-            const T *l = ok ? pl[s] + (long)ix * ldl[s] : cn;
-            T *dq = st + s * 128;
-            cp_async_zfill<sizeof(T)>(dq, l, nb);
-            cp_async_zfill<sizeof(T)>(dq + 32, p, nb);
-            cp_async_zfill<sizeof(T)>(dq + 64, ok ? p + d.qs : cn, nb);
-            cp_async_zfill<sizeof(T)>(dq + 96, ok ? p + 2 * (long)d.qs : cn, nb);
-            if (TWO) {
-                if (a.last) cp_async_zfill<sizeof(T)>(dq + SET, ok ? p2(l) : cn, nb);
-                cp_async_zfill<sizeof(T)>(dq + SET + 32, ok ? p2(p) : cn, nb);
-                cp_async_zfill<sizeof(T)>(dq + SET + 64, ok ? p2(p + d.qs) : cn, nb);
-                cp_async_zfill<sizeof(T)>(dq + SET + 96, ok ? p2(p + 2 * (long)d.qs) : cn, nb);
+            const bool ok = ix >= MX0 && ix < d.C0 && mx < mx_end;
+            const int nb = ok ? nbv[s] : 0;
+            const int ixc = ok ? ix : 0;              // keep the (unused) address inside the array
+#pragma unroll
+            for (int i = 0; i < NCI; ++i) {
+                const T *p = pv[s][i] + (long)ixc * ldv[s][i];
+                T *dq = st + s * 128 + i * (RPI * 32) + lane * EPV;
+                cp_async_zfill<16>(dq, p, nb);
+                // coarser-level LL already is the synthesis of the combined coefficients
+                if (TWO) cp_async_zfill<16>(dq + SET, p2(p), (i * RPI + rsub == 0 && !a.last) ? 0 : nb);
             }
         }
         if (has_self) {
-            const bool ok = ocol && mx >= MX0 && mx < mx_end;
-            const int nb = ok ? 2 * (int)sizeof(T) : 0;
+            const bool ok = mx >= MX0 && mx < mx_end;
 #pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                const T *q = ok ? pself + (long)(2 * mx + k) * a.ld_self : cn;
-                T *dq = st + lane + kSynSlots * 128 + k * 64;      // (st already holds +lane)
-                cp_async_zfill<2 * sizeof(T)>(dq, q, nb);
-                if (TWO) cp_async_zfill<2 * sizeof(T)>(dq + SET, ok ? p2(q) : cn, nb);
+            for (int i = 0; i < SNCI; ++i) {
+                const int k = i * SRPI + srow;
+                const T *q = pself + (long)(ok ? 2 * mx + k : 0) * a.ld_self;
+                T *dq = st + kSynSlots * 128 + k * 64 + sseg * EPV;
+                cp_async_zfill<16>(dq, q, ok ? nbself : 0);
+                if (TWO) cp_async_zfill<16>(dq + SET, p2(q), ok ? nbself : 0);
             }
         }
         cp_async_commit();
     };
-    // On coarser levels LL comes from the scratch, which already holds the
-    // synthesis of the combined coefficients: only quadrants 1..3 are doubled.
     auto consume = [&](const int mx, SynRow<T> &c) {
         const T *st = ring + ((mx - (MX0 - kSynHmax)) % kSynPD) * syn_stage_elems(TWO) + lane;
+        __syncwarp();                                  // vectors were fetched by other lanes
 #pragma unroll
         for (int s = 0; s < kSynSlots; ++s) {
             if (!(mask >> s & 1)) continue;
@@ -306,6 +333,7 @@ k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ cn2, const T *__re
                 }
             }
         }
+        __syncwarp();                                  // all lanes have read before the stage is refilled
     };
 
     T h0[1][4], h1[1][4], h2[2][4], h3[3][4];

@@ -187,9 +187,11 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     broke = False
     for k in range(maxit):
         if nat:
+            # the dual kernel leaves 2v - vp in the (dead) vp buffer: one coefficient
+            # set for the synthesis to read, which is instruction-issue bound
             P.dot_nat(xprev, vcur)
-            _dual_step(vprev, vcur, lam, sigma, w, n, bsum, write_u=False)
-            P.hdot_nat(vcur, xout, vprev)
+            _dual_step(vprev, vcur, lam, sigma, w, n, bsum)
+            P.hdot_nat(vprev, xout)
         elif fast:   # `vp = 2v - vp` (primal_dual.py:137) is fused into the synthesis loader
             psi(xprev, vcur)
             _dual_step(vprev, vcur, lam, sigma, w, n, bsum, write_u=False)
