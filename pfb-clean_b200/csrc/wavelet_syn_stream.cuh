@@ -161,23 +161,31 @@ __device__ __forceinline__ void syn_slot_step(const T (&c)[4], T (&h)[F > 2 ? F 
             const int d = H - j;                     // iy + H - j  <->  lane + d
             const T lo = d ? __shfl_down_sync(0xffffffffu, c[hx], d) : c[hx];
             const T hi = d ? __shfl_down_sync(0xffffffffu, c[2 + hx], d) : c[2 + hx];
-            e += tapc<T>(N, 2, 2 * j) * lo + tapc<T>(N, 3, 2 * j) * hi;
-            o += tapc<T>(N, 2, 2 * j + 1) * lo + tapc<T>(N, 3, 2 * j + 1) * hi;
+            // one FMA per tap (a*lo + b*hi added to e would cost FMUL + FFMA + FADD)
+            e = fma(tapc<T>(N, 2, 2 * j), lo, e);
+            e = fma(tapc<T>(N, 3, 2 * j), hi, e);
+            o = fma(tapc<T>(N, 2, 2 * j + 1), lo, o);
+            o = fma(tapc<T>(N, 3, 2 * j + 1), hi, o);
         }
         u[2 * hx] = e;
         u[2 * hx + 1] = o;
     }
 #pragma unroll
     for (int py = 0; py < 2; ++py) {
-        T e = tapc<T>(N, 2, 0) * u[py] + tapc<T>(N, 3, 0) * u[2 + py];
-        T o = tapc<T>(N, 2, 1) * u[py] + tapc<T>(N, 3, 1) * u[2 + py];
+        T e = acc[py], o = acc[2 + py];
+        e = fma(tapc<T>(N, 2, 0), u[py], e);
+        e = fma(tapc<T>(N, 3, 0), u[2 + py], e);
+        o = fma(tapc<T>(N, 2, 1), u[py], o);
+        o = fma(tapc<T>(N, 3, 1), u[2 + py], o);
 #pragma unroll
         for (int j = 1; j <= H; ++j) {
-            e += tapc<T>(N, 2, 2 * j) * h[j - 1][py] + tapc<T>(N, 3, 2 * j) * h[j - 1][2 + py];
-            o += tapc<T>(N, 2, 2 * j + 1) * h[j - 1][py] + tapc<T>(N, 3, 2 * j + 1) * h[j - 1][2 + py];
+            e = fma(tapc<T>(N, 2, 2 * j), h[j - 1][py], e);
+            e = fma(tapc<T>(N, 3, 2 * j), h[j - 1][2 + py], e);
+            o = fma(tapc<T>(N, 2, 2 * j + 1), h[j - 1][py], o);
+            o = fma(tapc<T>(N, 3, 2 * j + 1), h[j - 1][2 + py], o);
         }
-        acc[py] += e;
-        acc[2 + py] += o;
+        acc[py] = e;
+        acc[2 + py] = o;
     }
     if (H > 0) {
 #pragma unroll
@@ -189,18 +197,17 @@ __device__ __forceinline__ void syn_slot_step(const T (&c)[4], T (&h)[F > 2 ? F 
     }
 }
 
-// grid.x = [kSynSlots *] nband * nchunk * ceil(nstrip / kSynWarps).
-// per_basis = 0 (finest level): a task sums every basis and writes the image;
-// per_basis = 1 (coarser levels): the task index also selects the slot and the
-// result is that basis' LL scratch for the next finer level.
-template <class T, bool TWO>
-__global__ void __launch_bounds__(32 * kSynWarps)
-k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ cn2, const T *__restrict__ scr_in,
-              T *out, SynArgs a, int nstrip, int nchunk, int NJ, int per_basis) {
+// SLOT < 0: finest level, every slot takes part (absent ones see zeros);
+// SLOT >= 0: a coarser level of that one filter bank.  Compile-time on purpose:
+// the warp shuffles must not sit under a run-time condition (the compiler then
+// wraps each of them in a convergence-barrier sequence).
+template <class T, bool TWO, int SLOT>
+__device__ __forceinline__ void syn_walk(const T *__restrict__ cn, const T *__restrict__ cn2,
+                                         const T *__restrict__ scr_in, T *out, const SynArgs &a,
+                                         int nstrip, int nchunk, int NJ, long idx) {
+    constexpr bool per_basis = SLOT >= 0;
+    constexpr int sel = SLOT >= 0 ? SLOT : 0;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    long idx = blockIdx.x;
-    int sel = -1;
-    if (per_basis) { sel = (int)(idx % kSynSlots); idx /= kSynSlots; }
     const int nsg = (nstrip + kSynWarps - 1) / kSynWarps;
     const int sg = (int)(idx % nsg); idx /= nsg;
     const int chunk = (int)(idx % nchunk);
@@ -357,10 +364,10 @@ k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ cn2, const T *__re
         prefetch(mx + kSynPD);                                 // refill the stage just read
         T acc[4] = {cur.sf[0].v[0], cur.sf[0].v[1], cur.sf[1].v[0], cur.sf[1].v[1]};
         T part[4] = {(T)0, (T)0, (T)0, (T)0};
-        if (mask & 1u) syn_slot_step<T, 2>(cur.c[0], h0, part);
-        if (mask & 2u) syn_slot_step<T, 4>(cur.c[1], h1, part);
-        if (mask & 4u) syn_slot_step<T, 6>(cur.c[2], h2, part);
-        if (mask & 8u) syn_slot_step<T, 8>(cur.c[3], h3, part);
+        if (SLOT < 0 || SLOT == 0) syn_slot_step<T, 2>(cur.c[0], h0, part);
+        if (SLOT < 0 || SLOT == 1) syn_slot_step<T, 4>(cur.c[1], h1, part);
+        if (SLOT < 0 || SLOT == 2) syn_slot_step<T, 6>(cur.c[2], h2, part);
+        if (SLOT < 0 || SLOT == 3) syn_slot_step<T, 8>(cur.c[3], h3, part);
         if (mx >= MX0 && ocol) {
             Vec2<T> r0, r1;
             r0.v[0] = part[0] + acc[0]; r0.v[1] = part[1] + acc[1];
@@ -370,6 +377,26 @@ k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ cn2, const T *__re
         }
     }
     cp_async_wait<0>();
+}
+
+// grid.x = [kSynSlots *] nband * nchunk * ceil(nstrip / kSynWarps).
+// per_basis = 0 (finest level): a task sums every basis and writes the image;
+// per_basis = 1 (coarser levels): the task index also selects the slot and the
+// result is that basis' LL scratch for the next finer level.
+template <class T, bool TWO>
+__global__ void __launch_bounds__(32 * kSynWarps)
+k_idwt_stream(const T *__restrict__ cn, const T *__restrict__ cn2, const T *__restrict__ scr_in,
+              T *out, SynArgs a, int nstrip, int nchunk, int NJ, int per_basis) {
+    long idx = blockIdx.x;
+    if (!per_basis) { syn_walk<T, TWO, -1>(cn, cn2, scr_in, out, a, nstrip, nchunk, NJ, idx); return; }
+    const int sel = (int)(idx % kSynSlots);
+    idx /= kSynSlots;
+    switch (sel) {
+    case 0: syn_walk<T, TWO, 0>(cn, cn2, scr_in, out, a, nstrip, nchunk, NJ, idx); break;
+    case 1: syn_walk<T, TWO, 1>(cn, cn2, scr_in, out, a, nstrip, nchunk, NJ, idx); break;
+    case 2: syn_walk<T, TWO, 2>(cn, cn2, scr_in, out, a, nstrip, nchunk, NJ, idx); break;
+    default: syn_walk<T, TWO, 3>(cn, cn2, scr_in, out, a, nstrip, nchunk, NJ, idx); break;
+    }
 }
 
 }  // namespace pfb
