@@ -528,14 +528,34 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, bool nat, cuda
         const T *in = (l % 2 == 1) ? A : B;   // level l reads what level l-1 wrote
         T *out = (l % 2 == 0) ? A : B;
         if (stream) {
+            if (l == 0 && nat) {
+                // finest level: every bank (and 'self') in one walk over the image
+                DwtAllArgs g;
+                memset(&g, 0, sizeof g);
+                for (int s = 0; s < 4; ++s) g.s[s].basis = -1;
+                g.self_basis = -1;
+                g.ld_self = round32(p->ny);
+                for (int b = 0; b < p->nbasis; ++b) {
+                    if (p->bp[b].F == 0) { g.self_basis = b; continue; }
+                    DwtAllSlot &d = g.s[p->bp[b].F / 2 - 1];
+                    d.basis = b;
+                    d.C0 = a.d[b].C0; d.C1 = a.d[b].C1;
+                    d.ldn = a.d[b].ldn; d.qs = a.d[b].qs; d.ld_out = a.d[b].ld_out;
+                    d.off1 = a.d[b].off1;
+                }
+                int NJ = wC0 >= 1024 ? 128 : (wC0 >= 256 ? 64 : 32);
+                int SW = getenv("PFB_DWT_SW") ? atoi(getenv("PFB_DWT_SW")) : kStripNat;   // experiments only
+                int dbg = getenv("PFB_DWT_DBG") ? atoi(getenv("PFB_DWT_DBG")) : 0;
+                int nstrip = cdiv(wC1, SW), nchunk = cdiv(wC0, NJ);
+                size_t sm2 = sizeof(T) * stream_ring_elems() * kStreamWarps;
+                launch(&k_dwt_stream_all<T>, dim3((unsigned)((long)p->nband * nchunk * cdiv(nstrip, kStreamWarps))),
+                       dim3(32 * kStreamWarps), sm2, st, x, out, alpha, a, g, nstrip, nchunk, NJ, SW, dbg);
+                PFB_CHECK_LAUNCH();
+                continue;
+            }
             if (l == 0) {
                 for (int b = 0; b < p->nbasis; ++b)
-                    if (p->bp[b].F == 0 && nat) {
-                        long total = (long)p->nband * p->nx * (p->ny / 2);
-                        launch(&k_self_nat<T>, dim3((unsigned)std::min<long>(cdiv(total, 256), kNumSM * 16L)), dim3(256), 0, st,
-                               x, alpha, p->nx, p->ny, round32(p->ny), p->cn_stride, p->nbasis, b, total);
-                        PFB_CHECK_LAUNCH();
-                    } else if (p->bp[b].F == 0) {
+                    if (p->bp[b].F == 0) {
                         dim3 grid(cdiv(p->ny, 64), cdiv(p->nx, 64), p->nband);
                         launch(&k_self_dot<T>, grid, dim3(256), sizeof(T) * 64 * 65, st, x, alpha, a, b);
                         PFB_CHECK_LAUNCH();
@@ -543,19 +563,20 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, bool nat, cuda
             }
             if (wC0 == 0) continue;
             int NJ = wC0 >= 1024 ? 128 : (wC0 >= 256 ? 64 : 32);
-            int nstrip = cdiv(wC1, kStripOut), nchunk = cdiv(wC0, NJ);
+            const int SW = nat ? kStripNat : kStripOut;
+            int nstrip = cdiv(wC1, SW), nchunk = cdiv(wC0, NJ);
             long ntask = (long)p->nband * nstrip * nchunk;      // per basis
             int dbg = getenv("PFB_DWT_DBG") ? atoi(getenv("PFB_DWT_DBG")) : 0;   // experiments only
             dim3 sgrid((unsigned)((long)p->nbasis * p->nband * nchunk * cdiv(nstrip, kStreamWarps)));
             if (nat) {
                 size_t sm2 = sizeof(T) * stream_ring_elems() * kStreamWarps;
                 launch(&k_dwt_stream<T, true>, sgrid, dim3(32 * kStreamWarps), sm2, st, x, in, out, alpha, a,
-                       nstrip, nchunk, NJ, ntask, dbg);
+                       nstrip, nchunk, NJ, ntask, dbg, SW);
             } else {
                 size_t sm2 = sizeof(T) * (stream_smem_warp(a.last ? 4 : 3) + stream_ring_elems()) * kStreamWarps;
                 PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_stream<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
                 launch(&k_dwt_stream<T, false>, sgrid, dim3(32 * kStreamWarps), sm2, st, x, in, out, alpha, a,
-                       nstrip, nchunk, NJ, ntask, dbg);
+                       nstrip, nchunk, NJ, ntask, dbg, SW);
             }
             PFB_CHECK_LAUNCH();
             continue;

@@ -33,7 +33,13 @@ namespace pfb {
 // B200: 8-wide runs cost 2.7 ms per Psi.dot at 8x4096^2, 16-wide 1.4 ms,
 // 32-wide 0.9 ms -- profiles/dbg_dwt.sh), and with one column per lane its
 // shared-memory staging (3 x 32 x 29 values) is small enough for 16 warps/SM.
-static const int kStripOut = 29;     // coefficient columns per warp strip
+static const int kStripOut = 29;     // coefficient columns per warp strip (slab output)
+// Natural-orientation output stores one row segment per warp and sub-band straight
+// from registers: 24 columns = 96 bytes (fp32) keep every segment aligned to the
+// 32-byte DRAM sector.  Measured at 8x4096^2 (profiles/dbg_dwt.sh): 29-wide
+// (unaligned) segments 1.68 ms per Psi.dot, 28-wide 1.36 ms, 24-wide 1.16 ms, no
+// stores at all 0.73 ms -- partial-sector writes, not bytes, were the cost.
+static const int kStripNat = 24;
 static const int kJB = 32;           // jx per transposed write-out block
 static const int kPitch = 31;        // staging pitch (odd: conflict-free transposed reads)
 static const int kStreamWarps = 4;   // warps (independent tasks) per CTA
@@ -124,14 +130,14 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
                                                 const LevelDesc &d, T *slab, const int ldslab,
                                                 T *ll_out, const bool last, const int strip,
                                                 const int chunk, const int NJ, T *s_out,
-                                                T *ring, const int dbg) {
+                                                T *ring, const int dbg, const int SW) {
     const int lane = threadIdx.x & 31;
-    const int T0 = kStripOut * strip;
+    const int T0 = SW * strip;
     const int c = 2 * T0 - 6 + 2 * lane;             // first column of this lane's pair
     const bool cvalid = c >= 0 && c < ld;            // ld, c even
     const int tl = lane - 3;                         // local output column (lanes 0..2: halo only)
     const int ta = T0 + tl;
-    const bool tval = lane >= 3 && ta < d.C1;
+    const bool tval = lane >= 3 && lane < 3 + SW && ta < d.C1;
     const int JX0 = chunk * NJ;
     const int jx_end = JX0 + NJ < d.C0 ? JX0 + NJ : d.C0;
     const int s0 = last ? 0 : 1;                     // first staged sub-band
@@ -140,7 +146,7 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
 #pragma unroll
     for (int i = 0; i < NH; ++i) hs[i][0] = hs[i][1] = (T)0;
     int tmax0 = d.C1 - T0;
-    tmax0 = tmax0 < kStripOut ? tmax0 : kStripOut;
+    tmax0 = tmax0 < SW ? tmax0 : SW;
     // bytes of this lane's pair that lie inside the image row (0 => zero fill)
     const int cbytes = (!cvalid || (dbg & 4)) ? 0 : (c + 1 < d.n1 ? 2 : (c < d.n1 ? 1 : 0)) * (int)sizeof(T);
     T *myring = ring + 2 * lane;                     // slot layout [iter % kPD][row 0/1][lane][2]
@@ -225,7 +231,7 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
 template <class T, bool NAT>
 __global__ void __launch_bounds__(32 * kStreamWarps)
 k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out, T *alpha,
-             LevelArgs a, int nstrip, int nchunk, int NJ, long ntask, int dbg) {
+             LevelArgs a, int nstrip, int nchunk, int NJ, long ntask, int dbg, int SW) {
     PFB_DYN_SMEM(raw);
     const int warp = threadIdx.x >> 5;
     T *ring = reinterpret_cast<T *>(raw) + warp * stream_ring_elems();       // 16-byte aligned
@@ -244,7 +250,7 @@ k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out
     const int strip = sg * kStreamWarps + warp;
     if (band >= a.nband) return;
     const LevelDesc &d = a.d[basis];
-    if (d.F == 0 || kStripOut * strip >= d.C1 || chunk * NJ >= d.C0) return;
+    if (d.F == 0 || SW * strip >= d.C1 || chunk * NJ >= d.C0) return;
     const long slabsz = (long)a.Nymax * a.Nxmax;
     T *slab = alpha + ((long)band * a.nbasis + basis) * (NAT ? a.cn_stride : slabsz);
     const long so = ((long)band * a.nbasis + basis) * a.scr_stride;
@@ -252,12 +258,177 @@ k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out
     const int ld = a.first ? a.ny : d.ld_in;
     T *ll = scr_out + so;
     switch (d.F) {
-    case 2: dwt_stream_task<T, 2, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
-    case 4: dwt_stream_task<T, 4, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
-    case 6: dwt_stream_task<T, 6, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
-    case 8: dwt_stream_task<T, 8, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg); break;
+    case 2: dwt_stream_task<T, 2, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW); break;
+    case 4: dwt_stream_task<T, 4, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW); break;
+    case 6: dwt_stream_task<T, 6, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW); break;
+    case 8: dwt_stream_task<T, 8, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW); break;
     default: break;   // F = 10 (db5) is routed to the tile kernel by the host
     }
+}
+
+// ---------------------------------------------------------------------------
+// Finest level, natural-orientation output, ALL filter banks in one walk: the
+// four Daubechies banks (slot s <-> db(s+1)) read the same image rows, so one
+// warp loads each row pair once, shares the 12 halo shuffles, and runs the four
+// row/column passes back to back (sum F = 20 taps); 'self' (the image itself in
+// that layout) is stored from the same registers.  Per coefficient row this is
+// ~270 instructions instead of 4 x ~130 for four single-bank walks, which matters
+// because these walks are instruction-issue bound, not HBM bound.
+struct DwtAllSlot {        // indexed with compile-time slot numbers only: every field
+    int basis;             // is then a constant-bank operand (a run-time index would
+    int C0, C1;            // turn each use into an LDC with a long-scoreboard wait)
+    int ldn, qs, ld_out;
+    long off1;
+};
+struct DwtAllArgs {
+    DwtAllSlot s[4];       // db1..db4, basis = -1: absent
+    int self_basis;        // -1 = absent
+    int ld_self;
+};
+
+template <class T, int F>
+__device__ __forceinline__ void dwt_all_bank(const T (&w0)[8], const T (&w1)[8],
+                                             T (&hs)[F > 2 ? F - 2 : 1][2], T (&o)[4]) {
+    constexpr int N = F / 2 - 1;
+    T m0[2] = {(T)0, (T)0}, m1[2] = {(T)0, (T)0};
+#pragma unroll
+    for (int k = 0; k < F; ++k) {
+        const T lo = tapc<T>(N, 0, k), hi = tapc<T>(N, 1, k);
+        m0[0] = fma(lo, w0[7 - k], m0[0]);
+        m0[1] = fma(hi, w0[7 - k], m0[1]);
+        m1[0] = fma(lo, w1[7 - k], m1[0]);
+        m1[1] = fma(hi, w1[7 - k], m1[1]);
+    }
+    o[0] = o[1] = o[2] = o[3] = (T)0;
+#pragma unroll
+    for (int k = 0; k < F; ++k) {
+        const T lo = tapc<T>(N, 0, k), hi = tapc<T>(N, 1, k);
+        const T *mm = k == 0 ? m1 : (k == 1 ? m0 : hs[k >= 2 ? k - 2 : 0]);
+        o[0] = fma(lo, mm[0], o[0]);
+        o[1] = fma(hi, mm[0], o[1]);
+        o[2] = fma(lo, mm[1], o[2]);
+        o[3] = fma(hi, mm[1], o[3]);
+    }
+    if (F > 2) {
+#pragma unroll
+        for (int i = F - 3; i >= 2; --i) { hs[i][0] = hs[i - 2][0]; hs[i][1] = hs[i - 2][1]; }
+        hs[1][0] = m0[0]; hs[1][1] = m0[1];
+        hs[0][0] = m1[0]; hs[0][1] = m1[1];
+    }
+}
+
+// grid.x = nband * nchunk * ceil(nstrip / kStreamWarps); smem = ring only
+template <class T>
+__global__ void __launch_bounds__(32 * kStreamWarps)
+k_dwt_stream_all(const T *__restrict__ img, T *scr_out, T *cn, LevelArgs a, DwtAllArgs g,
+                 int nstrip, int nchunk, int NJ, int SW, int dbg) {
+    PFB_DYN_SMEM(raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    T *ring = reinterpret_cast<T *>(raw) + warp * stream_ring_elems();
+    long cta = blockIdx.x;
+    const int nsg = (nstrip + kStreamWarps - 1) / kStreamWarps;
+    const int sg = (int)(cta % nsg); cta /= nsg;
+    const int chunk = (int)(cta % nchunk);
+    const int band = (int)(cta / nchunk);
+    const int strip = sg * kStreamWarps + warp;
+    if (band >= a.nband) return;
+    const int T0 = SW * strip, JX0 = chunk * NJ;
+    const int n0 = a.nx, n1 = a.ny, ld = a.ny;
+    // extents over all banks (db4 has the largest coefficient arrays)
+    int C0max = 0, C1max = 0;
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+        if (g.s[s].basis >= 0) {
+            C0max = g.s[s].C0 > C0max ? g.s[s].C0 : C0max;
+            C1max = g.s[s].C1 > C1max ? g.s[s].C1 : C1max;
+        }
+    if (T0 >= C1max || JX0 >= C0max) return;
+    const int jx_end = JX0 + NJ < C0max ? JX0 + NJ : C0max;
+    const T *in = img + band * a.img_band_stride;
+    const int c = 2 * T0 - 6 + 2 * lane;             // first column of this lane's pair
+    const bool cvalid = c >= 0 && c < ld;
+    const int ta = T0 + lane - 3;                    // coefficient column (lanes 0..2: halo only)
+    const int cbytes = !cvalid ? 0 : (c + 1 < n1 ? 2 : (c < n1 ? 1 : 0)) * (int)sizeof(T);
+
+    // per-bank output row pointers (quadrant 1 of row jx, column ta) and LL scratch rows
+    T *pq[4], *pll[4];
+    bool tv[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const DwtAllSlot &d = g.s[s];
+        const long bb = (long)band * a.nbasis + (d.basis >= 0 ? d.basis : 0);
+        pq[s] = cn + bb * a.cn_stride + d.off1 + ta;
+        pll[s] = a.last ? pq[s] - d.qs : scr_out + bb * a.scr_stride + ta;
+        tv[s] = d.basis >= 0 && lane >= 3 && lane < 3 + SW && ta < d.C1 && !(dbg & 1);
+    }
+    T *pself = cn;
+    const bool sv = g.self_basis >= 0 && lane >= 3 && lane < 3 + SW && c < n1 && !(dbg & 2);
+    if (g.self_basis >= 0) pself = cn + ((long)band * a.nbasis + g.self_basis) * a.cn_stride + c;
+
+    T *myring = ring + 2 * lane;                     // slot layout [iter % kPD][row 0/1][lane][2]
+    auto prefetch = [&](const int j) {               // rows 2j, 2j+1 -> ring slot j mod kPD
+        T *dst = myring + (j & (kPD - 1)) * 128;
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+            const int r = 2 * j + rr;
+            const bool ok = (unsigned)r < (unsigned)n0 && j < jx_end;
+            cp_async_zfill<2 * sizeof(T)>(dst + rr * 64, ok ? in + (long)r * ld + c : in, ok ? cbytes : 0);
+        }
+        cp_async_commit();
+    };
+    T h1[2][2], h2[4][2], h3[6][2], h0[1][2];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        h3[i][0] = h3[i][1] = (T)0;
+        if (i < 4) h2[i][0] = h2[i][1] = (T)0;
+        if (i < 2) h1[i][0] = h1[i][1] = (T)0;
+    }
+    h0[0][0] = h0[0][1] = (T)0;
+    const int jx_first = JX0 - 3;                    // db4 needs three coefficient rows of history
+#pragma unroll 1
+    for (int j = jx_first; j < jx_first + kPD; ++j) prefetch(j);
+
+#pragma unroll 1
+    for (int jx = jx_first; jx < jx_end; ++jx) {
+        cp_async_wait<kPD - 1>();
+        const T *slot = myring + (jx & (kPD - 1)) * 128;
+        const Vec2<T> q0 = ldv2(slot), q1 = ldv2(slot + 64);
+        prefetch(jx + kPD);
+        // the 8-wide window of both rows: 6 halo values from lanes l-1..l-3
+        T w0[8], w1[8];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            w0[2 * j] = __shfl_up_sync(0xffffffffu, q0.v[0], 3 - j);
+            w0[2 * j + 1] = __shfl_up_sync(0xffffffffu, q0.v[1], 3 - j);
+            w1[2 * j] = __shfl_up_sync(0xffffffffu, q1.v[0], 3 - j);
+            w1[2 * j + 1] = __shfl_up_sync(0xffffffffu, q1.v[1], 3 - j);
+        }
+        w0[6] = q0.v[0]; w0[7] = q0.v[1];
+        w1[6] = q1.v[0]; w1[7] = q1.v[1];
+        T o[4][4];
+        dwt_all_bank<T, 2>(w0, w1, h0, o[0]);
+        dwt_all_bank<T, 4>(w0, w1, h1, o[1]);
+        dwt_all_bank<T, 6>(w0, w1, h2, o[2]);
+        dwt_all_bank<T, 8>(w0, w1, h3, o[3]);
+        if (jx < JX0) continue;                      // warm-up rows of the history
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            const DwtAllSlot &d = g.s[s];
+            if (tv[s] && jx < d.C0) {
+                T *dst = pq[s] + (long)jx * d.ldn;
+                if (a.last) dst[-(long)d.qs] = o[s][0];
+                else pll[s][(long)jx * d.ld_out] = o[s][0];
+                dst[0] = o[s][1];
+                dst[d.qs] = o[s][2];
+                dst[2 * (long)d.qs] = o[s][3];
+            }
+        }
+        if (sv) {
+            if (2 * jx < n0) stv2(pself + (long)(2 * jx) * g.ld_self, q0);
+            if (2 * jx + 1 < n0) stv2(pself + (long)(2 * jx + 1) * g.ld_self, q1);
+        }
+    }
+    cp_async_wait<0>();
 }
 
 // 'self' basis alone: alphao[i, 0:ny, 0:nx] = x.T (pfb/operators/psi.py:196-199)

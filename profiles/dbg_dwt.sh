@@ -1,4 +1,9 @@
-# experiment: stream-DWT with flush on/off (PFB_DWT_DBG bit 0 = skip slab stores)
-for d in 0 1; do echo "dbg=$d"; PFB_DWT_DBG=$d python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline 2>/dev/null | python -c "
-import json,sys;d=json.load(sys.stdin);print(d['ms_per_step'],[ (k[:24],v['ms_per_step']) for k,v in d['kernels'].items() if 'dwt' in k or 'self' in k])"; done
-python -m pytest tests -m gpu -q -k "psi or minor" 2>&1 | tail -2
+#!/bin/bash
+# experiments on the finest-level analysis walk (k_dwt_stream_all): strip width and store suppression
+for cfg in "29 0" "24 0" "28 0" "16 0" "29 1" "29 2" "29 3" "24 1"; do
+  set -- $cfg
+  echo "== SW=$1 DBG=$2"
+  PFB_DWT_SW=$1 PFB_DWT_DBG=$2 python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['kernels'].get('k_dwt_stream'))"
+done

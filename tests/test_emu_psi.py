@@ -137,7 +137,8 @@ def test_psi_natural_layout(dtype, nx, ny, nlevel, bases):
     # analysis straight into the layout (padding cells must stay as they are: zero)
     nat2 = np.zeros_like(nat)
     ok(L.pfb_psi_dot_nat(psi.plan, ptr(x), ptr(nat2), None))
-    assert np.array_equal(nat2, nat)
+    assert rel(nat2, nat) < (1e-13 if dtype == np.float64 else 1e-6)
+    assert np.array_equal(nat2 == 0, nat == 0)
     # synthesis from the layout, plain and with the fused 2a - a2
     c1 = rng.standard_normal(fill.shape).astype(dtype)
     c2 = rng.standard_normal(fill.shape).astype(dtype)
