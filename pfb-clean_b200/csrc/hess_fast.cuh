@@ -72,20 +72,27 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
             Cx<T> *buf = bufs + l * ct_stride(M);
             Cx<T> v[16];
             const long ro = ((long)band * h.nx + row) * h.ny;
+            // all loads of the row first (one wait for the lot), then the beam
+            T2 a[16];
 #pragma unroll
             for (int e = 0; e < 16; ++e) {
                 const int c0 = 2 * (t + e * NT);
-                T2 a;
-                a.x = (T)0; a.y = (T)0;
-                if (row < h.nx && c0 < h.ny) {
-                    a = *reinterpret_cast<const T2 *>(x + ro + c0);
-                    if (beam) {
-                        T2 bm = *reinterpret_cast<const T2 *>(beam + ro + c0);
-                        a.x *= bm.x; a.y *= bm.y;
-                    }
-                }
-                v[e] = cx<T>(a.x, a.y);
+                a[e].x = (T)0; a[e].y = (T)0;
+                if (row < h.nx && c0 < h.ny) a[e] = *reinterpret_cast<const T2 *>(x + ro + c0);
             }
+            if (beam) {
+                T2 bm[16];
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const int c0 = 2 * (t + e * NT);
+                    bm[e].x = (T)1; bm[e].y = (T)1;
+                    if (row < h.nx && c0 < h.ny) bm[e] = *reinterpret_cast<const T2 *>(beam + ro + c0);
+                }
+#pragma unroll
+                for (int e = 0; e < 16; ++e) { a[e].x *= bm[e].x; a[e].y *= bm[e].y; }
+            }
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = cx<T>(a[e].x, a[e].y);
             ct_fft<T, M, -1>(v, t, buf, tab, bar);
             bar();
             Cx<T> *q = buf + ct_pad(t);
@@ -94,6 +101,7 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
         }
         __syncthreads();
         // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
+#pragma unroll 4
         for (int i = threadIdx.x; i < (M + 1) * RB; i += 2 * NT) {
             const int l = i & (RB - 1), k = i / RB;
             const Cx<T> *b2 = bufs + l * ct_stride(M);
@@ -185,6 +193,7 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
     for (int batch = blockIdx.x; batch < total; batch += gridDim.x) {
         const int band = batch / nbatch_band;
         const int row0 = (batch - band * nbatch_band) * RB;
+#pragma unroll 8
         for (int i = threadIdx.x; i < (M + 1) * RB; i += 2 * NT) {
             const int l = i & (RB - 1), k = i / RB;
             Cx<T> X = cx<T>((T)0, (T)0);
