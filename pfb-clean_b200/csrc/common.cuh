@@ -83,4 +83,34 @@ static const int kNumSM = 2;  // CPU emulator (tests only): keep grids tiny
 static const int kNumSM = 148;
 #endif
 
+// ---------------------------------------------------------------------------
+// cp.async (LDGSTS) helpers: global -> shared copies that tie up no registers
+// while in flight; bytes beyond `src_bytes` are zero-filled by the copy itself.
+template <int BYTES>
+__device__ __forceinline__ void cp_async_zfill(void *smem_dst, const void *gsrc, int src_bytes) {
+#ifdef PFB_EMU
+    unsigned char tmp[BYTES];
+    for (int i = 0; i < BYTES; ++i) tmp[i] = i < src_bytes ? ((const unsigned char *)gsrc)[i] : 0;
+    for (int i = 0; i < BYTES; ++i) ((unsigned char *)smem_dst)[i] = tmp[i];
+#else
+    unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+    if (BYTES == 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
+    else if (BYTES == 4)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
+#endif
+}
+__device__ __forceinline__ void cp_async_commit() {
+#ifndef PFB_EMU
+    asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
+}
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+#ifndef PFB_EMU
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+#endif
+}
+
 }  // namespace pfb

@@ -285,11 +285,22 @@ template <class T, int H>
 static int fast_cols(pfb_hess_plan *p, cudaStream_t st) {
     const HessDims &h = p->h;
     size_t smem = sizeof(Cx<T>) * ((size_t)2 * ct_stride(H) + ct_tab_size(H));
-    auto kern = &k_hessf_cols<T, H>;
-    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = persistent_grid((const void *)kern, H / 8, smem, h.nyo2 * h.nband, p->nsm);
-    launch(kern, dim3(grid), dim3(H / 8), smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
-           (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h);
+    // prefetching variant: 3H more complex values; S columns must be 16-byte aligned
+    const size_t smem_pf = smem + sizeof(Cx<T>) * 3 * (size_t)H;
+    const bool pf = smem_pf <= kMaxSmemFast && (h.nx * sizeof(Cx<T>)) % 16 == 0 && !getenv("PFB_HESS_NOPF");
+    if (pf) {
+        auto kern = &k_hessf_cols<T, H, true>;
+        PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pf));
+        int grid = persistent_grid((const void *)kern, H / 8, smem_pf, h.nyo2 * h.nband, p->nsm);
+        launch(kern, dim3(grid), dim3(H / 8), smem_pf, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
+               (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h);
+    } else {
+        auto kern = &k_hessf_cols<T, H, false>;
+        PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int grid = persistent_grid((const void *)kern, H / 8, smem, h.nyo2 * h.nband, p->nsm);
+        launch(kern, dim3(grid), dim3(H / 8), smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
+               (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h);
+    }
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }

@@ -119,36 +119,85 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
 // ------------------------------------------------------------------ pass B
 // psfE: (nband, nyo2, 2H) de-interleaved [even rows | odd rows], pre-scaled.
 // modg[n] = exp(-2 pi i n / (2H)), n < H.
-template <class T, int H>
+// PF: the next column of S (H complex) and this group's half of the next psfE
+// column are fetched with cp.async into two extra shared-memory stages while the
+// current column is being transformed, so neither load latency is exposed (one
+// CTA of 16 warps per SM cannot hide it by occupancy).  Needs 3H more complex
+// values of shared memory; the host falls back to PF = false when that does not
+// fit (fp64 at H = 4096).
+template <class T, int H, bool PF>
 __global__ void __launch_bounds__(H / 8, 1)
 k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__ tabg,
              const Cx<T> *__restrict__ modg, HessDims h) {
     PFB_DYN_SMEM(raw);
     Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
     Cx<T> *tab = bufs + 2 * ct_stride(H);
+    Cx<T> *stS = tab + ct_tab_size(H);           // PF: next column of S
+    Cx<T> *stP = stS + H;                        // PF: [even | odd] psfE of the column in flight
     constexpr int NT = H / 16;
+    constexpr int CPV = 16 / (int)sizeof(Cx<T>); // complex values per 16-byte copy (2 or 1)
     const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
     const GroupBar bar{1 + g, NT};
     ct_load_table<T, H>(tab, tabg);
-    __syncthreads();
     Cx<T> *buf = bufs + g * ct_stride(H);
     const int total = h.nyo2 * h.nband;
+    auto fetch_S = [&](const int col) {          // whole CTA, zero fill beyond nx
+        if (col < total) {
+            const Cx<T> *line = S + (long)col * h.nx;
+            for (int c = threadIdx.x; c < H / CPV; c += 2 * NT) {
+                int left = (h.nx - c * CPV) * (int)sizeof(Cx<T>);
+                left = left < 0 ? 0 : (left > 16 ? 16 : left);
+                cp_async_zfill<16>(stS + c * CPV, left ? line + c * CPV : S, left);
+            }
+        }
+        cp_async_commit();
+    };
+    auto fetch_P = [&](const int col) {          // this group's half only
+        if (col < total) {
+            const Cx<T> *src = psfE + (long)col * (2 * H) + g * H;
+            for (int c = t; c < H / CPV; c += NT) cp_async_zfill<16>(stP + g * H + c * CPV, src + c * CPV, 16);
+        }
+        cp_async_commit();
+    };
+    if (PF) {
+        fetch_S(blockIdx.x);
+        fetch_P(blockIdx.x);
+    }
+    __syncthreads();
     for (int col = blockIdx.x; col < total; col += gridDim.x) {
         Cx<T> *line = S + (long)col * h.nx;
         const Cx<T> *pl = psfE + (long)col * (2 * H) + g * H;
         Cx<T> v[16];
+        if (PF) {
+            cp_async_wait<1>();                  // S(col) has landed (psfE(col) may still be in flight)
+            __syncthreads();
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-            const int i = t + e * NT;
-            v[e] = i < h.nx ? line[i] : cx<T>((T)0, (T)0);
+            for (int e = 0; e < 16; ++e) v[e] = stS[t + e * NT];
+            __syncthreads();                     // both groups have read the stage
+            fetch_S(col + gridDim.x);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                const int i = t + e * NT;
+                v[e] = i < h.nx ? line[i] : cx<T>((T)0, (T)0);
+            }
         }
         if (g == 1) {
 #pragma unroll
             for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], modg[t + e * NT]);
         }
         ct_fft<T, H, -1>(v, t, buf, tab, bar);
+        if (PF) {
+            cp_async_wait<1>();                  // psfE(col): everything but the S fetch just issued
+            bar();                               // copies of the whole group are visible
 #pragma unroll
-        for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], pl[t + e * NT]);
+            for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], stP[g * H + t + e * NT]);
+            bar();
+            fetch_P(col + gridDim.x);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], pl[t + e * NT]);
+        }
         ct_fft<T, H, +1>(v, t, buf, tab, bar);
         if (g == 1) {
 #pragma unroll
@@ -172,6 +221,7 @@ k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__
         }
         __syncthreads();
     }
+    if (PF) cp_async_wait<0>();
 }
 
 // ------------------------------------------------------------------ pass C

@@ -51,33 +51,6 @@ static const int kPD = 8;            // prefetch distance (coefficient rows in f
 // image are zero-filled by the copy itself (src-size operand).
 __host__ __device__ constexpr int stream_ring_elems() { return kPD * 2 * 32 * 2; }
 
-template <int BYTES>
-__device__ __forceinline__ void cp_async_zfill(void *smem_dst, const void *gsrc, int src_bytes) {
-#ifdef PFB_EMU
-    unsigned char tmp[BYTES];
-    for (int i = 0; i < BYTES; ++i) tmp[i] = i < src_bytes ? ((const unsigned char *)gsrc)[i] : 0;
-    for (int i = 0; i < BYTES; ++i) ((unsigned char *)smem_dst)[i] = tmp[i];
-#else
-    unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
-    if (BYTES == 16)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
-    else if (BYTES == 4)
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
-    else
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
-#endif
-}
-__device__ __forceinline__ void cp_async_commit() {
-#ifndef PFB_EMU
-    asm volatile("cp.async.commit_group;" ::: "memory");
-#endif
-}
-template <int N> __device__ __forceinline__ void cp_async_wait() {
-#ifndef PFB_EMU
-    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-#endif
-}
-
 template <class T> struct Vec2 { T v[2]; };
 __device__ __forceinline__ Vec2<float> ldv2(const float *p) {
     float2 q = *reinterpret_cast<const float2 *>(p);
