@@ -151,9 +151,9 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
     per_kernel = {                              # inputs + outputs of each kernel, counted once
         "k_dwt_level": None, "k_idwt_level": None,   # per-op figure used instead (3 launches each)
         "k_dwt_stream": None, "k_idwt_stream": None,
-        "k_dual": nb_local * 3 * C1 + C1,       # read vp,v ; write v ; weight once (2v-vp is fused into hdot)
+        "k_dual": nb_local * 4 * C1 + C1,       # read vp,v ; write v and u = 2v-vp ; weight once
         "k_dual_partial": nb_local * 3 * C1 + C1,
-        "k_dual_apply": nb_local * 3 * C1 + 2 * C1,   # read vp,v,bsum,w ; write v
+        "k_dual_apply": nb_local * 4 * C1 + 2 * C1,   # read vp,v,bsum,w ; write v,u
         "k_hess_rows_fwd": nb_local * (P1 + S),
         "k_hess_cols": nb_local * (2 * S + psfhat),
         "k_hess_rows_inv": nb_local * (S + P1),
@@ -163,9 +163,9 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
         per_kernel["k_hessf_" + k] = per_kernel["k_hess_" + k]
     per_op = {                                  # SURVEY 8(d) table, x nb_local
         "psi_dot": nb_local * (P1 + C1),
-        "psi_hdot": nb_local * (2 * C1 + P1),   # hdot(2v - vp): both dual arrays are read
+        "psi_hdot": nb_local * (C1 + P1),       # hdot(u), u = 2v - vp written by the dual update
         "psf_convolve": nb_local * (2 * P1 + psfhat),
-        "dual_update": nb_local * 3 * C1 + C1,
+        "dual_update": nb_local * 4 * C1 + C1,
         "primal_update+eps": nb_local * 5 * P1,
     }
     fused_iter = nb_local * (3 * P1 + psfhat + 2 * C1) + C1     # SURVEY 8(d) headline lower bound

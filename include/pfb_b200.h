@@ -75,14 +75,15 @@ int pfb_dual_update(const void *vp, void *v, const void *weight, void *u,
 
 /* Band-sharded split of the same update (the reference's distributed analogue
  * is vtilde_update + get_ratio + update, pfb/opt/primal_dual.py:183-222):
- *   partial: v <- vp + sigma*v ; bsum[k] = sum (or sum of squares) over the
- *            LOCAL bands.  The caller all-reduces bsum (SUM) across ranks.
- *   apply  : v <- v * (1 - max(a - lam w/sigma, 0)/a), a from bsum; u as above
+ *   partial: bsum[k] = sum (or sum of squares) of vp + sigma*v over the LOCAL
+ *            bands; v is not modified.  The caller all-reduces bsum (SUM).
+ *   apply  : v <- (vp + sigma*v) * (1 - max(a - lam w/sigma, 0)/a), a from
+ *            bsum; u as above
  * band_stride = elements between consecutive bands of vp / v (0 => n); a value
  * > n lets the caller run the split on one basis slab of a (nband, nbasis, ...)
  * array at a time, so that the all-reduce of basis b overlaps the kernels of
  * basis b+1. */
-int pfb_dual_partial(const void *vp, void *v, void *bsum, int nband, long long n,
+int pfb_dual_partial(const void *vp, const void *v, void *bsum, int nband, long long n,
                      long long band_stride, double sigma, int mode, int dtype, void *stream);
 int pfb_dual_apply(const void *vp, void *v, const void *bsum, const void *weight,
                    void *u, int nband, long long n, long long band_stride, double lam,
@@ -183,6 +184,11 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
 int pfb_hess_plan_destroy(pfb_hess_plan *plan);
 /* (re)load the PSF transfer function; call again whenever psfhat changes */
 int pfb_hess_plan_set_psfhat(pfb_hess_plan *plan, const void *psfhat, void *stream);
+/* Work distribution of the persistent kernels: 0 (default) = static round-robin,
+ * 1 = items handed out by an atomic counter.  Dynamic costs a few percent on an
+ * idle GPU and wins when a concurrent kernel holds SMs (the NCCL all-reduce
+ * that the band-sharded solver overlaps with this operator). */
+int pfb_hess_plan_set_dynamic(pfb_hess_plan *plan, int on);
 /* out = conv(x)                                    beam NULL, add_x 0, has_wsum 0
  * out = beam*conv(beam*x) [/wsum] + sigmainv*x     add_x 1
  * out must not alias x. */

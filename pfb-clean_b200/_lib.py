@@ -54,6 +54,7 @@ _SIGS = {
     "pfb_hess_plan_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_int, c_int, c_int]),
     "pfb_hess_plan_destroy": (c_int, [_P]),
     "pfb_hess_plan_set_psfhat": (c_int, [_P, _P, _P]),
+    "pfb_hess_plan_set_dynamic": (c_int, [_P, c_int]),
     "pfb_hess_apply": (c_int, [_P, _P, _P, c_int, c_double, c_int, c_double, _P, _P]),
     "pfb_pcg_direction": (c_int, [_P, _P, c_double, c_double, c_longlong, c_int, _P, _P]),
 }

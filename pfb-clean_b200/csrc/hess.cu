@@ -204,6 +204,8 @@ struct pfb_hess_plan {
     void *tabM, *tabH;       // ct_fft stage tables for lengths M and H
     void *twr;               // exp(-2 pi i k / nyp), k = 0..M
     void *modg;              // exp(-2 pi i n / nxp), n = 0..H-1
+    int *ctr;                // work counters of the three persistent kernels (ItemQueue)
+    int dyn;                 // hand items out dynamically (see pfb_hess_set_dynamic)
 };
 
 namespace pfb {
@@ -257,12 +259,12 @@ template <class T, int M, int RB>
 static int fast_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
     const HessDims &h = p->h;
     size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
-    auto kern = &k_hessf_rows_fwd<T, M, RB>;
+    auto kern = p->dyn ? &k_hessf_rows_fwd<T, M, RB, true> : &k_hessf_rows_fwd<T, M, RB, false>;
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int nbb = cdiv(h.nx, RB);
     int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
     launch(kern, dim3(grid), dim3(M / 8), smem, st, x, beam, (Cx<T> *)p->S, (const Cx<T> *)p->tabM,
-           (const Cx<T> *)p->twr, h, nbb);
+           (const Cx<T> *)p->twr, h, nbb, p->ctr + 0);
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
@@ -271,12 +273,12 @@ template <class T, int M, int RB>
 static int fast_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
     const HessDims &h = p->h;
     size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
-    auto kern = &k_hessf_rows_inv<T, M, RB>;
+    auto kern = p->dyn ? &k_hessf_rows_inv<T, M, RB, true> : &k_hessf_rows_inv<T, M, RB, false>;
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int nbb = cdiv(h.nx, RB);
     int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
     launch(kern, dim3(grid), dim3(M / 8), smem, st, (const Cx<T> *)p->S, out, (const Cx<T> *)p->tabM,
-           (const Cx<T> *)p->twr, h, nbb, ep);
+           (const Cx<T> *)p->twr, h, nbb, ep, p->ctr + 2);
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
@@ -289,17 +291,17 @@ static int fast_cols(pfb_hess_plan *p, cudaStream_t st) {
     const size_t smem_pf = smem + sizeof(Cx<T>) * 3 * (size_t)H;
     const bool pf = smem_pf <= kMaxSmemFast && (h.nx * sizeof(Cx<T>)) % 16 == 0 && !getenv("PFB_HESS_NOPF");
     if (pf) {
-        auto kern = &k_hessf_cols<T, H, true>;
+        auto kern = p->dyn ? &k_hessf_cols<T, H, true, true> : &k_hessf_cols<T, H, true, false>;
         PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pf));
         int grid = persistent_grid((const void *)kern, H / 8, smem_pf, h.nyo2 * h.nband, p->nsm);
         launch(kern, dim3(grid), dim3(H / 8), smem_pf, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
-               (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h);
+               (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h, p->ctr + 1);
     } else {
-        auto kern = &k_hessf_cols<T, H, false>;
+        auto kern = p->dyn ? &k_hessf_cols<T, H, false, true> : &k_hessf_cols<T, H, false, false>;
         PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int grid = persistent_grid((const void *)kern, H / 8, smem, h.nyo2 * h.nband, p->nsm);
         launch(kern, dim3(grid), dim3(H / 8), smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
-               (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h);
+               (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h, p->ctr + 1);
     }
     PFB_CHECK_LAUNCH();
     return PFB_OK;
@@ -357,6 +359,7 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
     ep.wsum = (T)wsum;
     ep.sigmainv = (T)sigmainv;
     ep.has_wsum = has_wsum;
+    if (p->fast && p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
     if (fast_rows) {
         if (int rc = fast_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
     } else {
@@ -491,12 +494,17 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
             bool ok2 = upload(&p->tabM, ct_tab_size(M), [&](auto put) { ct_fill_table(M, put); }) &&
                        upload(&p->tabH, ct_tab_size(H), [&](auto put) { ct_fill_table(H, put); }) &&
                        upload(&p->twr, M + 1, lin(M + 1, nyp)) && upload(&p->modg, H, lin(H, nxp));
+            ok2 = ok2 && cudaMalloc((void **)&p->ctr, 3 * sizeof(int)) == cudaSuccess;
             if (!ok2) {
                 pfb_hess_plan_destroy(p);
                 return fail(PFB_ERR_ALLOC, "hessian plan (fast path tables) allocation failed");
             }
         }
         p->fast = fast ? 1 : 0;
+        // Dynamic distribution costs ~5 % when the GPU is otherwise idle (measured on the
+        // column pass) and wins when a concurrent kernel holds SMs (NCCL all-reduce of
+        // the band-sharded solver): off by default, the sharded solver turns it on.
+        p->dyn = getenv("PFB_HESS_DYNAMIC") ? atoi(getenv("PFB_HESS_DYNAMIC")) : 0;
     }
     *out = p;
     return PFB_OK;
@@ -508,8 +516,15 @@ int pfb_hess_plan_destroy(pfb_hess_plan *p) {
     if (p->tabH) cudaFree(p->tabH);
     if (p->twr) cudaFree(p->twr);
     if (p->modg) cudaFree(p->modg);
+    if (p->ctr) cudaFree(p->ctr);
     cudaFree(p->tw); cudaFree(p->S); cudaFree(p->psfT);
     delete p;
+    return PFB_OK;
+}
+
+int pfb_hess_plan_set_dynamic(pfb_hess_plan *p, int on) {
+    if (!p) return fail(PFB_ERR_BAD_ARG, "pfb_hess_plan_set_dynamic: null plan");
+    p->dyn = on ? 1 : 0;
     return PFB_OK;
 }
 

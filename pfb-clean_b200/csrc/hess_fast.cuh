@@ -46,13 +46,42 @@ __device__ __forceinline__ void ct_load_table(Cx<T> *dst, const Cx<T> *__restric
     for (int i = threadIdx.x; i < ct_tab_size(N); i += blockDim.x) dst[i] = src[i];
 }
 
+// Dynamic work distribution for the persistent CTAs: items are handed out by an
+// atomic counter (zeroed by the host before the launch), so a CTA that becomes
+// resident late -- another kernel, e.g. the NCCL all-reduce of the band-sharded
+// dual update, is holding SMs -- takes fewer items instead of stretching the
+// launch by its whole static share.  The atomic is issued one item ahead
+// (request) and its result is only touched at the end of the current item
+// (publish, which doubles as the loop's trailing barrier), so its latency is
+// never exposed.
+// DYN = false: static round-robin partition (blockIdx.x, += gridDim.x), no atomics.
+template <bool DYN> struct ItemQueue {
+    int *counter;
+    int r, phase;
+    __device__ __forceinline__ void init(int *c) { counter = c; r = (int)blockIdx.x - (int)gridDim.x; phase = 0; }
+    __device__ __forceinline__ void request() {
+        if (!DYN) r += gridDim.x;
+        else if (threadIdx.x == 0) r = atomicAdd(counter, 1);
+    }
+    // barrier + broadcast of the requested item.  Two slots, alternating: a slot is
+    // rewritten only after one more barrier, i.e. after everyone has read it.
+    __device__ __forceinline__ int publish() {
+        if (!DYN) { __syncthreads(); return r; }
+        __shared__ int s_item[2];
+        phase ^= 1;
+        if (threadIdx.x == 0) s_item[phase] = r;
+        __syncthreads();
+        return s_item[phase];
+    }
+};
+
 // ------------------------------------------------------------------ pass A
 // twr[k] = exp(-2 pi i k / nyp), k = 0..M
-template <class T, int M, int RB>
+template <class T, int M, int RB, bool DYN>
 __global__ void __launch_bounds__(M / 8, 1)
 k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__restrict__ S,
                  const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twr, HessDims h,
-                 int nbatch_band) {
+                 int nbatch_band, int *counter) {
     PFB_DYN_SMEM(raw);
     Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
     Cx<T> *tab = bufs + RB * ct_stride(M);
@@ -63,7 +92,12 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
     __syncthreads();
     typedef typename V2<T>::type T2;
     const int total = nbatch_band * h.nband;
-    for (int batch = blockIdx.x; batch < total; batch += gridDim.x) {
+    ItemQueue<DYN> q;
+    q.init(counter);
+    q.request();
+    int batch = q.publish();
+    while (batch < total) {
+        q.request();                             // the next batch, consumed by publish() below
         const int band = batch / nbatch_band;
         const int row0 = (batch - band * nbatch_band) * RB;
 #pragma unroll 1
@@ -112,7 +146,7 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
             const Cx<T> X = E + cmul(twr[k], O);
             if (row0 + l < h.nx) S[((long)band * h.nyo2 + k) * h.nx + row0 + l] = X;
         }
-        __syncthreads();
+        batch = q.publish();
     }
 }
 
@@ -125,10 +159,10 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
 // CTA of 16 warps per SM cannot hide it by occupancy).  Needs 3H more complex
 // values of shared memory; the host falls back to PF = false when that does not
 // fit (fp64 at H = 4096).
-template <class T, int H, bool PF>
+template <class T, int H, bool PF, bool DYN>
 __global__ void __launch_bounds__(H / 8, 1)
 k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__ tabg,
-             const Cx<T> *__restrict__ modg, HessDims h) {
+             const Cx<T> *__restrict__ modg, HessDims h, int *counter) {
     PFB_DYN_SMEM(raw);
     Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
     Cx<T> *tab = bufs + 2 * ct_stride(H);
@@ -159,12 +193,19 @@ k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__
         }
         cp_async_commit();
     };
+    ItemQueue<DYN> q;
+    q.init(counter);
+    q.request();
+    int col = q.publish();
+    q.request();
+    int nxt = q.publish();                       // prefetched while `col` is transformed
     if (PF) {
-        fetch_S(blockIdx.x);
-        fetch_P(blockIdx.x);
+        fetch_S(col);
+        fetch_P(col);
     }
     __syncthreads();
-    for (int col = blockIdx.x; col < total; col += gridDim.x) {
+    while (col < total) {
+        q.request();                             // the column after `nxt`
         Cx<T> *line = S + (long)col * h.nx;
         const Cx<T> *pl = psfE + (long)col * (2 * H) + g * H;
         Cx<T> v[16];
@@ -174,7 +215,7 @@ k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__
 #pragma unroll
             for (int e = 0; e < 16; ++e) v[e] = stS[t + e * NT];
             __syncthreads();                     // both groups have read the stage
-            fetch_S(col + gridDim.x);
+            fetch_S(nxt);
         } else {
 #pragma unroll
             for (int e = 0; e < 16; ++e) {
@@ -193,7 +234,7 @@ k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__
 #pragma unroll
             for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], stP[g * H + t + e * NT]);
             bar();
-            fetch_P(col + gridDim.x);
+            fetch_P(nxt);
         } else {
 #pragma unroll
             for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], pl[t + e * NT]);
@@ -219,17 +260,18 @@ k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__
                 if (i < h.nx) line[i] = y;
             }
         }
-        __syncthreads();
+        col = nxt;
+        nxt = q.publish();
     }
     if (PF) cp_async_wait<0>();
 }
 
 // ------------------------------------------------------------------ pass C
-template <class T, int M, int RB>
+template <class T, int M, int RB, bool DYN>
 __global__ void __launch_bounds__(M / 8, 1)
 k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
                  const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twr, HessDims h,
-                 int nbatch_band, Epilogue<T> ep) {
+                 int nbatch_band, Epilogue<T> ep, int *counter) {
     PFB_DYN_SMEM(raw);
     Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
     Cx<T> *tab = bufs + RB * ct_stride(M);
@@ -240,7 +282,12 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
     __syncthreads();
     typedef typename V2<T>::type T2;
     const int total = nbatch_band * h.nband;
-    for (int batch = blockIdx.x; batch < total; batch += gridDim.x) {
+    ItemQueue<DYN> q;
+    q.init(counter);
+    q.request();
+    int batch = q.publish();
+    while (batch < total) {
+        q.request();                             // the next batch, consumed by publish() below
         const int band = batch / nbatch_band;
         const int row0 = (batch - band * nbatch_band) * RB;
 #pragma unroll 8
@@ -288,7 +335,7 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
                 }
             }
         }
-        __syncthreads();
+        batch = q.publish();
     }
 }
 

@@ -124,6 +124,16 @@ k_prox21(const T *__restrict__ v, T *__restrict__ res, const T *__restrict__ w,
     }
 }
 
+// Shrink factor of the dual update, 1 - max(a - lam w/sigma, 0)/a with
+// a = |r|/sigma and r = band sum (21m) or l2 norm over bands (21).  Numerator and
+// denominator are multiplied by sigma, which leaves ONE fp64 division per
+// coefficient instead of three: with one band per GPU the three divisions made
+// the (then fp64-pipe bound) apply kernel twice as slow as its memory traffic.
+__device__ __forceinline__ double shrink_factor(double s, double lam_w, int mode) {
+    const double r = mode ? sqrt(s) : fabs(s);
+    return r != 0.0 ? 1.0 - fmax(r - lam_w, 0.0) / r : 1.0;
+}
+
 // ---------------------------------------------------------------------------
 // dual_update_numba, optionally fused with the `vp = 2 v - vp` that follows it
 // in primal_dual_optimised (pfb/opt/primal_dual.py:136-137).
@@ -132,7 +142,7 @@ k_prox21(const T *__restrict__ v, T *__restrict__ res, const T *__restrict__ w,
 // The raw vp/v packs stay in registers (vt is recomputed for the store instead
 // of being kept in fp64) so a thread has 2*NB 16-byte loads in flight.
 template <class T, int V, int NB>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)      // <= 128 registers: two CTAs (128 KB of loads) in flight per SM
 k_dual(const T *vp, T *v, const T *__restrict__ w, T *u, int nband, long n,
        double lam, double sigma, int mode) {
     long nv = n / V;
@@ -170,9 +180,7 @@ k_dual(const T *vp, T *v, const T *__restrict__ w, T *u, int nband, long n,
         double f[V];
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-            double a = fabs((mode ? sqrt(s[e]) : s[e]) / sigma);
-            f[e] = 1.0;
-            if (a != 0.0) f[e] = 1.0 - fmax(a - lam * (double)wk.v[e] / sigma, 0.0) / a;
+            f[e] = shrink_factor(s[e], lam * (double)wk.v[e], mode);
         }
         if (NB > 0) {
 #pragma unroll
@@ -205,12 +213,14 @@ k_dual(const T *vp, T *v, const T *__restrict__ w, T *u, int nband, long n,
 // ---------------------------------------------------------------------------
 // Band-sharded (multi-GPU) split of the dual update.  Each rank owns nband
 // local bands:
-//   k_dual_partial : v <- vt = vp + sigma*v (in place), bsum[k] = red_local(vt)
+//   k_dual_partial : bsum[k] = red_local(vp + sigma*v)        (v is NOT modified)
 //   (NCCL all-reduce SUM of bsum over ranks, issued by the host)
-//   k_dual_apply   : v <- vt * factor(bsum), u <- 2 v - vp
-template <class T, int V>
-__global__ void __launch_bounds__(256)
-k_dual_partial(const T *__restrict__ vp, T *v, T *__restrict__ bsum, int nband,
+//   k_dual_apply   : v <- (vp + sigma*v) * factor(bsum), u <- 2 v - vp
+// vt is recomputed by apply instead of being stored by partial: 2*nband*C fewer
+// bytes per iteration.  NB as in k_dual (0 = run-time band count).
+template <class T, int V, int NB>
+__global__ void __launch_bounds__(256, 2)
+k_dual_partial(const T *__restrict__ vp, const T *__restrict__ v, T *__restrict__ bsum, int nband,
                long n, long bs, double sigma, int mode) {
     long nv = n / V;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
@@ -219,15 +229,29 @@ k_dual_partial(const T *__restrict__ vp, T *v, T *__restrict__ bsum, int nband,
         double s[V];
 #pragma unroll
         for (int e = 0; e < V; ++e) s[e] = 0.0;
-        for (int b = 0; b < nband; ++b) {
-            Pack<T, V> a = ld<T, V>(vp + b * bs + k), c = ld<T, V>(v + b * bs + k), o;
+        if (NB > 0) {
+            Pack<T, V> pa[NB > 0 ? NB : 1], pc[NB > 0 ? NB : 1];
 #pragma unroll
-            for (int e = 0; e < V; ++e) {
-                double x = (double)a.v[e] + sigma * (double)c.v[e];
-                o.v[e] = (T)x;
-                s[e] += mode ? x * x : x;
+            for (int b = 0; b < NB; ++b) {
+                pa[b] = ld<T, V>(vp + b * bs + k);
+                pc[b] = ld<T, V>(v + b * bs + k);
             }
-            st<T, V>(v + b * bs + k, o);
+#pragma unroll
+            for (int b = 0; b < NB; ++b)
+#pragma unroll
+                for (int e = 0; e < V; ++e) {
+                    double x = (double)pa[b].v[e] + sigma * (double)pc[b].v[e];
+                    s[e] += mode ? x * x : x;
+                }
+        } else {
+            for (int b = 0; b < nband; ++b) {
+                Pack<T, V> a = ld<T, V>(vp + b * bs + k), c = ld<T, V>(v + b * bs + k);
+#pragma unroll
+                for (int e = 0; e < V; ++e) {
+                    double x = (double)a.v[e] + sigma * (double)c.v[e];
+                    s[e] += mode ? x * x : x;
+                }
+            }
         }
         Pack<T, V> so;
 #pragma unroll
@@ -236,8 +260,8 @@ k_dual_partial(const T *__restrict__ vp, T *v, T *__restrict__ bsum, int nband,
     }
 }
 
-template <class T, int V>
-__global__ void __launch_bounds__(256)
+template <class T, int V, int NB>
+__global__ void __launch_bounds__(256, 2)
 k_dual_apply(const T *vp, T *v, const T *__restrict__ bsum,
              const T *__restrict__ w, T *u, int nband, long n, long bs, double lam,
              double sigma, int mode) {
@@ -245,25 +269,44 @@ k_dual_apply(const T *vp, T *v, const T *__restrict__ bsum,
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long)gridDim.x * blockDim.x) {
         long k = i * V;
+        Pack<T, V> pa[NB > 0 ? NB : 1], pc[NB > 0 ? NB : 1];
+        if (NB > 0) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                pa[b] = ld<T, V>(vp + b * bs + k);
+                pc[b] = ld<T, V>(v + b * bs + k);
+            }
+        }
         Pack<T, V> sk = ld<T, V>(bsum + k), wk = ld<T, V>(w + k);
         double f[V];
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-            double s = (double)sk.v[e];
-            double a = fabs((mode ? sqrt(s) : s) / sigma);
-            f[e] = 1.0;
-            if (a != 0.0) f[e] = 1.0 - fmax(a - lam * (double)wk.v[e] / sigma, 0.0) / a;
+            f[e] = shrink_factor((double)sk.v[e], lam * (double)wk.v[e], mode);
         }
-        for (int b = 0; b < nband; ++b) {
-            Pack<T, V> c = ld<T, V>(v + b * bs + k), o, uo, a;
-            if (u) a = ld<T, V>(vp + b * bs + k);
+        if (NB > 0) {
 #pragma unroll
-            for (int e = 0; e < V; ++e) {
-                o.v[e] = (T)((double)c.v[e] * f[e]);
-                if (u) uo.v[e] = (T)2 * o.v[e] - a.v[e];
+            for (int b = 0; b < NB; ++b) {
+                Pack<T, V> o, uo;
+#pragma unroll
+                for (int e = 0; e < V; ++e) {
+                    double x = (double)pa[b].v[e] + sigma * (double)pc[b].v[e];
+                    o.v[e] = (T)(x * f[e]);
+                    uo.v[e] = (T)2 * o.v[e] - pa[b].v[e];
+                }
+                st<T, V>(v + b * bs + k, o);
+                if (u) st<T, V>(u + b * bs + k, uo);
             }
-            st<T, V>(v + b * bs + k, o);
-            if (u) st<T, V>(u + b * bs + k, uo);
+        } else {
+            for (int b = 0; b < nband; ++b) {
+                Pack<T, V> a = ld<T, V>(vp + b * bs + k), c = ld<T, V>(v + b * bs + k), o, uo;
+#pragma unroll
+                for (int e = 0; e < V; ++e) {
+                    o.v[e] = (T)(((double)a.v[e] + sigma * (double)c.v[e]) * f[e]);
+                    uo.v[e] = (T)2 * o.v[e] - a.v[e];
+                }
+                st<T, V>(v + b * bs + k, o);
+                if (u) st<T, V>(u + b * bs + k, uo);
+            }
         }
     }
 }
@@ -561,12 +604,18 @@ static int dual_t(const T *vp, T *v, const T *w, T *u, int nband, long n, double
 }
 
 template <class T>
-static int dual_partial_t(const T *vp, T *v, T *bsum, int nband, long n, long bs, double sigma,
+static int dual_partial_t(const T *vp, const T *v, T *bsum, int nband, long n, long bs, double sigma,
                           int mode, cudaStream_t st) {
     const int V = 16 / sizeof(T);
     bool vec = (n % V == 0) && (bs % V == 0) && aligned16<T>(v) && aligned16<T>(vp) && aligned16<T>(bsum);
-    if (vec) launch(&k_dual_partial<T, V>, dim3(stream_grid(n / V)), dim3(256), 0, st, vp, v, bsum, nband, n, bs, sigma, mode);
-    else launch(&k_dual_partial<T, 1>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, bsum, nband, n, bs, sigma, mode);
+    if (vec) {
+        dim3 g(stream_grid(n / V)), b(256);
+#define PFB_CALL(NB) launch(&k_dual_partial<T, V, NB>, g, b, 0, st, vp, v, bsum, nband, n, bs, sigma, mode)
+        PFB_NB_SWITCH(nband, PFB_CALL)
+#undef PFB_CALL
+    } else {
+        launch(&k_dual_partial<T, 1, 0>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, bsum, nband, n, bs, sigma, mode);
+    }
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
@@ -577,8 +626,14 @@ static int dual_apply_t(const T *vp, T *v, const T *bsum, const T *w, T *u, int 
     const int V = 16 / sizeof(T);
     bool vec = (n % V == 0) && (bs % V == 0) && aligned16<T>(v) && aligned16<T>(vp) && aligned16<T>(bsum) &&
                aligned16<T>(w) && aligned16<T>(u);
-    if (vec) launch(&k_dual_apply<T, V>, dim3(stream_grid(n / V)), dim3(256), 0, st, vp, v, bsum, w, u, nband, n, bs, lam, sigma, mode);
-    else launch(&k_dual_apply<T, 1>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, bsum, w, u, nband, n, bs, lam, sigma, mode);
+    if (vec) {
+        dim3 g(stream_grid(n / V)), b(256);
+#define PFB_CALL(NB) launch(&k_dual_apply<T, V, NB>, g, b, 0, st, vp, v, bsum, w, u, nband, n, bs, lam, sigma, mode)
+        PFB_NB_SWITCH(nband, PFB_CALL)
+#undef PFB_CALL
+    } else {
+        launch(&k_dual_apply<T, 1, 0>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, bsum, w, u, nband, n, bs, lam, sigma, mode);
+    }
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
@@ -680,7 +735,7 @@ int pfb_dual_update(const void *vp, void *v, const void *weight, void *u, int nb
                  dual_t<double>((const double *)vp, (double *)v, (const double *)weight, (double *)u, nband, n, lam, sigma, mode, st));
 }
 
-int pfb_dual_partial(const void *vp, void *v, void *bsum, int nband, long long n,
+int pfb_dual_partial(const void *vp, const void *v, void *bsum, int nband, long long n,
                      long long band_stride, double sigma, int mode, int dtype, void *stream) {
     if (band_stride <= 0) band_stride = n;
     if (!vp || !v || !bsum || nband < 1 || n < 0 || band_stride < n)
@@ -688,8 +743,8 @@ int pfb_dual_partial(const void *vp, void *v, void *bsum, int nband, long long n
     if (n == 0) return PFB_OK;
     cudaStream_t st = as_stream(stream);
     PFB_DISPATCH(dtype,
-                 dual_partial_t<float>((const float *)vp, (float *)v, (float *)bsum, nband, n, band_stride, sigma, mode, st),
-                 dual_partial_t<double>((const double *)vp, (double *)v, (double *)bsum, nband, n, band_stride, sigma, mode, st));
+                 dual_partial_t<float>((const float *)vp, (const float *)v, (float *)bsum, nband, n, band_stride, sigma, mode, st),
+                 dual_partial_t<double>((const double *)vp, (const double *)v, (double *)bsum, nband, n, band_stride, sigma, mode, st));
 }
 
 int pfb_dual_apply(const void *vp, void *v, const void *bsum, const void *weight, void *u,

@@ -12,7 +12,7 @@ import weakref
 
 import torch
 
-from .. import _dev, _lib
+from .. import _dev, _lib, parallel
 
 
 class HessPlan:
@@ -25,9 +25,17 @@ class HessPlan:
                                                    nxp, nyp, dtype_code))
         self.shape = (nband, nx, ny, nxp, nyp, dtype_code)
         self.psf_key = None
+        self._dyn = None
 
     def set_psfhat(self, psfhat_dev):
         _lib.check(_lib.lib().pfb_hess_plan_set_psfhat(self._h, _dev.ptr(psfhat_dev), _dev.stream()))
+
+    def set_dynamic(self, on):
+        """Dynamic work distribution of the persistent kernels (used by the band-sharded
+        solver, whose all-reduce runs concurrently with this operator)."""
+        if on != self._dyn:
+            _lib.check(_lib.lib().pfb_hess_plan_set_dynamic(self._h, int(on)))
+            self._dyn = on
 
     def apply(self, x, out, beam=None, add_x=False, sigmainv=0.0, wsum=None):
         _lib.check(_lib.lib().pfb_hess_apply(
@@ -98,6 +106,7 @@ def _convolve(psfhat, lastsize, x, xout, beam=None, add_x=False, sigmainv=0.0, w
     bd = _dev.to_dev(beam) if beam is not None else None
     if bd is not None and bd.dtype != rdt:
         bd = bd.to(rdt)
+    plan.set_dynamic(parallel.active())
     plan.apply(xd, res, bd, add_x, sigmainv, wsum)
     if not direct:
         od.copy_(res)

@@ -80,36 +80,64 @@ def _off(t, nbytes):
     return ctypes.c_void_p(t.data_ptr() + nbytes)
 
 
+def _chunks(nbasis):
+    """Basis slabs are exchanged in groups: more groups pipeline the all-reduce
+    with the partial / apply kernels of the other groups, fewer groups make
+    larger (more bandwidth-efficient) messages.  Measured (profiles/scale_probe2.sh):
+    8 x B200: 5 x 68 MB cost 1.40 ms, 1 x 339 MB 0.88 ms, and the step is fastest
+    with one group (435 / 424 / 396 it/s for 1 / 2 / 5); 2 x B200: 185 / 194 / 190.
+    Default: 2 groups on 2 ranks, 1 beyond; PFB_PAR_CHUNKS overrides."""
+    dflt = "2" if parallel.world_size() <= 2 else "1"
+    k = max(1, min(nbasis, int(os.environ.get("PFB_PAR_CHUNKS", dflt))))
+    edges = [round(i * nbasis / k) for i in range(k + 1)]
+    return [(edges[i], edges[i + 1]) for i in range(k) if edges[i + 1] > edges[i]]
+
+
+def _dual_begin(vp, v, sigma, n, bsum):
+    """Band-sharded dual update, first half: local band sums of vp + sigma*v, one
+    group of basis slabs at a time, each followed by its asynchronous all-reduce
+    (NCCL's own stream).  Returns the work handles.  v is not modified, so
+    whatever the caller launches next (the PSF convolution of the primal step)
+    overlaps the exchange."""
+    L = _lib.lib()
+    nb, nbasis = v.shape[0], v.shape[1]
+    nslab = n // nbasis
+    esz = v.element_size()
+    works = []
+    for b0, b1 in _chunks(nbasis):
+        off = b0 * nslab * esz
+        _lib.check(L.pfb_dual_partial(_off(vp, off), _off(v, off), _off(bsum, off), nb, (b1 - b0) * nslab, n,
+                                      float(sigma), _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
+        works.append(parallel.allreduce_sum_async(bsum.view(-1)[b0 * nslab:b1 * nslab]))
+    return works
+
+
+def _dual_end(works, vp, v, lam, sigma, w, n, bsum, write_u=True):
+    """Second half: v <- (vp + sigma*v) * shrink(all-reduced sums); vp <- 2v - vp."""
+    L = _lib.lib()
+    nb, nbasis = v.shape[0], v.shape[1]
+    nslab = n // nbasis
+    esz = v.element_size()
+    for (b0, b1), work in zip(_chunks(nbasis), works):
+        off = b0 * nslab * esz
+        if work is not None:
+            work.wait()
+        _lib.check(L.pfb_dual_apply(_off(vp, off), _off(v, off), _off(bsum, off), _off(w, off),
+                                    _off(vp, off) if write_u else None, nb, (b1 - b0) * nslab, n, float(lam),
+                                    float(sigma), _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
+
+
 def _dual_step(vp, v, lam, sigma, w, n, bsum, write_u=True):
     """v <- dual update(vp, v); if write_u: vp <- 2 v - vp (else the caller
     fuses 2v - vp into the Psi.hdot loader and vp is left untouched).
     Sharded: split around the all-reduce of the band-sum slab."""
-    L = _lib.lib()
-    nb = v.shape[0]
-    u = _dev.ptr(vp) if write_u else None
     if parallel.active():
-        # one basis slab at a time: the all-reduce of slab b (NCCL's own stream)
-        # overlaps the partial kernel of slab b+1 and the apply kernel of slab b-1
-        nbasis = v.shape[1]
-        nslab = n // nbasis
-        esz = v.element_size()
-        works = []
-        for b in range(nbasis):
-            off = b * nslab * esz
-            _lib.check(L.pfb_dual_partial(_off(vp, off), _off(v, off), _off(bsum, off), nb, nslab, n,
-                                          float(sigma), _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
-            works.append(parallel.allreduce_sum_async(bsum.view(nbasis, -1)[b]))
-        for b in range(nbasis):
-            off = b * nslab * esz
-            if works[b] is not None:
-                works[b].wait()
-            _lib.check(L.pfb_dual_apply(_off(vp, off), _off(v, off), _off(bsum, off), _off(w, off),
-                                        _off(vp, off) if write_u else None, nb, nslab, n, float(lam),
-                                        float(sigma), _lib.BAND_SUM, _dev.dcode(v), _dev.stream()))
+        _dual_end(_dual_begin(vp, v, sigma, n, bsum), vp, v, lam, sigma, w, n, bsum, write_u)
     else:
-        _lib.check(L.pfb_dual_update(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(w), u, nb, n,
-                                     float(lam), float(sigma), _lib.BAND_SUM, _dev.dcode(v),
-                                     _dev.stream()))
+        _lib.check(_lib.lib().pfb_dual_update(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(w),
+                                              _dev.ptr(vp) if write_u else None, v.shape[0], n,
+                                              float(lam), float(sigma), _lib.BAND_SUM, _dev.dcode(v),
+                                              _dev.stream()))
 
 
 def _gap_index(psi_obj, device):
@@ -186,11 +214,22 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     k = -1
     broke = False
     for k in range(maxit):
+        def gradient():
+            if bound is not None:
+                return _convolve(bound[0], bound[1], xprev, conv_buf)
+            return _dev.to_dev(grad.psf_convolve(xprev) if fused_grad else grad(xprev))
+        g = None
         if nat:
             # the dual kernel leaves 2v - vp in the (dead) vp buffer: one coefficient
             # set for the synthesis to read, which is instruction-issue bound
             P.dot_nat(xprev, vcur)
-            _dual_step(vprev, vcur, lam, sigma, w, n, bsum)
+            if parallel.active() and not os.environ.get("PFB_PAR_NOOVERLAP"):
+                # the PSF convolution hides the all-reduce of the band sums
+                works = _dual_begin(vprev, vcur, sigma, n, bsum)
+                g = gradient()
+                _dual_end(works, vprev, vcur, lam, sigma, w, n, bsum)
+            else:
+                _dual_step(vprev, vcur, lam, sigma, w, n, bsum)
             P.hdot_nat(vprev, xout)
         elif fast:   # `vp = 2v - vp` (primal_dual.py:137) is fused into the synthesis loader
             psi(xprev, vcur)
@@ -200,10 +239,8 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             psi(xprev, vcur)
             _dual_step(vprev, vcur, lam, sigma, w, n, bsum)      # vprev now holds 2v - vp
             psiH(vprev, xout)
-        if bound is not None:
-            g = _convolve(bound[0], bound[1], xprev, conv_buf)
-        else:
-            g = _dev.to_dev(grad.psf_convolve(xprev) if fused_grad else grad(xprev))
+        if g is None:
+            g = gradient()
         if g.dtype != xa.dtype:
             g = g.to(xa.dtype)
         _vec.pd_primal(xcur, xprev, xout, g, data, tau, pos_kernel, terms)

@@ -144,6 +144,23 @@ def test_hess_vs_oracle(dtype, nx, ny, nxp, nyp):
     assert rel(got2, exp2) < TOL[dtype]
 
 
+def test_hess_dynamic_distribution_matches_static():
+    """pfb_hess_plan_set_dynamic: same result bit for bit (items are independent)."""
+    from pfb_b200.operators import psf as P
+    rng = np.random.default_rng(3)
+    nband, nx, ny, nxp, nyp = 3, 600, 700, 2048, 2048
+    psfhat = np.fft.rfft2(rng.standard_normal((nband, nxp, nyp)), axes=(1, 2)).astype(np.complex64)
+    x = torch.from_numpy(rng.standard_normal((nband, nx, ny)).astype(np.float32)).cuda()
+    plan = P.get_plan(psfhat, nyp, tuple(x.shape), 0)
+    outs = []
+    for dyn in (False, True, False):
+        plan.set_dynamic(dyn)
+        o = torch.empty_like(x)
+        plan.apply(x, o)
+        outs.append(o)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
 def test_hess_delta_kat_full_size():
     """Config-3 band at full size: x = delta at (p,q) => out = shifted PSF crop
     (SURVEY 8c); exercises the 8192-point column and 4096-point row FFTs."""

@@ -71,7 +71,9 @@ def test_prox_api(backend, tag):
     from pfb_b200.prox import prox_21 as p21
     g = golden(tag)
     v, vp, w = g["v"], g["vp"], g["w"]
-    tol = 1e-14 if v.dtype == np.float64 else 3e-7
+    # 1e-12: the shrink factor 1 - max(a - t, 0)/a cancels when the factor is small; the
+    # kernels evaluate it with one division, the reference with three (north star: 1e-11)
+    tol = 1e-12 if v.dtype == np.float64 else 3e-7
     for i in range(4):
         lam, sigma = g[f"params_{i}"]
         res = np.full(v.shape, np.nan, v.dtype)
