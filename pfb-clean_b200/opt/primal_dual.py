@@ -209,6 +209,18 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         data = data.to(xa.dtype)
     pos_kernel = positivity if not (positivity == 2 and parallel.active()) else 0
 
+    # Convergence test without draining the GPU: the two eps terms are copied to
+    # pinned host memory on a side stream right behind the primal kernel, while
+    # the compute stream already runs the analysis Psi(x) of the next iteration
+    # (valid whatever the test decides: on a break its output buffer is the dead
+    # one).  Only the side stream is synchronised.
+    ahead = nat and not _dev._EMULATED and not os.environ.get("PFB_PD_NOAHEAD")
+    if ahead:
+        side = torch.cuda.Stream()
+        host_terms = torch.empty(2, dtype=torch.float64, pin_memory=True)
+        ev = torch.cuda.Event()
+    have_dot = False            # Psi(xprev) -> vcur was already issued by the previous iteration
+
     eps = 1.0
     numreweight = 0
     k = -1
@@ -222,7 +234,9 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         if nat:
             # the dual kernel leaves 2v - vp in the (dead) vp buffer: one coefficient
             # set for the synthesis to read, which is instruction-issue bound
-            P.dot_nat(xprev, vcur)
+            if not have_dot:
+                P.dot_nat(xprev, vcur)
+            have_dot = False
             if parallel.active() and not os.environ.get("PFB_PAR_NOOVERLAP"):
                 # the PSF convolution hides the all-reduce of the band sums
                 works = _dual_begin(vprev, vcur, sigma, n, bsum)
@@ -249,7 +263,19 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             parallel.allreduce_max(neg)
             xcur[:, neg.bool()] = 0
             norm_diff_terms(xcur, xprev, out=terms)
-        num, den = parallel.allreduce_sum(terms).tolist()
+        if ahead and pos_kernel == positivity:
+            ev.record()
+            if k + 1 < maxit:
+                P.dot_nat(xcur, vprev)       # next iteration: xprev = xcur, vcur = vprev (holds the dead 2v - vp)
+                have_dot = True
+            with torch.cuda.stream(side):
+                side.wait_event(ev)
+                parallel.allreduce_sum(terms)
+                host_terms.copy_(terms, non_blocking=True)
+            side.synchronize()
+            num, den = host_terms.tolist()
+        else:
+            num, den = parallel.allreduce_sum(terms).tolist()
         if den == 0.0:
             raise FloatingPointError("primal_dual: model is identically zero "
                                      "(the reference drops into pdb here)")
