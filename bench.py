@@ -386,8 +386,19 @@ def finish_ours(a, env):
         what = f"{dname}: {op} algorithmic bytes / {NLEVEL} level launches"
     avg_s = dt_ms * 1e-3 / dn
     ach = balg / avg_s / 1e9
+    # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture
+    # (profiles/make_traffic.py); only meaningful for the single-GPU workload it was taken on
+    traffic, traffic_src = None, None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        tk = tj["kernels"].get(dname) or tj["kernels"].get(dname + "_vec")
+        if tk and world == 1 and nb == 8 and nx == 4096 and a.dtype == "f32":
+            traffic, traffic_src = tk["dram_bytes_per_launch"], tj["source"]
+    except (OSError, ValueError, KeyError):
+        pass
     roofline = {"bound": "hbm", "kernel": dname, "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
-                "frac": round(ach / hbm, 4), "traffic": None, "peak_source": peak_src,
+                "frac": round(ach / hbm, 4), "traffic": traffic, "traffic_source": traffic_src,
+                "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": balg, "avg_launch_ms": round(avg_s * 1e3, 4),
                 "share_of_step": round(dt_ms / tot_k, 4), "basis": what}
     kernels = {k: {"launches": n, "ms_per_step": round(t / K, 4), "share": round(t / tot_k, 4)}
