@@ -148,16 +148,19 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
     C1 = nbasis * Nmax * Nmax * s
     psfhat = 2 * s * nxp * nyo2
     S = 2 * s * nx * nyo2                      # pruned half spectrum (pipeline intermediate)
+    # default loop: synthesis by linearity (opt/primal_dual.py `lin`): the dual kernels do not
+    # write 2v - vp, the primal kernel reads w_k and w_{k-1} instead of xout
+    lin = 0 if os.environ.get("PFB_PD_NOLIN") else 1
     per_kernel = {                              # inputs + outputs of each kernel, counted once
         "k_dwt_level": None, "k_idwt_level": None,   # per-op figure used instead (3 launches each)
         "k_dwt_stream": None, "k_idwt_stream": None,
-        "k_dual": nb_local * 4 * C1 + C1,       # read vp,v ; write v and u = 2v-vp ; weight once
+        "k_dual": nb_local * (4 - lin) * C1 + C1,     # read vp,v ; write v (and u = 2v-vp if not lin) ; weight once
         "k_dual_partial": nb_local * 3 * C1 + C1,
-        "k_dual_apply": nb_local * 4 * C1 + 2 * C1,   # read vp,v,bsum,w ; write v,u
+        "k_dual_apply": nb_local * (4 - lin) * C1 + 2 * C1,   # read vp,v,bsum,w ; write v (,u)
         "k_hess_rows_fwd": nb_local * (P1 + S),
         "k_hess_cols": nb_local * (2 * S + psfhat),
         "k_hess_rows_inv": nb_local * (S + P1),
-        "k_pd_primal": nb_local * 5 * P1,       # read xp,xout,conv,data ; write x
+        "k_pd_primal": nb_local * (5 + lin) * P1,     # read xp,xout(,wprev),conv,data ; write x
     }
     for k in ("rows_fwd", "cols", "rows_inv"):  # fast-path kernels move the same bytes
         per_kernel["k_hessf_" + k] = per_kernel["k_hess_" + k]
@@ -165,8 +168,8 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
         "psi_dot": nb_local * (P1 + C1),
         "psi_hdot": nb_local * (C1 + P1),       # hdot(u), u = 2v - vp written by the dual update
         "psf_convolve": nb_local * (2 * P1 + psfhat),
-        "dual_update": nb_local * 4 * C1 + C1,
-        "primal_update+eps": nb_local * 5 * P1,
+        "dual_update": nb_local * (4 - lin) * C1 + C1,
+        "primal_update+eps": nb_local * (5 + lin) * P1,
     }
     fused_iter = nb_local * (3 * P1 + psfhat + 2 * C1) + C1     # SURVEY 8(d) headline lower bound
     return per_kernel, per_op, fused_iter

@@ -111,6 +111,13 @@ int pfb_norm_diff(const void *x, const void *xp, long long n, int dtype,
 int pfb_pd_primal(void *x, const void *xp, const void *xout, const void *conv,
                   const void *data, double tau, int positivity, int nband,
                   long long npix, int dtype, double *out2, void *stream);
+/* Same step with the synthesis taken by linearity: the solver keeps w_k = Psi(v_k)
+ * of the last two iterations and forms xout = Psi(2 v_k - v_{k-1}) = 2 w - wprev
+ * (primal_dual.py:137-138) inside this kernel, so the dual update does not have
+ * to write 2v - vp (one pass over the coefficient cube less per iteration). */
+int pfb_pd_primal_lin(void *x, const void *xp, const void *w, const void *wprev,
+                      const void *conv, const void *data, double tau, int positivity,
+                      int nband, long long npix, int dtype, double *out2, void *stream);
 /* pcg line update, pfb/opt/pcg.py:92-101: x = xp + alpha p; r = rp + alpha Ap;
  * out3 = {<r, minv*r>, sum (x-xp)^2, sum x^2} */
 int pfb_pcg_update(void *x, void *r, const void *xp, const void *rp, const void *p,
@@ -177,7 +184,11 @@ int pfb_psi_hdot_nat(const pfb_psi_plan *plan, const void *nat, const void *nat2
  * = r2c(ifftshift(psf)) as built by pfb/operators/gridder.py:712-714.
  * The plan owns what the reference keeps in xpad/xhat (here: a pruned,
  * transposed half-spectrum) and a transposed, 1/(nxp*nyp)-scaled copy of
- * psfhat.  Padded sizes must be powers of two (PFB_ERR_FFT_SIZE otherwise).  */
+ * psfhat.  Padded sizes: powers of two take the register-resident kernels; any
+ * other even nyp / nxp whose transform lengths factor into 2,3,5,7,11,13 (the
+ * ducc0 good_size lengths of pfb/workers/grid.py:276-284) take the mixed-radix
+ * kernels (hess_mixed.cuh); PFB_ERR_FFT_SIZE otherwise (odd nyp, a larger prime
+ * factor, or two transform lines beyond shared memory).  */
 typedef struct pfb_hess_plan pfb_hess_plan;
 int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp,
                          int nyp, int dtype);

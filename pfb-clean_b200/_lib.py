@@ -39,6 +39,7 @@ _SIGS = {
     "pfb_vdot": (c_int, [_P, _P, _P, _P, c_longlong, c_int, _P, _P]),
     "pfb_norm_diff": (c_int, [_P, _P, c_longlong, c_int, _P, _P]),
     "pfb_pd_primal": (c_int, [_P, _P, _P, _P, _P, c_double, c_int, c_int, c_longlong, c_int, _P, _P]),
+    "pfb_pd_primal_lin": (c_int, [_P, _P, _P, _P, _P, _P, c_double, c_int, c_int, c_longlong, c_int, _P, _P]),
     "pfb_pcg_update": (c_int, [_P, _P, _P, _P, _P, _P, c_double, c_double, c_longlong, c_int, _P, _P]),
     "pfb_psi_plan_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_int, POINTER(c_int), c_int, c_int]),
     "pfb_psi_plan_destroy": (c_int, [_P]),

@@ -20,6 +20,7 @@
 // HBM traffic per band: x + out + psfhat^T + 4 x (nx x nyo2 complex) instead
 // of the reference's ~5 passes over the 4x larger padded arrays.
 #include "hess_fast.cuh"
+#include "hess_mixed.cuh"
 #include <cmath>
 #include <vector>
 
@@ -206,6 +207,11 @@ struct pfb_hess_plan {
     void *modg;              // exp(-2 pi i n / nxp), n = 0..H-1
     int *ctr;                // work counters of the three persistent kernels (ItemQueue)
     int dyn;                 // hand items out dynamically (see pfb_hess_set_dynamic)
+    // mixed-radix path (hess_mixed.cuh): padded sizes that are not powers of two
+    int mixed, split, Lrow;  // split: even/odd pruned column pass (nxp = 2H, nx <= H)
+    pfb::MxDesc mrow, mcol;
+    void *mtwM, *mtwC, *mroots;   // length-M / length-(H or nxp) twiddle tables, odd-radix roots
+    int deint;               // psfT rows stored [even | odd] per column
 };
 
 namespace pfb {
@@ -234,7 +240,7 @@ static int hess_set_psf_t(pfb_hess_plan *p, const void *psfhat, cudaStream_t st)
     dim3 grid(cdiv(h.nyo2, 32), cdiv(h.nxp, 32), h.nband), block(32, 8);
     T scale = (T)(1.0 / ((double)h.nxp * (double)h.nyp));
     launch(&k_psfhat_prepare<T>, grid, block, 0, st, (const Cx<T> *)psfhat, (Cx<T> *)p->psfT,
-           h.nxp, h.nyo2, scale, p->fast);
+           h.nxp, h.nyo2, scale, p->deint);
     PFB_CHECK_LAUNCH();
     p->have_psf = 1;
     return PFB_OK;
@@ -359,6 +365,34 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
     ep.wsum = (T)wsum;
     ep.sigmainv = (T)sigmainv;
     ep.has_wsum = has_wsum;
+    if (p->mixed) {
+        HessDims h = h0;
+        h.R = p->Lrow;
+        const size_t cs = sizeof(Cx<T>);
+        const size_t smr = mx_smem_bytes(h.M, h.R, cs), smc = mx_smem_bytes(p->mcol.N, 1, cs);
+        auto nthr = [](long work) { return work >= 2048 ? 512 : work >= 512 ? 256 : 128; };
+        const int tr = nthr((long)h.M * h.R / 4), tc = nthr(p->mcol.N / 4);
+        const dim3 grow(cdiv(h.nx, h.R), h.nband), gcol(h.nyo2, h.nband);
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_fwd<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
+        launch(&k_hessm_rows_fwd<T>, grow, dim3(tr), smr, st, x, beam_in, S, (const Cx<T> *)p->mtwM,
+               (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h);
+        PFB_CHECK_LAUNCH();
+        if (p->split) {
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_cols<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));
+            launch(&k_hessm_cols<T, true>, gcol, dim3(tc), smc, st, S, (const Cx<T> *)p->psfT,
+                   (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, p->mcol, h);
+        } else {
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_cols<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));
+            launch(&k_hessm_cols<T, false>, gcol, dim3(tc), smc, st, S, (const Cx<T> *)p->psfT,
+                   (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, p->mcol, h);
+        }
+        PFB_CHECK_LAUNCH();
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_inv<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
+        launch(&k_hessm_rows_inv<T>, grow, dim3(tr), smr, st, (const Cx<T> *)S, out, (const Cx<T> *)p->mtwM,
+               (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h, ep);
+        PFB_CHECK_LAUNCH();
+        return PFB_OK;
+    }
     if (p->fast && p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
     if (fast_rows) {
         if (int rc = fast_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
@@ -400,6 +434,70 @@ static int lines_per_cta(int NT, int N, size_t csize, int want) {
     return r;
 }
 
+// Plan of the mixed-radix path (hess_mixed.cuh) for padded sizes the power-of-two
+// kernels do not take.
+static int hess_plan_create_mixed(pfb_hess_plan **out, int nband, int nx, int ny, int nxp, int nyp,
+                                  int dtype) {
+    const size_t cs = 2 * dtype_size(dtype);
+    const int M = nyp / 2, H = nxp / 2;
+    const bool split = (nxp % 2 == 0) && nx <= H;
+    const int Nc = split ? H : nxp;
+    MxDesc mrow, mcol;
+    if (nyp % 2 || M < 1)
+        return fail(PFB_ERR_FFT_SIZE, "padded size (%d,%d) unsupported: nyp (lastsize) must be even", nxp, nyp);
+    if (!mx_make_desc(M, mrow) || !mx_make_desc(Nc, mcol))
+        return fail(PFB_ERR_FFT_SIZE,
+                    "padded size (%d,%d) unsupported: nyp/2 and %s must factor into 2, 3, 5, 7, 11, 13",
+                    nxp, nyp, split ? "nxp/2" : "nxp");
+    if (mx_smem_bytes(M, 1, cs) > kMaxSmemFast || mx_smem_bytes(Nc, 1, cs) > kMaxSmemFast)
+        return fail(PFB_ERR_FFT_SIZE,
+                    "padded size (%d,%d) unsupported: two transform lines (%d / %d complex) exceed %zu KB "
+                    "of shared memory", nxp, nyp, M, Nc, kMaxSmemFast / 1024);
+    pfb_hess_plan *p = new pfb_hess_plan();
+    memset(p, 0, sizeof *p);
+    p->dtype = dtype;
+    HessDims &h = p->h;
+    h.nband = nband; h.nx = nx; h.ny = ny; h.nxp = nxp; h.nyp = nyp;
+    h.nyo2 = nyp / 2 + 1; h.M = M; h.twN = 0;
+    p->mixed = 1;
+    p->split = split ? 1 : 0;
+    p->deint = p->split;
+    p->mrow = mrow;
+    p->mcol = mcol;
+    p->nsm = kNumSM;
+    // rows per CTA: transposed scratch written in 32-byte runs when shared memory allows
+    p->Lrow = dtype == PFB_F32 ? 4 : 2;
+    while (p->Lrow > 1 && mx_smem_bytes(M, p->Lrow, cs) > kMaxSmemFast) p->Lrow >>= 1;
+    auto upload = [&](void **dst, int n, auto gen) -> bool {
+        std::vector<char> hbuf(cs * (size_t)n);
+        for (int i = 0; i < n; ++i) {
+            const long double a = gen(i);
+            const double c = (double)cosl(a), sn = (double)sinl(a);
+            if (dtype == PFB_F32) { ((float *)hbuf.data())[2 * i] = (float)c; ((float *)hbuf.data())[2 * i + 1] = (float)sn; }
+            else { ((double *)hbuf.data())[2 * i] = c; ((double *)hbuf.data())[2 * i + 1] = sn; }
+        }
+        return cudaMalloc(dst, hbuf.size()) == cudaSuccess &&
+               cudaMemcpy(*dst, hbuf.data(), hbuf.size(), cudaMemcpyHostToDevice) == cudaSuccess;
+    };
+    const long double tau = -2.0L * 3.14159265358979323846264338327950288L;
+    auto lin = [&](int N) { return [=](int i) { return tau * (long double)i / (long double)N; }; };
+    auto root = [&](int i) {
+        const int R = i < 3 ? 3 : i < 8 ? 5 : i < 15 ? 7 : i < 26 ? 11 : 13;
+        return tau * (long double)(i - mx_root_off(R)) / (long double)R;
+    };
+    const size_t sS = cs * (size_t)nband * h.nyo2 * nx, sP = cs * (size_t)nband * h.nyo2 * nxp;
+    bool good = upload(&p->mtwM, M, lin(M)) && upload(&p->mtwC, Nc, lin(Nc)) &&
+                upload(&p->twr, M + 1, lin(nyp)) && upload(&p->modg, std::max(H, 1), lin(nxp)) &&
+                upload(&p->mroots, kMxRoots, root) &&
+                cudaMalloc(&p->S, sS) == cudaSuccess && cudaMalloc(&p->psfT, sP) == cudaSuccess;
+    if (!good) {
+        pfb_hess_plan_destroy(p);
+        return fail(PFB_ERR_ALLOC, "hessian plan (mixed radix) allocation failed (%zu + %zu bytes)", sS, sP);
+    }
+    *out = p;
+    return PFB_OK;
+}
+
 }  // namespace pfb
 
 using namespace pfb;
@@ -416,11 +514,7 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
     bool ok = (nyp % 2 == 0) && M >= 16 && !(M & (M - 1)) && nxp >= 16 && !(nxp & (nxp - 1)) &&
               M / 16 <= 1024 && nxp / 16 <= 1024 &&
               cs * fft_smem_elems(M) <= kMaxSmem && cs * fft_smem_elems(nxp) <= kMaxSmem;
-    if (!ok)
-        return fail(PFB_ERR_FFT_SIZE,
-                    "padded size (%d,%d) unsupported: need powers of two, nxp in [16,16384], "
-                    "nyp in [32,32768] and one line within %zu KB of shared memory",
-                    nxp, nyp, kMaxSmem / 1024);
+    if (!ok) return hess_plan_create_mixed(out, nband, nx, ny, nxp, nyp, dtype);
     pfb_hess_plan *p = new pfb_hess_plan();
     memset(p, 0, sizeof *p);
     p->dtype = dtype;
@@ -501,6 +595,7 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
             }
         }
         p->fast = fast ? 1 : 0;
+        p->deint = p->fast;
         // Dynamic distribution costs ~5 % when the GPU is otherwise idle (measured on the
         // column pass) and wins when a concurrent kernel holds SMs (NCCL all-reduce of
         // the band-sharded solver): off by default, the sharded solver turns it on.
@@ -517,7 +612,12 @@ int pfb_hess_plan_destroy(pfb_hess_plan *p) {
     if (p->twr) cudaFree(p->twr);
     if (p->modg) cudaFree(p->modg);
     if (p->ctr) cudaFree(p->ctr);
-    cudaFree(p->tw); cudaFree(p->S); cudaFree(p->psfT);
+    if (p->mtwM) cudaFree(p->mtwM);
+    if (p->mtwC) cudaFree(p->mtwC);
+    if (p->mroots) cudaFree(p->mroots);
+    if (p->tw) cudaFree(p->tw);
+    if (p->S) cudaFree(p->S);
+    if (p->psfT) cudaFree(p->psfT);
     delete p;
     return PFB_OK;
 }

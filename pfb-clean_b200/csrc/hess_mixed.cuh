@@ -1,0 +1,270 @@
+// Mixed-radix path of the PSF Hessian: padded sizes that are not powers of two.
+//
+// The reference pads to ducc0 `good_size` lengths made even
+// (pfb/workers/grid.py:276-284): 2^a 3^b 5^c 7^d 11^e, e.g. 20480 = 2^12 * 5 for
+// the 10240^2 cube of BASELINE config 5, or 12000 for a 6000^2 image.  Same
+// three passes and the same pruned, transposed scratch S[band][k][row] as
+// hess.cu; the transform itself is a shared-memory Stockham FFT with a run-time
+// radix list (8, 4, 2, 3, 5, 7, 11, 13), ping-ponging between two line buffers:
+//     butterfly j in [0, N/R):  k = j mod Ns
+//     in : u[r] = src[j + r*N/R] * w^(r*k),   w = exp(-/+ 2 pi i / (Ns*R))
+//     out: dst[(j-k)*R + k + r*Ns] = DFT_R(u)[r]
+// Twiddles come from a length-N table exp(-2 pi i m / N) (fp64 on the host,
+// rounded once); the odd radices use a direct O(R^2) DFT on a table of R-th
+// roots held in shared memory.
+//
+//  pass A  k_hessm_rows_fwd : L rows per CTA, real row packed as M = nyp/2
+//          complex, FFT, real-FFT post-processing, transposed store.
+//  pass B  k_hessm_cols     : one column per CTA.  SPLIT (nxp = 2H, nx <= H): the
+//          length-2H pair is replaced by two length-H pairs on the even / odd
+//          spectrum exactly as in hess_fast.cuh, run one after the other on the
+//          same two buffers (the even result is parked in the S line, which is
+//          dead once the odd input has been formed).  FULL otherwise.
+//  pass C  k_hessm_rows_inv : mirror of pass A with the epilogue fused.
+//
+// Limits: two lines of the transform length must fit in shared memory
+// (fp32: nyp, nxp(split) <= 28672; fp64: 14336).
+#pragma once
+#include "hess_fast.cuh"
+
+namespace pfb {
+
+struct MxDesc {
+    int N, nstage;
+    int radix[24];
+};
+
+// offsets of the R-th root tables inside the `roots` array
+__host__ __device__ constexpr int mx_root_off(int R) {
+    return R == 3 ? 0 : R == 5 ? 3 : R == 7 ? 8 : R == 11 ? 15 : 26;   // 13 -> 26
+}
+static const int kMxRoots = 39;
+
+// host: radix list for N (true if N is 13-smooth)
+static inline bool mx_make_desc(int N, MxDesc &d) {
+    d.N = N;
+    d.nstage = 0;
+    int rem = N;
+    if (N < 1) return false;
+    while (rem % 8 == 0 && d.nstage < 24) { d.radix[d.nstage++] = 8; rem /= 8; }
+    if (rem % 4 == 0) { d.radix[d.nstage++] = 4; rem /= 4; }
+    if (rem % 2 == 0) { d.radix[d.nstage++] = 2; rem /= 2; }
+    const int odd[5] = {3, 5, 7, 11, 13};
+    for (int q = 0; q < 5; ++q)
+        while (rem % odd[q] == 0 && d.nstage < 24) { d.radix[d.nstage++] = odd[q]; rem /= odd[q]; }
+    return rem == 1;
+}
+
+template <class T, int R, int DIR> struct MxDft {
+    // direct DFT of odd prime length R; rt[m] = exp(-2 pi i m / R)
+    static __device__ __forceinline__ void run(Cx<T> (&u)[R], const Cx<T> *rt) {
+        Cx<T> w[R];
+#pragma unroll
+        for (int m = 0; m < R; ++m) w[m] = twd<T, DIR>(rt[mx_root_off(R) + m]);
+        Cx<T> o[R];
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            Cx<T> acc = u[0];
+#pragma unroll
+            for (int r = 1; r < R; ++r) acc = acc + cmul(u[r], w[(q * r) % R]);
+            o[q] = acc;
+        }
+#pragma unroll
+        for (int q = 0; q < R; ++q) u[q] = o[q];
+    }
+};
+template <class T, int DIR> struct MxDft<T, 2, DIR> {
+    static __device__ __forceinline__ void run(Cx<T> (&u)[2], const Cx<T> *) { Dft<T, 2, DIR>::run(u); }
+};
+template <class T, int DIR> struct MxDft<T, 4, DIR> {
+    static __device__ __forceinline__ void run(Cx<T> (&u)[4], const Cx<T> *) { Dft<T, 4, DIR>::run(u); }
+};
+template <class T, int DIR> struct MxDft<T, 8, DIR> {
+    static __device__ __forceinline__ void run(Cx<T> (&u)[8], const Cx<T> *) { Dft<T, 8, DIR>::run(u); }
+};
+
+// one radix-R stage over L lines of length N (line l at src + l*N)
+template <class T, int R, int DIR>
+__device__ __forceinline__ void mx_stage(const Cx<T> *src, Cx<T> *dst, int L, int N, int Ns,
+                                         const Cx<T> *__restrict__ tw, const Cx<T> *rt) {
+    const int nb = N / R;
+    const int twm = N / (Ns * R);
+    for (int i = threadIdx.x; i < nb * L; i += blockDim.x) {
+        const int l = i / nb, j = i - l * nb;
+        const int k = j % Ns;
+        const Cx<T> *s = src + (long)l * N + j;
+        Cx<T> u[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) u[r] = s[r * nb];
+        if (Ns > 1) {
+#pragma unroll
+            for (int r = 1; r < R; ++r) u[r] = cmul(u[r], twd<T, DIR>(tw[r * k * twm]));
+        }
+        MxDft<T, R, DIR>::run(u, rt);
+        Cx<T> *o = dst + (long)l * N + (j - k) * R + k;
+#pragma unroll
+        for (int r = 0; r < R; ++r) o[r * Ns] = u[r];
+    }
+}
+
+// L transforms of length d.N: data in `a` (visible to all threads on entry: the
+// caller has synchronised), scratch `b`.  Returns the buffer holding the result
+// (synchronised).  Every thread of the block must call it.
+template <class T, int DIR>
+__device__ __forceinline__ Cx<T> *mx_fft(Cx<T> *a, Cx<T> *b, int L, const MxDesc &d,
+                                         const Cx<T> *__restrict__ tw, const Cx<T> *rt) {
+    int Ns = 1;
+    for (int s = 0; s < d.nstage; ++s) {
+        const int R = d.radix[s];
+        switch (R) {
+        case 8: mx_stage<T, 8, DIR>(a, b, L, d.N, Ns, tw, rt); break;
+        case 4: mx_stage<T, 4, DIR>(a, b, L, d.N, Ns, tw, rt); break;
+        case 2: mx_stage<T, 2, DIR>(a, b, L, d.N, Ns, tw, rt); break;
+        case 3: mx_stage<T, 3, DIR>(a, b, L, d.N, Ns, tw, rt); break;
+        case 5: mx_stage<T, 5, DIR>(a, b, L, d.N, Ns, tw, rt); break;
+        case 7: mx_stage<T, 7, DIR>(a, b, L, d.N, Ns, tw, rt); break;
+        case 11: mx_stage<T, 11, DIR>(a, b, L, d.N, Ns, tw, rt); break;
+        default: mx_stage<T, 13, DIR>(a, b, L, d.N, Ns, tw, rt); break;
+        }
+        __syncthreads();
+        Cx<T> *t = a; a = b; b = t;
+        Ns *= R;
+    }
+    return a;
+}
+
+template <class T>
+__device__ __forceinline__ void mx_load_roots(Cx<T> *rt, const Cx<T> *__restrict__ roots) {
+    for (int i = threadIdx.x; i < kMxRoots; i += blockDim.x) rt[i] = roots[i];
+}
+
+// shared memory: [roots (kMxRoots, padded to 40)] [A: L*N] [B: L*N]
+static inline size_t mx_smem_bytes(int N, int L, size_t cs) { return cs * (40 + (size_t)2 * L * N); }
+
+// ------------------------------------------------------------------ pass A
+template <class T>
+__global__ void __launch_bounds__(512)
+k_hessm_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__restrict__ S,
+                 const Cx<T> *__restrict__ tw, const Cx<T> *__restrict__ twr,
+                 const Cx<T> *__restrict__ roots, MxDesc d, HessDims h) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
+    const int M = h.M, L = h.R;
+    Cx<T> *A = rt + 40, *B = A + (long)L * M;
+    const int band = blockIdx.y, row0 = blockIdx.x * L;
+    mx_load_roots(rt, roots);
+    for (int i = threadIdx.x; i < L * M; i += blockDim.x) {
+        const int l = i / M, m = i - l * M, row = row0 + l, c0 = 2 * m;
+        T a = (T)0, b = (T)0;
+        if (row < h.nx) {
+            const long ro = ((long)band * h.nx + row) * h.ny;
+            if (c0 < h.ny) { a = x[ro + c0]; if (beam) a *= beam[ro + c0]; }
+            if (c0 + 1 < h.ny) { b = x[ro + c0 + 1]; if (beam) b *= beam[ro + c0 + 1]; }
+        }
+        A[i] = cx<T>(a, b);
+    }
+    __syncthreads();
+    const Cx<T> *Z = mx_fft<T, -1>(A, B, L, d, tw, rt);
+    // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
+    for (int i = threadIdx.x; i < (M + 1) * L; i += blockDim.x) {
+        const int k = i / L, l = i - k * L;
+        const Cx<T> *z = Z + (long)l * M;
+        const Cx<T> zk = z[k == M ? 0 : k], zm = cconj(z[k == 0 ? 0 : M - k]);
+        const Cx<T> E = cx<T>((T)0.5 * (zk.x + zm.x), (T)0.5 * (zk.y + zm.y));
+        const Cx<T> D = cx<T>((T)0.5 * (zk.x - zm.x), (T)0.5 * (zk.y - zm.y));
+        const Cx<T> O = cx<T>(D.y, -D.x);
+        const Cx<T> X = E + cmul(twr[k], O);
+        if (row0 + l < h.nx) S[((long)band * h.nyo2 + k) * h.nx + row0 + l] = X;
+    }
+}
+
+// ------------------------------------------------------------------ pass B
+// SPLIT: psfT de-interleaved [even | odd] per column, modg[n] = exp(-2 pi i n / nxp)
+template <class T, bool SPLIT>
+__global__ void __launch_bounds__(512)
+k_hessm_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__ tw,
+             const Cx<T> *__restrict__ modg, const Cx<T> *__restrict__ roots, MxDesc d, HessDims h) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
+    const int N = d.N;
+    Cx<T> *A = rt + 40, *B = A + N;
+    const int band = blockIdx.y, col = blockIdx.x;
+    Cx<T> *line = S + ((long)band * h.nyo2 + col) * h.nx;
+    const Cx<T> *pl = psfT + ((long)band * h.nyo2 + col) * h.nxp;
+    mx_load_roots(rt, roots);
+    for (int n = threadIdx.x; n < N; n += blockDim.x) A[n] = n < h.nx ? line[n] : cx<T>((T)0, (T)0);
+    __syncthreads();
+    Cx<T> *c = mx_fft<T, -1>(A, B, 1, d, tw, rt);
+    Cx<T> *o = c == A ? B : A;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) c[n] = cmul(c[n], pl[n]);
+    __syncthreads();
+    Cx<T> *r = mx_fft<T, +1>(c, o, 1, d, tw, rt);
+    if (!SPLIT) {
+        for (int n = threadIdx.x; n < h.nx; n += blockDim.x) line[n] = r[n];
+        return;
+    }
+    // odd spectrum: input a[n] w^n; park the even result in the (now dead) S line
+    o = r == A ? B : A;
+    for (int n = threadIdx.x; n < N; n += blockDim.x)
+        o[n] = n < h.nx ? cmul(line[n], modg[n]) : cx<T>((T)0, (T)0);
+    __syncthreads();                              // every read of the line is done
+    for (int n = threadIdx.x; n < h.nx; n += blockDim.x) line[n] = r[n];
+    __syncthreads();
+    c = mx_fft<T, -1>(o, r, 1, d, tw, rt);
+    o = c == A ? B : A;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) c[n] = cmul(c[n], pl[N + n]);
+    __syncthreads();
+    r = mx_fft<T, +1>(c, o, 1, d, tw, rt);
+    // same thread wrote line[n] above (same index mapping): no fence needed
+    for (int n = threadIdx.x; n < h.nx; n += blockDim.x)
+        line[n] = line[n] + cmul(r[n], cconj(modg[n]));
+}
+
+// ------------------------------------------------------------------ pass C
+template <class T>
+__global__ void __launch_bounds__(512)
+k_hessm_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *__restrict__ tw,
+                 const Cx<T> *__restrict__ twr, const Cx<T> *__restrict__ roots, MxDesc d,
+                 HessDims h, Epilogue<T> ep) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
+    const int M = h.M, L = h.R;
+    Cx<T> *A = rt + 40, *B = A + (long)L * M;
+    const int band = blockIdx.y, row0 = blockIdx.x * L;
+    mx_load_roots(rt, roots);
+    // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m]), m < M
+    for (int i = threadIdx.x; i < M * L; i += blockDim.x) {
+        const int m = i / L, l = i - m * L;
+        Cx<T> xm = cx<T>((T)0, (T)0), xr = xm;
+        if (row0 + l < h.nx) {
+            const Cx<T> *col = S + (long)band * h.nyo2 * h.nx + row0 + l;
+            xm = col[(long)m * h.nx];
+            xr = cconj(col[(long)(M - m) * h.nx]);
+        }
+        const Cx<T> P = xm + xr, Q = xm - xr;
+        const Cx<T> wQ = cmul(cconj(twr[m]), Q);
+        A[(long)l * M + m] = cx<T>(P.x - wQ.y, P.y + wQ.x);
+    }
+    __syncthreads();
+    const Cx<T> *Z = mx_fft<T, +1>(A, B, L, d, tw, rt);
+    for (int i = threadIdx.x; i < L * M; i += blockDim.x) {
+        const int l = i / M, m = i - l * M, row = row0 + l, c0 = 2 * m;
+        if (row >= h.nx) continue;
+        const long ro = ((long)band * h.nx + row) * h.ny;
+        const Cx<T> z = Z[i];
+        const T val[2] = {z.x, z.y};
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int c = c0 + q;
+            if (c < h.ny) {
+                T o = val[q];
+                if (ep.beam) o *= ep.beam[ro + c];
+                if (ep.has_wsum) o /= ep.wsum;
+                if (ep.x) o += ep.x[ro + c] * ep.sigmainv;
+                out[ro + c] = o;
+            }
+        }
+    }
+}
+
+}  // namespace pfb

@@ -422,8 +422,8 @@ k_norm_diff(const T *__restrict__ x, const T *__restrict__ xp, long n, double *p
 template <class T>
 __global__ void __launch_bounds__(256)
 k_pd_primal(T *x, const T *__restrict__ xp, const T *__restrict__ xout,
-            const T *__restrict__ conv, const T *__restrict__ data, T tau,
-            int positivity, int nband, long npix, double *part) {
+            const T *__restrict__ wprev, const T *__restrict__ conv, const T *__restrict__ data,
+            T tau, int positivity, int nband, long npix, double *part) {
     double acc[2] = {0.0, 0.0};
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < npix;
          i += (long)gridDim.x * blockDim.x) {
@@ -432,6 +432,7 @@ k_pd_primal(T *x, const T *__restrict__ xp, const T *__restrict__ xout,
             for (int b = 0; b < nband; ++b) {
                 long k = b * npix + i;
                 T g = xout[k];
+                if (wprev) g = (T)2 * g - wprev[k];
                 if (conv) {
                     T gr = conv[k];
                     if (data) gr = gr - data[k];
@@ -463,19 +464,21 @@ k_pd_primal(T *x, const T *__restrict__ xp, const T *__restrict__ xout,
 template <class T, int V>
 __global__ void __launch_bounds__(256)
 k_pd_primal_vec(T *x, const T *__restrict__ xp, const T *__restrict__ xout,
-                const T *__restrict__ conv, const T *__restrict__ data, T tau,
-                int positivity, long n, double *part) {
+                const T *__restrict__ wprev, const T *__restrict__ conv,
+                const T *__restrict__ data, T tau, int positivity, long n, double *part) {
     double acc[2] = {0.0, 0.0};
     long nv = n / V;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long)gridDim.x * blockDim.x) {
         long k = i * V;
-        Pack<T, V> g = ld<T, V>(xout + k), p = ld<T, V>(xp + k), c, d, o;
+        Pack<T, V> g = ld<T, V>(xout + k), p = ld<T, V>(xp + k), c, d, o, wq;
+        if (wprev) wq = ld<T, V>(wprev + k);
         if (conv) c = ld<T, V>(conv + k);
         if (data) d = ld<T, V>(data + k);
 #pragma unroll
         for (int e = 0; e < V; ++e) {
             T ge = g.v[e];
+            if (wprev) ge = (T)2 * ge - wq.v[e];
             if (conv) {
                 T gr = c.v[e];
                 if (data) gr = gr - d.v[e];
@@ -802,28 +805,42 @@ int pfb_norm_diff(const void *x, const void *xp, long long n, int dtype, double 
     return finish_reduce(2, out2, st);
 }
 
-int pfb_pd_primal(void *x, const void *xp, const void *xout, const void *conv,
-                  const void *data, double tau, int positivity, int nband, long long npix,
-                  int dtype, double *out2, void *stream) {
+static int pd_primal_impl(void *x, const void *xp, const void *xout, const void *wprev,
+                          const void *conv, const void *data, double tau, int positivity,
+                          int nband, long long npix, int dtype, double *out2, void *stream) {
     if (!x || !xp || !xout || !out2 || nband < 1 || npix < 0 || (data && !conv))
         return fail(PFB_ERR_BAD_ARG, "pfb_pd_primal: bad argument");
     int rc = ensure_part();
     if (rc) return rc;
     cudaStream_t st = as_stream(stream);
     long ntot = (long)nband * (long)npix;
-    bool al = (((uintptr_t)x | (uintptr_t)xp | (uintptr_t)xout | (uintptr_t)conv | (uintptr_t)data) & 15) == 0;
+    bool al = (((uintptr_t)x | (uintptr_t)xp | (uintptr_t)xout | (uintptr_t)wprev | (uintptr_t)conv |
+                (uintptr_t)data) & 15) == 0;
     if (positivity != 2 && al && dtype == PFB_F32 && ntot % 4 == 0)
-        launch(&k_pd_primal_vec<float, 4>, dim3(kRedBlocks), dim3(256), 0, st, (float *)x, (const float *)xp, (const float *)xout, (const float *)conv, (const float *)data, (float)tau, positivity, ntot, g_part);
+        launch(&k_pd_primal_vec<float, 4>, dim3(kRedBlocks), dim3(256), 0, st, (float *)x, (const float *)xp, (const float *)xout, (const float *)wprev, (const float *)conv, (const float *)data, (float)tau, positivity, ntot, g_part);
     else if (positivity != 2 && al && dtype == PFB_F64 && ntot % 2 == 0)
-        launch(&k_pd_primal_vec<double, 2>, dim3(kRedBlocks), dim3(256), 0, st, (double *)x, (const double *)xp, (const double *)xout, (const double *)conv, (const double *)data, tau, positivity, ntot, g_part);
+        launch(&k_pd_primal_vec<double, 2>, dim3(kRedBlocks), dim3(256), 0, st, (double *)x, (const double *)xp, (const double *)xout, (const double *)wprev, (const double *)conv, (const double *)data, tau, positivity, ntot, g_part);
     else if (dtype == PFB_F32)
-        launch(&k_pd_primal<float>, dim3(kRedBlocks), dim3(256), 0, st, (float *)x, (const float *)xp, (const float *)xout, (const float *)conv, (const float *)data, (float)tau, positivity, nband, (long)npix, g_part);
+        launch(&k_pd_primal<float>, dim3(kRedBlocks), dim3(256), 0, st, (float *)x, (const float *)xp, (const float *)xout, (const float *)wprev, (const float *)conv, (const float *)data, (float)tau, positivity, nband, (long)npix, g_part);
     else if (dtype == PFB_F64)
-        launch(&k_pd_primal<double>, dim3(kRedBlocks), dim3(256), 0, st, (double *)x, (const double *)xp, (const double *)xout, (const double *)conv, (const double *)data, tau, positivity, nband, (long)npix, g_part);
+        launch(&k_pd_primal<double>, dim3(kRedBlocks), dim3(256), 0, st, (double *)x, (const double *)xp, (const double *)xout, (const double *)wprev, (const double *)conv, (const double *)data, tau, positivity, nband, (long)npix, g_part);
     else
         return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
     PFB_CHECK_LAUNCH();
     return finish_reduce(2, out2, st);
+}
+
+int pfb_pd_primal(void *x, const void *xp, const void *xout, const void *conv,
+                  const void *data, double tau, int positivity, int nband, long long npix,
+                  int dtype, double *out2, void *stream) {
+    return pd_primal_impl(x, xp, xout, nullptr, conv, data, tau, positivity, nband, npix, dtype, out2, stream);
+}
+
+int pfb_pd_primal_lin(void *x, const void *xp, const void *w, const void *wprev, const void *conv,
+                      const void *data, double tau, int positivity, int nband, long long npix,
+                      int dtype, double *out2, void *stream) {
+    if (!wprev) return fail(PFB_ERR_BAD_ARG, "pfb_pd_primal_lin: wprev is null");
+    return pd_primal_impl(x, xp, w, wprev, conv, data, tau, positivity, nband, npix, dtype, out2, stream);
 }
 
 int pfb_pcg_update(void *x, void *r, const void *xp, const void *rp, const void *p,

@@ -30,9 +30,15 @@ def pcg_direction(p, r, beta, minv, out):
     return out
 
 
-def pd_primal(x, xp, xout, conv, data, tau, positivity, out):
+def pd_primal(x, xp, xout, conv, data, tau, positivity, out, wprev=None):
+    """wprev given: xout is w = Psi(v) and the kernel forms 2 w - wprev itself."""
     nband = x.shape[0]
     npix = x.numel() // nband
+    if wprev is not None:
+        _lib.check(_lib.lib().pfb_pd_primal_lin(_dev.ptr(x), _dev.ptr(xp), _dev.ptr(xout), _dev.ptr(wprev),
+                                                _dev.ptr(conv), _dev.ptr(data), float(tau), int(positivity),
+                                                nband, npix, _dev.dcode(x), _dev.ptr(out), _dev.stream()))
+        return out
     _lib.check(_lib.lib().pfb_pd_primal(_dev.ptr(x), _dev.ptr(xp), _dev.ptr(xout), _dev.ptr(conv),
                                         _dev.ptr(data), float(tau), int(positivity), nband, npix,
                                         _dev.dcode(x), _dev.ptr(out), _dev.stream()))

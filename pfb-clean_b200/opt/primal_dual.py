@@ -220,6 +220,14 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         host_terms = torch.empty(2, dtype=torch.float64, pin_memory=True)
         ev = torch.cuda.Event()
     have_dot = False            # Psi(xprev) -> vcur was already issued by the previous iteration
+    # Synthesis by linearity: Psi(2 v_k - v_{k-1}) = 2 w_k - w_{k-1} with w_k = Psi(v_k).  The
+    # dual kernel then writes v only (no 2v - vp: one pass over the coefficient cube less per
+    # iteration) and the primal kernel forms 2 w_k - w_{k-1} from two image-sized arrays.
+    lin = nat and not os.environ.get("PFB_PD_NOLIN")
+    wprev = None
+    if lin:
+        wprev = torch.empty_like(xa)
+        P.hdot_nat(vprev, wprev)            # w_{-1} = Psi(v_0)
 
     eps = 1.0
     numreweight = 0
@@ -232,7 +240,7 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             return _dev.to_dev(grad.psf_convolve(xprev) if fused_grad else grad(xprev))
         g = None
         if nat:
-            # the dual kernel leaves 2v - vp in the (dead) vp buffer: one coefficient
+            # not lin: the dual kernel leaves 2v - vp in the (dead) vp buffer: one coefficient
             # set for the synthesis to read, which is instruction-issue bound
             if not have_dot:
                 P.dot_nat(xprev, vcur)
@@ -241,10 +249,10 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
                 # the PSF convolution hides the all-reduce of the band sums
                 works = _dual_begin(vprev, vcur, sigma, n, bsum)
                 g = gradient()
-                _dual_end(works, vprev, vcur, lam, sigma, w, n, bsum)
+                _dual_end(works, vprev, vcur, lam, sigma, w, n, bsum, write_u=not lin)
             else:
-                _dual_step(vprev, vcur, lam, sigma, w, n, bsum)
-            P.hdot_nat(vprev, xout)
+                _dual_step(vprev, vcur, lam, sigma, w, n, bsum, write_u=not lin)
+            P.hdot_nat(vcur if lin else vprev, xout)
         elif fast:   # `vp = 2v - vp` (primal_dual.py:137) is fused into the synthesis loader
             psi(xprev, vcur)
             _dual_step(vprev, vcur, lam, sigma, w, n, bsum, write_u=False)
@@ -257,7 +265,9 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             g = gradient()
         if g.dtype != xa.dtype:
             g = g.to(xa.dtype)
-        _vec.pd_primal(xcur, xprev, xout, g, data, tau, pos_kernel, terms)
+        _vec.pd_primal(xcur, xprev, xout, g, data, tau, pos_kernel, terms, wprev=wprev)
+        if lin:
+            xout, wprev = wprev, xout
         if pos_kernel != positivity:   # positivity 2 across band-sharded ranks
             neg = (xcur <= 0).any(dim=0).to(torch.int32)
             parallel.allreduce_max(neg)

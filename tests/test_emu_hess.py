@@ -89,7 +89,39 @@ def test_hess_delta_kat():
     assert np.abs(out[0] - psf[0, nxp // 2 + ii - p, nyp // 2 + jj - q]).max() < 1e-13
 
 
+# padded sizes that are not powers of two (ducc0 good_size lengths made even,
+# pfb/workers/grid.py:276-284): mixed-radix path, split and full column pass
+MIXED = [(8, 8, 24, 32), (8, 8, 16, 16), (5, 6, 10, 12), (12, 14, 24, 28), (9, 20, 30, 42),
+         (20, 18, 44, 36), (13, 10, 26, 52), (30, 50, 60, 100), (40, 24, 48, 50),   # nx > nxp/2: full
+         (7, 9, 15, 18), (6, 4, 21, 10),                                           # odd nxp: full
+         (48, 70, 96, 140), (75, 66, 150, 132), (10, 600, 20, 1200), (350, 8, 700, 16)]
+
+
+@pmp("dtype", [np.float32, np.float64])
+@pmp("nx,ny,nxp,nyp", MIXED)
+def test_hess_mixed_radix_oracle(dtype, nx, ny, nxp, nyp):
+    rng = np.random.default_rng(13)
+    nband = 2
+    cdt = np.complex64 if dtype == np.float32 else np.complex128
+    psf = rng.standard_normal((nband, nxp, nyp))
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2)).astype(cdt)
+    x = rng.standard_normal((nband, nx, ny)).astype(dtype)
+    beam = (0.5 + rng.random(x.shape)).astype(dtype)
+    H = EmuHess(nband, nx, ny, nxp, nyp, dtype)
+    assert H.rc == 0
+    H.set_psfhat(psfhat)
+    xpad, xhat = np.empty((nband, nxp, nyp), dtype), np.empty(psfhat.shape, cdt)
+    xout = np.empty(x.shape, dtype)
+    tol = 1e-13 if dtype == np.float64 else 1e-6
+    exp = ref.psf_convolve_cube(xpad, xhat, xout, psfhat, nyp, x).copy()
+    assert rel(H.apply(x), exp) < tol
+    exp2 = ref.hessian_psf_cube(xpad, xhat, xout, beam, psfhat, nyp, x, sigmainv=0.25, wsum=3.5)
+    assert rel(H.apply(x, beam, 1, 0.25, 3.5), exp2) < tol
+
+
 def test_hess_plan_errors():
-    assert EmuHess(1, 8, 8, 24, 32, np.float64).rc == 4      # not a power of two
-    assert EmuHess(1, 8, 8, 16, 16, np.float64).rc == 4      # nyp/2 < 16
+    assert EmuHess(1, 8, 8, 24, 33, np.float64).rc == 4      # odd lastsize
+    assert EmuHess(1, 8, 8, 34, 32, np.float64).rc == 4      # nxp/2 = 17: prime factor > 13
+    assert EmuHess(1, 8, 8, 32, 76, np.float64).rc == 4      # nyp/2 = 38 = 2 * 19
+    assert EmuHess(1, 8, 8, 32, 2 * 15000, np.float64).rc == 4   # two lines beyond shared memory
     assert EmuHess(1, 40, 8, 32, 32, np.float64).rc == 1     # image larger than PSF

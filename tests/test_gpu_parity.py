@@ -144,6 +144,52 @@ def test_hess_vs_oracle(dtype, nx, ny, nxp, nyp):
     assert rel(got2, exp2) < TOL[dtype]
 
 
+@pmp("dtype", [np.float32, np.float64])
+@pmp("nx,ny,nxp,nyp", [(8, 8, 24, 32), (9, 20, 30, 42), (20, 18, 44, 36), (13, 10, 26, 52),
+                        (40, 24, 48, 50), (7, 9, 15, 18), (75, 66, 150, 132), (10, 600, 20, 1200),
+                        (350, 8, 700, 16), (600, 540, 1200, 1080), (1500, 1350, 3000, 2700),
+                        (900, 1000, 1344, 2200)])
+def test_hess_mixed_radix_vs_oracle(dtype, nx, ny, nxp, nyp):
+    """Padded sizes that are not powers of two (ducc0 good_size lengths,
+    pfb/workers/grid.py:276-284): hess_mixed.cuh, split and full column pass."""
+    from pfb_b200.operators.psf import psf_convolve_cube
+    from pfb_b200.operators.hessian import hessian_psf_cube
+    rng = np.random.default_rng(17)
+    nband = 2
+    cdt = np.complex64 if dtype == np.float32 else np.complex128
+    psf = rng.standard_normal((nband, nxp, nyp))
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2)).astype(cdt)
+    x = rng.standard_normal((nband, nx, ny)).astype(dtype)
+    beam = (0.5 + rng.random(x.shape)).astype(dtype)
+    xpad, xhat = np.empty((nband, nxp, nyp), dtype), np.empty(psfhat.shape, cdt)
+    xo = np.empty(x.shape, dtype)
+    exp = ref.psf_convolve_cube(xpad, xhat, xo, psfhat, nyp, x).copy()
+    out = np.full(x.shape, np.nan, dtype)
+    assert psf_convolve_cube(None, None, out, psfhat, nyp, x) is out
+    assert rel(out, exp) < TOL[dtype]
+    exp2 = ref.hessian_psf_cube(xpad, xhat, xo, beam, psfhat, nyp, x, sigmainv=0.25, wsum=3.5)
+    got2 = hessian_psf_cube(None, None, None, beam, psfhat, nyp, x, sigmainv=0.25, wsum=3.5)
+    assert rel(got2, exp2) < TOL[dtype]
+
+
+@pmp("nx,nxp", [(6000, 12000), (10240, 20480)])
+def test_hess_mixed_radix_delta_kat_full_size(nx, nxp):
+    """One band at 6000^2 / 12000^2 (2^5 3 5^3) and at BASELINE config 5's 10240^2 /
+    20480^2 (2^12 5): x = delta at (p,q) => out = shifted PSF crop."""
+    from pfb_b200.operators.psf import psf_convolve_cube
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(7)
+    psf = torch.randn((1, nxp, nxp), generator=g, dtype=torch.float32, device=dev)
+    psfhat = torch.fft.rfft2(torch.fft.ifftshift(psf, dim=(1, 2)), dim=(1, 2))
+    x = torch.zeros((1, nx, nx), dtype=torch.float32, device=dev)
+    p, q = nx // 3 + 1, nx - 95
+    x[0, p, q] = 1.0
+    out = torch.empty_like(x)
+    psf_convolve_cube(None, None, out, psfhat, nxp, x)
+    exp = psf[0, nxp // 2 - p: nxp // 2 - p + nx, nxp // 2 - q: nxp // 2 - q + nx]
+    assert rel(out[0], exp) < 2e-6
+
+
 def test_hess_dynamic_distribution_matches_static():
     """pfb_hess_plan_set_dynamic: same result bit for bit (items are independent)."""
     from pfb_b200.operators import psf as P
