@@ -131,6 +131,10 @@ int pfb_pcg_direction(void *p, const void *r, double beta, double minv,
  * Multi-basis wavelet dictionary, pfb/operators/psi.py:269-310 (class Psi) over
  * pfb/wavelets/wavelets.py dwt2d :174 / idwt2d :260.  basis_ids: 0 = 'self',
  * N = 'dbN' (1..5).  Coefficients are (nband, nbasis, Nymax, Nxmax).         */
+/* Daubechies db<order> (order 1..5) filter bank compiled into the kernels, as
+ * pywt.Wavelet('db<order>').filter_bank (pfb/operators/psi.py:37-41):
+ * taps[w*10 + k], w = 0 dec_lo, 1 dec_hi, 2 rec_lo, 3 rec_hi, k < 2*order (rest 0). */
+int pfb_filter_bank(int order, double *taps);
 typedef struct pfb_psi_plan pfb_psi_plan;
 /* Psi(nband, nx, ny, bases, nlevel, nthreads) + psi_band_maker
  * pfb/operators/psi.py:17-123, :270-282.  PFB_ERR_NLEVEL mirrors the

@@ -261,11 +261,10 @@ static int persistent_grid(const void *func, int threads, size_t smem, int total
 #endif
 }
 
-template <class T, int M, int RB>
-static int fast_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
+template <class T, int M, int RB, bool TWS>
+static int fast_rows_fwd_k(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st, size_t smem) {
     const HessDims &h = p->h;
-    size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
-    auto kern = p->dyn ? &k_hessf_rows_fwd<T, M, RB, true> : &k_hessf_rows_fwd<T, M, RB, false>;
+    auto kern = p->dyn ? &k_hessf_rows_fwd<T, M, RB, TWS, true> : &k_hessf_rows_fwd<T, M, RB, TWS, false>;
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int nbb = cdiv(h.nx, RB);
     int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
@@ -276,8 +275,37 @@ static int fast_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream
 }
 
 template <class T, int M, int RB>
+static int fast_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
+    const size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
+    const size_t smem_tw = smem + sizeof(Cx<T>) * (M + 1);
+    if (smem_tw <= kMaxSmemFast && !getenv("PFB_HESS_NOTWS"))
+        return fast_rows_fwd_k<T, M, RB, true>(p, x, beam, st, smem_tw);
+    return fast_rows_fwd_k<T, M, RB, false>(p, x, beam, st, smem);
+}
+
+template <class T, int M, bool TWS>
+static int fast_rows_inv2(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st, size_t smem) {
+    const HessDims &h = p->h;
+    auto kern = p->dyn ? &k_hessf_rows_inv2<T, M, TWS, true> : &k_hessf_rows_inv2<T, M, TWS, false>;
+    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int nbb = cdiv(h.nx, 4);
+    int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
+    launch(kern, dim3(grid), dim3(M / 8), smem, st, (const Cx<T> *)p->S, out, (const Cx<T> *)p->tabM,
+           (const Cx<T> *)p->twr, h, nbb, ep, p->ctr + 2);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+template <class T, int M, int RB>
 static int fast_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
     const HessDims &h = p->h;
+    // pipelined kernel (four lines: gather of the next row pair under the transforms) when it fits
+    const size_t smem4 = sizeof(Cx<T>) * ((size_t)4 * ct_stride(M) + ct_tab_size(M));
+    if (!getenv("PFB_HESS_NOPIPE") && h.nx % 2 == 0) {
+        if (smem4 + sizeof(Cx<T>) * M <= kMaxSmemFast)
+            return fast_rows_inv2<T, M, true>(p, out, ep, st, smem4 + sizeof(Cx<T>) * M);
+        if (smem4 <= kMaxSmemFast) return fast_rows_inv2<T, M, false>(p, out, ep, st, smem4);
+    }
     size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
     auto kern = p->dyn ? &k_hessf_rows_inv<T, M, RB, true> : &k_hessf_rows_inv<T, M, RB, false>;
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -77,18 +77,24 @@ template <bool DYN> struct ItemQueue {
 
 // ------------------------------------------------------------------ pass A
 // twr[k] = exp(-2 pi i k / nyp), k = 0..M
-template <class T, int M, int RB, bool DYN>
+// TWS: twr (M + 1 entries) is staged in shared memory (ncu r01k: 13 % of the samples of
+// this kernel sat on the global twr[k] load of the post-processing loop).
+template <class T, int M, int RB, bool TWS, bool DYN>
 __global__ void __launch_bounds__(M / 8, 1)
 k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__restrict__ S,
-                 const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twr, HessDims h,
+                 const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twrg, HessDims h,
                  int nbatch_band, int *counter) {
     PFB_DYN_SMEM(raw);
     Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
     Cx<T> *tab = bufs + RB * ct_stride(M);
+    Cx<T> *tws = tab + ct_tab_size(M);
     constexpr int NT = M / 16;
     const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
     const GroupBar bar{1 + g, NT};
     ct_load_table<T, M>(tab, tabg);
+    if (TWS)
+        for (int i = threadIdx.x; i <= M; i += blockDim.x) tws[i] = twrg[i];
+    const Cx<T> *twr = TWS ? tws : twrg;
     __syncthreads();
     typedef typename V2<T>::type T2;
     const int total = nbatch_band * h.nband;
@@ -337,6 +343,114 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
         }
         batch = q.publish();
     }
+}
+
+// Pass C, pipelined: the CTA owns four lines; while its two transform groups work
+// on one row pair (lines 2c, 2c+1: pre-processing, inverse FFT, crop + epilogue
+// straight from registers) the transposed gather of the NEXT row pair streams into
+// the other two lines with cp.async, so the gather latency (one CTA of 16 warps per
+// SM cannot hide it by occupancy: ncu r01k, 32 % of the samples of k_hessf_rows_inv
+// on the gather's long-scoreboard stalls) is off the critical path.  Adjacent lanes
+// copy the two rows of a pair (one 16-byte run per k); the other half of each
+// 32-byte sector is fetched by the next pair, one transform later (L2 hit).
+// TWS: twr (M entries) is staged in shared memory.
+template <class T, int M, bool TWS, bool DYN>
+__global__ void __launch_bounds__(M / 8, 1)
+k_hessf_rows_inv2(const Cx<T> *__restrict__ S, T *__restrict__ out,
+                  const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twrg, HessDims h,
+                  int nbatch_band, Epilogue<T> ep, int *counter) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
+    Cx<T> *tab = bufs + 4 * ct_stride(M);
+    Cx<T> *tws = tab + ct_tab_size(M);
+    constexpr int NT = M / 16;
+    const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
+    const GroupBar bar{1 + g, NT};
+    ct_load_table<T, M>(tab, tabg);
+    if (TWS)
+        for (int i = threadIdx.x; i < M; i += blockDim.x) tws[i] = twrg[i];
+    const Cx<T> *twr = TWS ? tws : twrg;
+    typedef typename V2<T>::type T2;
+    const int total = nbatch_band * h.nband;
+    // rows (row0 + 2 ph, row0 + 2 ph + 1) of item `batch` -> the two lines 2 c, 2 c + 1 used as
+    // ONE interleaved stage [k][2] (16-byte copies; needs nx even for the alignment)
+    constexpr int PP = 2 * (int)sizeof(Cx<T>) / 16;       // 16-byte pieces per k (1 or 2)
+    constexpr int EP = 16 / (int)sizeof(Cx<T>);           // complex values per piece (2 or 1)
+    auto gather = [&](const int batch, const int ph, const int c) {
+        if (batch < total) {
+            const int band = batch / nbatch_band;
+            const int row0 = (batch - band * nbatch_band) * 4 + 2 * ph;
+            const Cx<T> *src = S + (long)band * h.nyo2 * h.nx + row0;
+            Cx<T> *dst = bufs + 2 * c * ct_stride(M);
+            for (int i = threadIdx.x; i < PP * (M + 1); i += 2 * NT) {
+                const int k = i / PP, part = i - k * PP;
+                int left = (h.nx - row0 - part * EP) * (int)sizeof(Cx<T>);
+                left = left < 0 ? 0 : (left > 16 ? 16 : left);
+                cp_async_zfill<16>(dst + 2 * k + part * EP, left ? src + (long)k * h.nx + part * EP : S, left);
+            }
+        }
+        cp_async_commit();
+    };
+    ItemQueue<DYN> q;
+    q.init(counter);
+    q.request();
+    int batch = q.publish();
+    q.request();
+    int nxt = q.publish();
+    gather(batch, 0, 0);
+    int c = 0;
+    while (batch < total) {
+        q.request();                             // the item after `nxt`
+        const int band = batch / nbatch_band;
+        const int row0 = (batch - band * nbatch_band) * 4;
+#pragma unroll 1
+        for (int ph = 0; ph < 2; ++ph) {
+            cp_async_wait<0>();
+            __syncthreads();                     // pair (batch, ph) has landed; the other two lines are free
+            if (ph == 0) gather(batch, 1, c ^ 1);
+            else gather(nxt, 0, c ^ 1);
+            const int row = row0 + 2 * ph + g;
+            Cx<T> *buf = bufs + (2 * c + g) * ct_stride(M);
+            const Cx<T> *stg = bufs + 2 * c * ct_stride(M) + g;
+            // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m])
+            Cx<T> v[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                const int m = t + e * NT;
+                const Cx<T> xm = stg[2 * m], xr = cconj(stg[2 * (M - m)]);
+                const Cx<T> A = xm + xr, B = xm - xr;
+                const Cx<T> wB = cmul(cconj(twr[m]), B);
+                v[e] = cx<T>(A.x - wB.y, A.y + wB.x);
+            }
+            __syncthreads();                     // both rows are in registers: the stage becomes the exchange lines
+            ct_fft<T, M, +1>(v, t, buf, tab, bar);
+            if (row < h.nx) {
+                const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const int c0 = 2 * (t + e * NT);
+                    if (c0 < h.ny) {
+                        T2 o;
+                        o.x = v[e].x; o.y = v[e].y;
+                        if (ep.beam) {
+                            T2 bm = *reinterpret_cast<const T2 *>(ep.beam + ro + c0);
+                            o.x *= bm.x; o.y *= bm.y;
+                        }
+                        if (ep.has_wsum) { o.x /= ep.wsum; o.y /= ep.wsum; }
+                        if (ep.x) {
+                            T2 xx = *reinterpret_cast<const T2 *>(ep.x + ro + c0);
+                            o.x += xx.x * ep.sigmainv; o.y += xx.y * ep.sigmainv;
+                        }
+                        *reinterpret_cast<T2 *>(out + ro + c0) = o;
+                    }
+                }
+            }
+            c ^= 1;
+        }
+        batch = nxt;
+        nxt = q.publish();
+    }
+    cp_async_wait<0>();
 }
 
 }  // namespace pfb

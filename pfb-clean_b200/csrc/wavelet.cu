@@ -849,6 +849,14 @@ int pfb_psi_plan_destroy(pfb_psi_plan *p) {
     return PFB_OK;
 }
 
+int pfb_filter_bank(int order, double *taps) {
+    static const double h_taps[5][4][10] = PFB_TAPS_INIT;
+    if (order < 1 || order > 5 || !taps) return fail(PFB_ERR_BAD_ARG, "pfb_filter_bank: order must be 1..5");
+    for (int w = 0; w < 4; ++w)
+        for (int k = 0; k < 10; ++k) taps[w * 10 + k] = h_taps[order - 1][w][k];
+    return PFB_OK;
+}
+
 int pfb_psi_plan_query(const pfb_psi_plan *p, int *Nxmax, int *Nymax) {
     if (!p) return fail(PFB_ERR_BAD_ARG, "null plan");
     if (Nxmax) *Nxmax = p->Nxmax;

@@ -132,9 +132,29 @@ def _pcg_psf_impl(psfhat, b, x0, beam, lastsize, nthreads, sigmainv, tol=1e-5,
     model = torch.zeros_like(bd)
     M = ScalarPrecond(sigmainv) if sigmainv > 0 else None
     for k in range(nband):
-        A = partial(_hessian_psf_slice, None, None, None, psfd[k], beamd[k], lastsize,
+        A = partial(_hessian_psf_slice, None, None, None, psfd[k],
+                    beamd[k] if beamd is not None else None, lastsize,
                     nthreads=nthreads, sigmainv=sigmainv)
         model[k] = pcg(A, bd[k], x0d[k], M=M, tol=tol, maxit=maxit, minit=minit,
                        verbosity=verbosity, report_freq=report_freq, backtrack=backtrack,
                        _global=False)
     return _dev.like(b, model)
+
+
+def pcg_psf(psfhat, b, x0, beam, lastsize, nthreads, sigmainv, cgopts, compute=True):
+    """pfb/opt/pcg.py:310-360.  The reference wraps _pcg_psf_impl in a
+    dask.blockwise graph over band chunks; here the bands are solved one after
+    the other on the device (eagerly: `compute=False` returns the same array, not
+    a lazy graph).  beam: None, (nx, ny), (1, nx, ny) (tiled over the bands) or
+    (nband, nx, ny); anything else raises ValueError like the reference."""
+    nband = psfhat.shape[0]
+    if beam is not None:
+        bd = _dev.to_dev(beam)
+        if bd.dim() == 2:
+            bd = bd[None]
+        if bd.shape[0] == 1:
+            bd = bd.expand(nband, -1, -1).contiguous()
+        elif bd.shape[0] != nband:
+            raise ValueError('Beam has incorrect shape')
+        beam = bd
+    return _pcg_psf_impl(psfhat, b, x0, beam, lastsize, nthreads, sigmainv, **cgopts)

@@ -227,3 +227,54 @@ def test_nonzero_gap_dual(backend):
                               None, w, None, lambda z: oconv(z) - dirty, nu=len(bases), tol=0.0,
                               maxit=4)
     assert rel(x, ox) < 1e-11 and rel(v, ov) < 1e-11
+
+
+@pmp("wavelet,nx,ny,nlevel", [("db1", 32, 48, 2), ("db3", 64, 40, 2), ("db4", 128, 128, 3)])
+def test_wavelets_functional_api(backend, wavelet, nx, ny, nlevel):
+    """The reference's own wavelet test (tests/test_wavelets.py:76-82): dwt2d then
+    idwt2d through the functional signatures reconstructs the image; the
+    coefficient slab equals the oracle's Psi.dot of the same basis."""
+    from pfb_b200.wavelets import dwt2d, idwt2d, copyT, filter_bank, coeff_size, signal_size
+    from oracle import ref
+    dec_lo, dec_hi, rec_lo, rec_hi = filter_bank(wavelet)
+    F = len(dec_lo)
+    assert F == 2 * int(wavelet[2:]) and abs(np.sum(dec_lo) - np.sqrt(2)) < 1e-12
+    opsi = ref.Psi(1, nx, ny, [wavelet], nlevel)
+    Ntoty, Ntotx = opsi.Nymax, opsi.Nxmax
+    rng = np.random.default_rng(420)
+    data = rng.standard_normal((nx, ny))
+    alpha2 = np.zeros((Ntoty, Ntotx))
+    dwt2d(data, alpha2, None, None, None, None, None, None, dec_lo, dec_hi, nlevel)
+    exp = np.zeros((1, 1, Ntoty, Ntotx))
+    opsi.dot(data[None], exp)
+    assert rel(alpha2, exp[0, 0]) < 1e-13
+    xrec2 = np.zeros((nx, ny))
+    idwt2d(alpha2, xrec2, None, None, None, None, None, None, None, None, None, rec_lo, rec_hi, nlevel)
+    np.testing.assert_array_almost_equal(data, xrec2, decimal=12)
+    assert coeff_size(nx, F) == (nx + F - 1) // 2 and signal_size(coeff_size(nx, F), F) == nx + nx % 2
+    out = np.zeros((ny, nx))
+    copyT(data, out)
+    assert np.array_equal(out, data.T)
+    with pytest.raises(ValueError):
+        dwt2d(data, alpha2, None, None, None, None, None, None, dec_lo * 1.01, dec_hi, nlevel)
+
+
+def test_pcg_psf_api(backend):
+    """pcg_psf (pfb/opt/pcg.py:310-360): per-band PCG, beam None / tiled from (1, nx, ny)."""
+    from pfb_b200.opt.pcg import pcg_psf
+    from oracle import ref
+    rng = np.random.default_rng(5)
+    nband, nx, ny, nxp, nyp = 2, 16, 16, 32, 32
+    psf = np.exp(-0.5 * (((np.arange(nxp) - nxp // 2)[:, None] / 1.5) ** 2 +
+                         ((np.arange(nyp) - nyp // 2)[None, :] / 2.0) ** 2))
+    psf = np.stack([psf / psf.sum() * (1 + 0.2 * b) for b in range(nband)])
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2))
+    b = rng.standard_normal((nband, nx, ny))
+    x0 = np.zeros_like(b)
+    opts = dict(tol=0.0, maxit=4, minit=4, verbosity=0, report_freq=10, backtrack=True)
+    beam1 = 0.5 + rng.random((1, nx, ny))
+    got = pcg_psf(psfhat, b, x0, beam1, nyp, 1, 1e-2, opts)
+    exp = ref._pcg_psf_impl(psfhat, b, x0, np.tile(beam1, (nband, 1, 1)), nyp, 1, 1e-2, **opts)
+    assert rel(got, exp) < 1e-11
+    with pytest.raises(ValueError):
+        pcg_psf(psfhat, b, x0, np.ones((3, nx, ny)), nyp, 1, 1e-2, opts)
