@@ -102,6 +102,14 @@ __device__ __forceinline__ void cp_async_zfill(void *smem_dst, const void *gsrc,
         asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(sa), "l"(gsrc), "r"(src_bytes) : "memory");
 #endif
 }
+// L2 prefetch of the 128-byte line holding `p` (no register, no scoreboard)
+__device__ __forceinline__ void prefetch_l2(const void *p) {
+#ifndef PFB_EMU
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+    (void)p;
+#endif
+}
 __device__ __forceinline__ void cp_async_commit() {
 #ifndef PFB_EMU
     asm volatile("cp.async.commit_group;" ::: "memory");

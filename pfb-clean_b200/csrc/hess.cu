@@ -318,8 +318,25 @@ static int fast_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaSt
 }
 
 template <class T, int H>
+static int fast_cols1(pfb_hess_plan *p, cudaStream_t st) {
+    const HessDims &h = p->h;
+    const size_t smem = sizeof(Cx<T>) * ((size_t)2 * ct_stride(H) + ct_tab_size(H));
+    auto kern = p->dyn ? &k_hessf_cols1<T, H, true> : &k_hessf_cols1<T, H, false>;
+    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = persistent_grid((const void *)kern, H / 16, smem, h.nyo2 * h.nband, p->nsm);
+    launch(kern, dim3(grid), dim3(H / 16), smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
+           (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h, p->ctr + 1);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+template <class T, int H>
 static int fast_cols(pfb_hess_plan *p, cudaStream_t st) {
     const HessDims &h = p->h;
+    // one-group CTAs, two per SM (see k_hessf_cols1) when both fit in shared memory
+    if (2 * sizeof(Cx<T>) * ((size_t)2 * ct_stride(H) + ct_tab_size(H)) + 2048 <= 227 * 1024 &&
+        !getenv("PFB_HESS_COLS2G"))
+        return fast_cols1<T, H>(p, st);
     size_t smem = sizeof(Cx<T>) * ((size_t)2 * ct_stride(H) + ct_tab_size(H));
     // prefetching variant: 3H more complex values; S columns must be 16-byte aligned
     const size_t smem_pf = smem + sizeof(Cx<T>) * 3 * (size_t)H;
@@ -477,7 +494,8 @@ static int hess_plan_create_mixed(pfb_hess_plan **out, int nband, int nx, int ny
         return fail(PFB_ERR_FFT_SIZE,
                     "padded size (%d,%d) unsupported: nyp/2 and %s must factor into 2, 3, 5, 7, 11, 13",
                     nxp, nyp, split ? "nxp/2" : "nxp");
-    if (mx_smem_bytes(M, 1, cs) > kMaxSmemFast || mx_smem_bytes(Nc, 1, cs) > kMaxSmemFast)
+    if (mx_smem_bytes(M, 1, cs) > kMaxSmemFast || mx_smem_bytes(Nc, 1, cs) > kMaxSmemFast ||
+        mx_tw_entries(M) > kMxTwMax || mx_tw_entries(Nc) > kMxTwMax)
         return fail(PFB_ERR_FFT_SIZE,
                     "padded size (%d,%d) unsupported: two transform lines (%d / %d complex) exceed %zu KB "
                     "of shared memory", nxp, nyp, M, Nc, kMaxSmemFast / 1024);
@@ -514,7 +532,8 @@ static int hess_plan_create_mixed(pfb_hess_plan **out, int nband, int nx, int ny
         return tau * (long double)(i - mx_root_off(R)) / (long double)R;
     };
     const size_t sS = cs * (size_t)nband * h.nyo2 * nx, sP = cs * (size_t)nband * h.nyo2 * nxp;
-    bool good = upload(&p->mtwM, M, lin(M)) && upload(&p->mtwC, Nc, lin(Nc)) &&
+    auto two = [&](int N) { return [=](int i) { return tau * (long double)mx_tw_index(i) / (long double)N; }; };
+    bool good = upload(&p->mtwM, mx_tw_entries(M), two(M)) && upload(&p->mtwC, mx_tw_entries(Nc), two(Nc)) &&
                 upload(&p->twr, M + 1, lin(nyp)) && upload(&p->modg, std::max(H, 1), lin(nxp)) &&
                 upload(&p->mroots, kMxRoots, root) &&
                 cudaMalloc(&p->S, sS) == cudaSuccess && cudaMalloc(&p->psfT, sP) == cudaSuccess;

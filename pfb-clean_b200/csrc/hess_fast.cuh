@@ -453,4 +453,77 @@ k_hessf_rows_inv2(const Cx<T> *__restrict__ S, T *__restrict__ out,
     cp_async_wait<0>();
 }
 
+// Pass B, one transform group per CTA: the CTA's NT = H/16 threads run the even
+// half and then the odd half of a column (the even result is parked in shared
+// memory, each thread re-reading only its own slots), so a column needs no
+// CTA-wide barrier and no cross-group combine.  For H <= 4096 two such CTAs are
+// resident per SM (same registers and occupancy as the two-group kernel) and,
+// being independent, drift out of phase: the shared-memory exchange / barrier
+// phases of one overlap the butterfly arithmetic of the other, which the
+// two-group kernel (both groups in lock step: ncu r01k, 20 % mio-throttle + 18 %
+// barrier stalls at 53 % issue utilisation) cannot do.  H = 8192 runs one CTA of
+// 512 threads per SM (fp32), which the two-group form cannot hold in registers.
+template <class T, int H, bool DYN>
+__global__ void __launch_bounds__(H / 16, (H <= 4096 ? 2 : 1))
+k_hessf_cols1(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__ tabg,
+              const Cx<T> *__restrict__ modg, HessDims h, int *counter) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *buf = reinterpret_cast<Cx<T> *>(raw);
+    Cx<T> *park = buf + ct_stride(H);
+    Cx<T> *tab = park + ct_stride(H);
+    constexpr int NT = H / 16;
+    const int t = threadIdx.x;
+    const GroupBar bar{1, NT};
+    ct_load_table<T, H>(tab, tabg);
+    const int total = h.nyo2 * h.nband;
+    ItemQueue<DYN> q;
+    q.init(counter);
+    q.request();
+    int col = q.publish();                       // also orders the table load
+    Cx<T> *const pk = park + ct_pad(t);
+    while (col < total) {
+        q.request();
+        Cx<T> *line = S + (long)col * h.nx;
+        const Cx<T> *pl = psfE + (long)col * (2 * H);
+        if (!DYN && col + (int)gridDim.x < total) {
+            // static partition: the next column of this CTA is known -- pull its S line and
+            // psfE column from DRAM into L2 while this one is transformed (shared memory is
+            // full with two CTAs per SM, so no cp.async stage; ncu r01n: 15 % long-scoreboard)
+            constexpr int PL = 128 / (int)sizeof(Cx<T>);     // complex values per 128-byte line
+            const long nc = col + (int)gridDim.x;
+            for (int i = t * PL; i < h.nx; i += NT * PL) prefetch_l2(S + nc * h.nx + i);
+            for (int i = t * PL; i < 2 * H; i += NT * PL) prefetch_l2(psfE + nc * (2 * H) + i);
+        }
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            Cx<T> v[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                const int i = t + e * NT;
+                v[e] = i < h.nx ? line[i] : cx<T>((T)0, (T)0);
+            }
+            if (half == 1) {
+#pragma unroll
+                for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], modg[t + e * NT]);
+            }
+            ct_fft<T, H, -1>(v, t, buf, tab, bar);
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], pl[half * H + t + e * NT]);
+            ct_fft<T, H, +1>(v, t, buf, tab, bar);
+            if (half == 0) {
+#pragma unroll
+                for (int e = 0; e < 16; ++e) pk[e * (NT + NT / 16)] = v[e];
+            } else {
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const int i = t + e * NT;
+                    const Cx<T> y = pk[e * (NT + NT / 16)] + cmul(v[e], cconj(modg[i]));
+                    if (i < h.nx) line[i] = y;
+                }
+            }
+        }
+        col = q.publish();
+    }
+}
+
 }  // namespace pfb

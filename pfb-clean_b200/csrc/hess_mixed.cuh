@@ -9,7 +9,7 @@
 //     butterfly j in [0, N/R):  k = j mod Ns
 //     in : u[r] = src[j + r*N/R] * w^(r*k),   w = exp(-/+ 2 pi i / (Ns*R))
 //     out: dst[(j-k)*R + k + r*Ns] = DFT_R(u)[r]
-// Twiddles come from a length-N table exp(-2 pi i m / N) (fp64 on the host,
+// Twiddles are the product of two small shared-memory tables (fp64 on the host,
 // rounded once); the odd radices use a direct O(R^2) DFT on a table of R-th
 // roots held in shared memory.
 //
@@ -83,10 +83,25 @@ template <class T, int DIR> struct MxDft<T, 8, DIR> {
     static __device__ __forceinline__ void run(Cx<T> (&u)[8], const Cx<T> *) { Dft<T, 8, DIR>::run(u); }
 };
 
+// Twiddles: w_N^m = T1[m >> 6] * T0[m & 63] from two small tables held in shared
+// memory (T0[i] = w_N^i, i < 64; T1[i] = w_N^(64 i)): one extra complex multiply
+// instead of a gather from a length-N table in global memory, whose L2 latency
+// was exposed once per butterfly (first measurement of this path: 111 us per
+// 10240-point column pair, 7x its shared-memory traffic bound).
+static const int kMxTw0 = 64, kMxTwMax = 64 + 256;       // N <= 16384
+static inline int mx_tw_entries(int N) { return kMxTw0 + (N + kMxTw0 - 1) / kMxTw0; }
+// host: angle index (in units of 2 pi / N) of table entry i
+static inline long mx_tw_index(int i) { return i < kMxTw0 ? i : (long)(i - kMxTw0) * kMxTw0; }
+
+template <class T>
+__device__ __forceinline__ Cx<T> mx_twiddle(const Cx<T> *tws, int m) {
+    return cmul(tws[kMxTw0 + (m >> 6)], tws[m & 63]);
+}
+
 // one radix-R stage over L lines of length N (line l at src + l*N)
 template <class T, int R, int DIR>
 __device__ __forceinline__ void mx_stage(const Cx<T> *src, Cx<T> *dst, int L, int N, int Ns,
-                                         const Cx<T> *__restrict__ tw, const Cx<T> *rt) {
+                                         const Cx<T> *tws, const Cx<T> *rt) {
     const int nb = N / R;
     const int twm = N / (Ns * R);
     for (int i = threadIdx.x; i < nb * L; i += blockDim.x) {
@@ -98,7 +113,7 @@ __device__ __forceinline__ void mx_stage(const Cx<T> *src, Cx<T> *dst, int L, in
         for (int r = 0; r < R; ++r) u[r] = s[r * nb];
         if (Ns > 1) {
 #pragma unroll
-            for (int r = 1; r < R; ++r) u[r] = cmul(u[r], twd<T, DIR>(tw[r * k * twm]));
+            for (int r = 1; r < R; ++r) u[r] = cmul(u[r], twd<T, DIR>(mx_twiddle(tws, r * k * twm)));
         }
         MxDft<T, R, DIR>::run(u, rt);
         Cx<T> *o = dst + (long)l * N + (j - k) * R + k;
@@ -112,7 +127,7 @@ __device__ __forceinline__ void mx_stage(const Cx<T> *src, Cx<T> *dst, int L, in
 // (synchronised).  Every thread of the block must call it.
 template <class T, int DIR>
 __device__ __forceinline__ Cx<T> *mx_fft(Cx<T> *a, Cx<T> *b, int L, const MxDesc &d,
-                                         const Cx<T> *__restrict__ tw, const Cx<T> *rt) {
+                                         const Cx<T> *tw, const Cx<T> *rt) {
     int Ns = 1;
     for (int s = 0; s < d.nstage; ++s) {
         const int R = d.radix[s];
@@ -133,13 +148,18 @@ __device__ __forceinline__ Cx<T> *mx_fft(Cx<T> *a, Cx<T> *b, int L, const MxDesc
     return a;
 }
 
-template <class T>
-__device__ __forceinline__ void mx_load_roots(Cx<T> *rt, const Cx<T> *__restrict__ roots) {
-    for (int i = threadIdx.x; i < kMxRoots; i += blockDim.x) rt[i] = roots[i];
-}
+// shared memory: [roots (kMxRoots, padded to 40)] [twiddle tables (kMxTwMax)] [A: L*N] [B: L*N]
+static const int kMxHead = 40 + kMxTwMax;
+static inline size_t mx_smem_bytes(int N, int L, size_t cs) { return cs * (kMxHead + (size_t)2 * L * N); }
 
-// shared memory: [roots (kMxRoots, padded to 40)] [A: L*N] [B: L*N]
-static inline size_t mx_smem_bytes(int N, int L, size_t cs) { return cs * (40 + (size_t)2 * L * N); }
+// roots -> rt[0..40), two-level twiddle tables of length N -> rt[40..)
+template <class T>
+__device__ __forceinline__ void mx_load_tables(Cx<T> *rt, const Cx<T> *__restrict__ roots,
+                                               const Cx<T> *__restrict__ tw, int N) {
+    for (int i = threadIdx.x; i < kMxRoots; i += blockDim.x) rt[i] = roots[i];
+    const int n = kMxTw0 + (N + kMxTw0 - 1) / kMxTw0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) rt[40 + i] = tw[i];
+}
 
 // ------------------------------------------------------------------ pass A
 template <class T>
@@ -150,9 +170,9 @@ k_hessm_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
     PFB_DYN_SMEM(raw);
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
     const int M = h.M, L = h.R;
-    Cx<T> *A = rt + 40, *B = A + (long)L * M;
+    Cx<T> *A = rt + kMxHead, *B = A + (long)L * M;
     const int band = blockIdx.y, row0 = blockIdx.x * L;
-    mx_load_roots(rt, roots);
+    mx_load_tables(rt, roots, tw, M);
     for (int i = threadIdx.x; i < L * M; i += blockDim.x) {
         const int l = i / M, m = i - l * M, row = row0 + l, c0 = 2 * m;
         T a = (T)0, b = (T)0;
@@ -164,7 +184,7 @@ k_hessm_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
         A[i] = cx<T>(a, b);
     }
     __syncthreads();
-    const Cx<T> *Z = mx_fft<T, -1>(A, B, L, d, tw, rt);
+    const Cx<T> *Z = mx_fft<T, -1>(A, B, L, d, rt + 40, rt);
     // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
     for (int i = threadIdx.x; i < (M + 1) * L; i += blockDim.x) {
         const int k = i / L, l = i - k * L;
@@ -187,18 +207,19 @@ k_hessm_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
     PFB_DYN_SMEM(raw);
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
     const int N = d.N;
-    Cx<T> *A = rt + 40, *B = A + N;
+    Cx<T> *A = rt + kMxHead, *B = A + N;
     const int band = blockIdx.y, col = blockIdx.x;
     Cx<T> *line = S + ((long)band * h.nyo2 + col) * h.nx;
     const Cx<T> *pl = psfT + ((long)band * h.nyo2 + col) * h.nxp;
-    mx_load_roots(rt, roots);
+    mx_load_tables(rt, roots, tw, N);
+    const Cx<T> *tws = rt + 40;
     for (int n = threadIdx.x; n < N; n += blockDim.x) A[n] = n < h.nx ? line[n] : cx<T>((T)0, (T)0);
     __syncthreads();
-    Cx<T> *c = mx_fft<T, -1>(A, B, 1, d, tw, rt);
+    Cx<T> *c = mx_fft<T, -1>(A, B, 1, d, tws, rt);
     Cx<T> *o = c == A ? B : A;
     for (int n = threadIdx.x; n < N; n += blockDim.x) c[n] = cmul(c[n], pl[n]);
     __syncthreads();
-    Cx<T> *r = mx_fft<T, +1>(c, o, 1, d, tw, rt);
+    Cx<T> *r = mx_fft<T, +1>(c, o, 1, d, tws, rt);
     if (!SPLIT) {
         for (int n = threadIdx.x; n < h.nx; n += blockDim.x) line[n] = r[n];
         return;
@@ -210,11 +231,11 @@ k_hessm_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
     __syncthreads();                              // every read of the line is done
     for (int n = threadIdx.x; n < h.nx; n += blockDim.x) line[n] = r[n];
     __syncthreads();
-    c = mx_fft<T, -1>(o, r, 1, d, tw, rt);
+    c = mx_fft<T, -1>(o, r, 1, d, tws, rt);
     o = c == A ? B : A;
     for (int n = threadIdx.x; n < N; n += blockDim.x) c[n] = cmul(c[n], pl[N + n]);
     __syncthreads();
-    r = mx_fft<T, +1>(c, o, 1, d, tw, rt);
+    r = mx_fft<T, +1>(c, o, 1, d, tws, rt);
     // same thread wrote line[n] above (same index mapping): no fence needed
     for (int n = threadIdx.x; n < h.nx; n += blockDim.x)
         line[n] = line[n] + cmul(r[n], cconj(modg[n]));
@@ -229,9 +250,9 @@ k_hessm_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *
     PFB_DYN_SMEM(raw);
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
     const int M = h.M, L = h.R;
-    Cx<T> *A = rt + 40, *B = A + (long)L * M;
+    Cx<T> *A = rt + kMxHead, *B = A + (long)L * M;
     const int band = blockIdx.y, row0 = blockIdx.x * L;
-    mx_load_roots(rt, roots);
+    mx_load_tables(rt, roots, tw, M);
     // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m]), m < M
     for (int i = threadIdx.x; i < M * L; i += blockDim.x) {
         const int m = i / L, l = i - m * L;
@@ -246,7 +267,7 @@ k_hessm_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *
         A[(long)l * M + m] = cx<T>(P.x - wQ.y, P.y + wQ.x);
     }
     __syncthreads();
-    const Cx<T> *Z = mx_fft<T, +1>(A, B, L, d, tw, rt);
+    const Cx<T> *Z = mx_fft<T, +1>(A, B, L, d, rt + 40, rt);
     for (int i = threadIdx.x; i < L * M; i += blockDim.x) {
         const int l = i / M, m = i - l * M, row = row0 + l, c0 = 2 * m;
         if (row >= h.nx) continue;
