@@ -212,6 +212,10 @@ struct pfb_hess_plan {
     pfb::MxDesc mrow, mcol;
     void *mtwM, *mtwC, *mroots;   // length-M / length-(H or nxp) twiddle tables, odd-radix roots
     int deint;               // psfT rows stored [even | odd] per column
+#ifndef PFB_EMU
+    CUtensorMap tmS;         // S as (band, k, row) tensor of 8-byte elements, box 2 rows x 256 k (fp32 fast path)
+#endif
+    int have_tma;
 };
 
 namespace pfb {
@@ -296,9 +300,66 @@ static int fast_rows_inv2(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaS
     return PFB_OK;
 }
 
+#ifndef PFB_EMU
+// S described to the TMA unit: dims (row, k, band), 8-byte elements, box (2, 256, 1)
+static bool make_tma_S(pfb_hess_plan *p) {
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess || !fn) {
+        cudaGetLastError();
+        return false;
+    }
+    const HessDims &h = p->h;
+    const cuuint64_t dims[3] = {(cuuint64_t)h.nx, (cuuint64_t)h.nyo2, (cuuint64_t)h.nband};
+    const cuuint64_t strides[2] = {(cuuint64_t)h.nx * 8, (cuuint64_t)h.nx * 8 * (cuuint64_t)h.nyo2};
+    const cuuint32_t box[3] = {2, (cuuint32_t)kTmaBoxK, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult rc = ((encode_fn)fn)(&p->tmS, CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, p->S, dims, strides, box, estr,
+                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return rc == CUDA_SUCCESS;
+}
+
+template <int M>
+static int fast_rows_inv_tma(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st) {
+    const HessDims &h = p->h;
+    const size_t smem = sizeof(Cx<float>) * ((size_t)2 * tma_stage_elems<M>() + ct_tab_size(M) + M) + 16 + 128;
+    auto kern = p->dyn ? &k_hessf_rows_inv_tma<M, true> : &k_hessf_rows_inv_tma<M, false>;
+    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int nbb = cdiv(h.nx, 4);
+    int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
+    launch(kern, dim3(grid), dim3(M / 8), smem, st, p->tmS, out, (const Cx<float> *)p->tabM,
+           (const Cx<float> *)p->twr, h, nbb, ep, p->ctr + 2);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+template <class T, int M> struct RowsInvTma {
+    static bool fits() { return false; }
+    static int run(pfb_hess_plan *, T *, const Epilogue<T> &, cudaStream_t) { return PFB_ERR_BAD_ARG; }
+};
+template <int M> struct RowsInvTma<float, M> {
+    static bool fits() {
+        return sizeof(Cx<float>) * ((size_t)2 * tma_stage_elems<M>() + ct_tab_size(M) + M) + 144 <= kMaxSmemFast;
+    }
+    static int run(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st) {
+        return fast_rows_inv_tma<M>(p, out, ep, st);
+    }
+};
+#endif
+
 template <class T, int M, int RB>
 static int fast_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
     const HessDims &h = p->h;
+#ifndef PFB_EMU
+    if (p->have_tma && h.nx % 2 == 0 && RowsInvTma<T, M>::fits() && !getenv("PFB_HESS_NOTMA") &&
+        !getenv("PFB_HESS_NOPIPE"))
+        return RowsInvTma<T, M>::run(p, out, ep, st);
+#endif
     // pipelined kernel (four lines: gather of the next row pair under the transforms) when it fits
     const size_t smem4 = sizeof(Cx<T>) * ((size_t)4 * ct_stride(M) + ct_tab_size(M));
     if (!getenv("PFB_HESS_NOPIPE") && h.nx % 2 == 0) {
@@ -643,6 +704,9 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
         }
         p->fast = fast ? 1 : 0;
         p->deint = p->fast;
+#ifndef PFB_EMU
+        p->have_tma = (fast && dtype == PFB_F32 && nx % 2 == 0 && make_tma_S(p)) ? 1 : 0;
+#endif
         // Dynamic distribution costs ~5 % when the GPU is otherwise idle (measured on the
         // column pass) and wins when a concurrent kernel holds SMs (NCCL all-reduce of
         // the band-sharded solver): off by default, the sharded solver turns it on.

@@ -20,6 +20,9 @@
 //          pre-processing, inverse transform, crop + epilogue).
 #pragma once
 #include "fft_ct.cuh"
+#ifndef PFB_EMU
+#include <cuda.h>          // CUtensorMap (pass C gathers through the TMA unit)
+#endif
 
 namespace pfb {
 
@@ -106,6 +109,16 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
         q.request();                             // the next batch, consumed by publish() below
         const int band = batch / nbatch_band;
         const int row0 = (batch - band * nbatch_band) * RB;
+        if (!DYN && batch + (int)gridDim.x < total) {
+            // static partition: pull the next batch's image rows from DRAM into L2 now
+            const int nb2 = batch + (int)gridDim.x, band2 = nb2 / nbatch_band;
+            const int r2 = (nb2 - band2 * nbatch_band) * RB;
+            const int nrow = h.nx - r2 < RB ? h.nx - r2 : RB;
+            const T *src = x + ((long)band2 * h.nx + r2) * h.ny;
+            constexpr int PL = 128 / (int)sizeof(T);
+            for (long i = (long)threadIdx.x * PL; i < (long)nrow * h.ny; i += (long)blockDim.x * PL)
+                prefetch_l2(src + i);
+        }
 #pragma unroll 1
         for (int ph = 0; ph < RB / 2; ++ph) {
             const int l = 2 * ph + g, row = row0 + l;
@@ -525,5 +538,154 @@ k_hessf_cols1(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict_
         col = q.publish();
     }
 }
+
+#ifndef PFB_EMU
+// ---------------------------------------------------------------------------
+// Pass C with the transposed gather done by the TMA unit (fp32).  S is described
+// to the hardware as a 3-D tensor (row fastest, then k, then band) of 8-byte
+// elements; one box = 2 rows x 256 k lands as a dense [k][2] block, i.e. exactly the
+// interleaved stage the cp.async kernel builds, but without a single LSU
+// instruction: in k_hessf_rows_inv2 the 16-byte gather copies each cost an L1TEX
+// wavefront and queue in front of the transforms' own shared-memory traffic (ncu
+// r01l: 38 % mio-throttle stalls).  One elected thread arms an mbarrier with the
+// byte count of the 17 boxes of a row pair and issues them; everybody waits on the
+// mbarrier's phase bit before touching the stage.  Rows beyond k = M are
+// zero-filled by the unit (out-of-bounds box rows).
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(void *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra LAB_DONE;\n"
+        "bra LAB_WAIT;\n"
+        "LAB_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const void *tmap, int c0, int c1, int c2, void *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(smem_u32(dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
+
+constexpr int kTmaBoxK = 256;                              // k rows per box (hardware limit)
+// bytes of one stage: 17 boxes of 256 x 16 B for M = 4096, rounded to 128 B; also holds the
+// two exchange lines of the pair
+template <int M> __host__ __device__ constexpr int tma_stage_elems() {
+    constexpr int boxes = (M + 1 + kTmaBoxK - 1) / kTmaBoxK;
+    constexpr int need = boxes * kTmaBoxK * 2;
+    constexpr int lines = 2 * ct_stride(M);
+    return ((need > lines ? need : lines) + 15) / 16 * 16;
+}
+
+template <int M, bool DYN>
+__global__ void __launch_bounds__(M / 8, 1)
+k_hessf_rows_inv_tma(const __grid_constant__ CUtensorMap tmS, float *__restrict__ out,
+                     const Cx<float> *__restrict__ tabg, const Cx<float> *__restrict__ twrg,
+                     HessDims h, int nbatch_band, Epilogue<float> ep, int *counter) {
+    typedef float T;
+    PFB_DYN_SMEM(raw);
+    constexpr int SE = tma_stage_elems<M>();
+    constexpr int NBOX = (M + 1 + kTmaBoxK - 1) / kTmaBoxK;
+    // two stages of SE elements; TMA destinations must be 128-byte aligned
+    Cx<T> *bufs = reinterpret_cast<Cx<T> *>((reinterpret_cast<uintptr_t>(raw) + 127) & ~(uintptr_t)127);
+    Cx<T> *tab = bufs + 2 * SE;
+    Cx<T> *tws = tab + ct_tab_size(M);
+    unsigned long long *mbar = reinterpret_cast<unsigned long long *>(tws + M);
+    constexpr int NT = M / 16;
+    const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
+    const GroupBar bar{1 + g, NT};
+    ct_load_table<T, M>(tab, tabg);
+    for (int i = threadIdx.x; i < M; i += blockDim.x) tws[i] = twrg[i];
+    if (threadIdx.x == 0) {
+        mbar_init(&mbar[0], 1);
+        mbar_init(&mbar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int total = nbatch_band * h.nband;
+    // rows (row0 + 2 ph, row0 + 2 ph + 1) of item `batch` -> stage c (issued by thread 0 only)
+    auto gather = [&](const int batch, const int ph, const int c) {
+        if (batch < total && threadIdx.x == 0) {
+            const int band = batch / nbatch_band;
+            const int row0 = (batch - band * nbatch_band) * 4 + 2 * ph;
+            // the stage was last written through the generic proxy (exchange stores)
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_expect_tx(&mbar[c], (unsigned)(NBOX * kTmaBoxK * 2 * sizeof(Cx<T>)));
+#pragma unroll 1
+            for (int b = 0; b < NBOX; ++b)
+                tma_load_3d(bufs + c * SE + b * kTmaBoxK * 2, &tmS, row0, b * kTmaBoxK, band, &mbar[c]);
+        }
+    };
+    ItemQueue<DYN> q;
+    q.init(counter);
+    q.request();
+    int batch = q.publish();
+    q.request();
+    int nxt = q.publish();
+    gather(batch, 0, 0);
+    int c = 0;
+    unsigned par[2] = {0u, 0u};
+    while (batch < total) {
+        q.request();                             // the item after `nxt`
+        const int band = batch / nbatch_band;
+        const int row0 = (batch - band * nbatch_band) * 4;
+#pragma unroll 1
+        for (int ph = 0; ph < 2; ++ph) {
+            mbar_wait(&mbar[c], par[c]);         // pair (batch, ph) has landed
+            par[c] ^= 1u;
+            __syncthreads();                     // everyone is done with the other stage
+            if (ph == 0) gather(batch, 1, c ^ 1);
+            else gather(nxt, 0, c ^ 1);
+            const int row = row0 + 2 * ph + g;
+            Cx<T> *buf = bufs + c * SE + g * ct_stride(M);
+            const Cx<T> *stg = bufs + c * SE + g;
+            // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m])
+            Cx<T> v[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                const int m = t + e * NT;
+                const Cx<T> xm = stg[2 * m], xr = cconj(stg[2 * (M - m)]);
+                const Cx<T> A = xm + xr, B = xm - xr;
+                const Cx<T> wB = cmul(cconj(tws[m]), B);
+                v[e] = cx<T>(A.x - wB.y, A.y + wB.x);
+            }
+            __syncthreads();                     // both rows are in registers: the stage becomes the exchange lines
+            ct_fft<T, M, +1>(v, t, buf, tab, bar);
+            if (row < h.nx) {
+                const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const int c0 = 2 * (t + e * NT);
+                    if (c0 < h.ny) {
+                        float2 o;
+                        o.x = v[e].x; o.y = v[e].y;
+                        if (ep.beam) {
+                            float2 bm = *reinterpret_cast<const float2 *>(ep.beam + ro + c0);
+                            o.x *= bm.x; o.y *= bm.y;
+                        }
+                        if (ep.has_wsum) { o.x /= ep.wsum; o.y /= ep.wsum; }
+                        if (ep.x) {
+                            float2 xx = *reinterpret_cast<const float2 *>(ep.x + ro + c0);
+                            o.x += xx.x * ep.sigmainv; o.y += xx.y * ep.sigmainv;
+                        }
+                        *reinterpret_cast<float2 *>(out + ro + c0) = o;
+                    }
+                }
+            }
+            c ^= 1;
+        }
+        batch = nxt;
+        nxt = q.publish();
+    }
+}
+#endif  // !PFB_EMU
 
 }  // namespace pfb
