@@ -162,8 +162,9 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
         "k_hess_rows_inv": nb_local * (S + P1),
         "k_pd_primal": nb_local * (5 + lin) * P1,     # read xp,xout(,wprev),conv,data ; write x
     }
-    for k in ("rows_fwd", "cols", "rows_inv"):  # fast-path kernels move the same bytes
+    for k in ("rows_fwd", "cols", "rows_inv"):  # fast-path / mixed-radix kernels move the same bytes
         per_kernel["k_hessf_" + k] = per_kernel["k_hess_" + k]
+        per_kernel["k_hessm_" + k] = per_kernel["k_hess_" + k]
     per_op = {                                  # SURVEY 8(d) table, x nb_local
         "psi_dot": nb_local * (P1 + C1),
         "psi_hdot": nb_local * (C1 + P1),       # hdot(u), u = 2v - vp written by the dual update
@@ -178,7 +179,8 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
 def short_kernel_name(mangled):
     for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_slab_to_nat", "k_nat_to_slab", "k_dual_partial", "k_dual_apply", "k_dual",
               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
-              "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv", "k_pd_primal", "k_red_final",
+              "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
+              "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv", "k_pd_primal", "k_red_final",
               "k_norm_diff", "k_axpby", "k_dot", "k_prox21", "k_psfhat_prepare"):
         if k in mangled:
             return k
@@ -413,7 +415,8 @@ def finish_ours(a, env):
     ops = {}
     groups = {"psi_dot": ["k_dwt_level", "k_dwt_stream", "k_self_dot"], "psi_hdot": ["k_idwt_level", "k_idwt_stream", "k_slab_to_nat"],
               "psf_convolve": ["k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
-                               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv"],
+                               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
+                               "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv"],
               "dual_update": ["k_dual", "k_dual_partial", "k_dual_apply"],
               "primal_update+eps": ["k_pd_primal"]}
     for op, ks in groups.items():

@@ -507,14 +507,18 @@ k_hessf_cols1(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict_
             for (int i = t * PL; i < h.nx; i += NT * PL) prefetch_l2(S + nc * h.nx + i);
             for (int i = t * PL; i < 2 * H; i += NT * PL) prefetch_l2(psfE + nc * (2 * H) + i);
         }
+        // the column is read from global memory once: a copy is stashed in the (still unused)
+        // park line for the odd half; each thread only ever touches its own park slots
+        Cx<T> v[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            const int i = t + e * NT;
+            v[e] = i < h.nx ? line[i] : cx<T>((T)0, (T)0);
+        }
+#pragma unroll
+        for (int e = 0; e < 16; ++e) pk[e * (NT + NT / 16)] = v[e];
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
-            Cx<T> v[16];
-#pragma unroll
-            for (int e = 0; e < 16; ++e) {
-                const int i = t + e * NT;
-                v[e] = i < h.nx ? line[i] : cx<T>((T)0, (T)0);
-            }
             if (half == 1) {
 #pragma unroll
                 for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], modg[t + e * NT]);
@@ -523,9 +527,13 @@ k_hessf_cols1(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict_
 #pragma unroll
             for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], pl[half * H + t + e * NT]);
             ct_fft<T, H, +1>(v, t, buf, tab, bar);
-            if (half == 0) {
+            if (half == 0) {                     // swap: even result into the park, input back out
 #pragma unroll
-                for (int e = 0; e < 16; ++e) pk[e * (NT + NT / 16)] = v[e];
+                for (int e = 0; e < 16; ++e) {
+                    const Cx<T> a = pk[e * (NT + NT / 16)];
+                    pk[e * (NT + NT / 16)] = v[e];
+                    v[e] = a;
+                }
             } else {
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
