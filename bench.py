@@ -139,7 +139,7 @@ def summarise_clocks(rows):
 
 
 # -------------------------------------------------------- algorithmic bytes
-def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
+def byte_model(nb_local, nx, s, Nmax, nbasis, multi, fused=False):
     """Algorithmic (compulsory) bytes, SURVEY.md 8(d) / DESIGN.md, for the bands
     on ONE GPU.  s = bytes per real."""
     nxp = 2 * nx
@@ -172,6 +172,12 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi):
         "dual_update": nb_local * (4 - lin) * C1 + C1,
         "primal_update+eps": nb_local * (5 + lin) * P1,
     }
+    if fused:
+        # pfb_hess_apply_primal: pass C reads S, xp, w_k, w_{k-1}, data and writes x (no conv array,
+        # no separate primal kernel)
+        for k in ("k_hess_rows_inv", "k_hessf_rows_inv", "k_hessm_rows_inv"):
+            per_kernel[k] = nb_local * (S + 5 * P1)
+        per_op["psf_convolve+primal_update"] = nb_local * (6 * P1 + psfhat)
     fused_iter = nb_local * (3 * P1 + psfhat + 2 * C1) + C1     # SURVEY 8(d) headline lower bound
     return per_kernel, per_op, fused_iter
 
@@ -377,7 +383,8 @@ def finish_ours(a, env):
     if rank != 0:
         return None
     hbm, peak_src = peaks()
-    per_kernel, per_op, fused_iter = byte_model(nbl, nx, s, psi.Nxmax, nbasis, world > 1)
+    fused_primal = "k_pd_primal" not in kern       # pfb_hess_apply_primal ran (primal step inside pass C)
+    per_kernel, per_op, fused_iter = byte_model(nbl, nx, s, psi.Nxmax, nbasis, world > 1, fused_primal)
     # dominant kernel = largest total device time in the timed region
     tot_k = sum(t for _, t in kern.values())
     dom = max(kern.items(), key=lambda kv: kv[1][1])
@@ -419,6 +426,8 @@ def finish_ours(a, env):
                                "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv"],
               "dual_update": ["k_dual", "k_dual_partial", "k_dual_apply"],
               "primal_update+eps": ["k_pd_primal"]}
+    if fused_primal:
+        groups["psf_convolve+primal_update"] = groups.pop("psf_convolve")
     for op, ks in groups.items():
         t = sum(kern[k][1] for k in ks if k in kern) / K
         if t > 0:

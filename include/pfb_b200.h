@@ -211,6 +211,18 @@ int pfb_hess_apply(pfb_hess_plan *plan, const void *x, const void *beam, int add
                    double sigmainv, int has_wsum, double wsum, void *out,
                    void *stream);
 
+/* PSF convolution with the primal step of primal_dual_optimised
+ * (pfb/opt/primal_dual.py:138-150) fused into its last pass:
+ *   x = P+( xp - tau * (2 w - wprev + psf_convolve(xp) - data) ),  out2 as pfb_norm_diff
+ * (positivity 0 or 1; w, wprev = Psi(v) of this and the previous iteration, see
+ * pfb_pd_primal_lin).  The convolution result is never written.  Available when
+ * pfb_hess_plan_can_fuse_primal() is 1: fp32 power-of-two fast path whose pass C
+ * gathers through the TMA unit; otherwise use pfb_hess_apply + pfb_pd_primal_lin. */
+int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *plan);
+int pfb_hess_apply_primal(pfb_hess_plan *plan, const void *xp, const void *w, const void *wprev,
+                          const void *data, double tau, int positivity, void *x, double *out2,
+                          void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -216,6 +216,7 @@ struct pfb_hess_plan {
     CUtensorMap tmS;         // S as (band, k, row) tensor of 8-byte elements, box 2 rows x 256 k (fp32 fast path)
 #endif
     int have_tma;
+    double *pd_part;         // partial eps sums of the fused primal epilogue (2 per CTA)
 };
 
 namespace pfb {
@@ -325,31 +326,62 @@ static bool make_tma_S(pfb_hess_plan *p) {
     return rc == CUDA_SUCCESS;
 }
 
-template <int M>
-static int fast_rows_inv_tma(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st) {
+template <int M, bool PRIMAL>
+static int fast_rows_inv_tma(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, PrimalArgs pa,
+                             double *out2, cudaStream_t st) {
     const HessDims &h = p->h;
     const size_t smem = sizeof(Cx<float>) * ((size_t)2 * tma_stage_elems<M>() + ct_tab_size(M) + M) + 16 + 128;
-    auto kern = p->dyn ? &k_hessf_rows_inv_tma<M, true> : &k_hessf_rows_inv_tma<M, false>;
+    auto kern = p->dyn ? &k_hessf_rows_inv_tma<M, true, PRIMAL> : &k_hessf_rows_inv_tma<M, false, PRIMAL>;
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int nbb = cdiv(h.nx, 4);
     int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
+    if (grid > 4 * p->nsm) grid = 4 * p->nsm;      // size of pd_part
+    pa.part = p->pd_part;
     launch(kern, dim3(grid), dim3(M / 8), smem, st, p->tmS, out, (const Cx<float> *)p->tabM,
-           (const Cx<float> *)p->twr, h, nbb, ep, p->ctr + 2);
+           (const Cx<float> *)p->twr, h, nbb, ep, pa, p->ctr + 2);
     PFB_CHECK_LAUNCH();
+    if (PRIMAL) {
+        launch(&k_hess_red_final, dim3(1), dim3(32), 0, st, (const double *)p->pd_part, grid, out2);
+        PFB_CHECK_LAUNCH();
+    }
     return PFB_OK;
 }
 template <class T, int M> struct RowsInvTma {
     static bool fits() { return false; }
     static int run(pfb_hess_plan *, T *, const Epilogue<T> &, cudaStream_t) { return PFB_ERR_BAD_ARG; }
+    static int run_primal(pfb_hess_plan *, const PrimalArgs &, double *, cudaStream_t) { return PFB_ERR_BAD_ARG; }
 };
 template <int M> struct RowsInvTma<float, M> {
     static bool fits() {
         return sizeof(Cx<float>) * ((size_t)2 * tma_stage_elems<M>() + ct_tab_size(M) + M) + 144 <= kMaxSmemFast;
     }
     static int run(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st) {
-        return fast_rows_inv_tma<M>(p, out, ep, st);
+        return fast_rows_inv_tma<M, false>(p, out, ep, PrimalArgs(), nullptr, st);
+    }
+    static int run_primal(pfb_hess_plan *p, const PrimalArgs &pa, double *out2, cudaStream_t st) {
+        return fast_rows_inv_tma<M, true>(p, nullptr, Epilogue<float>(), pa, out2, st);
     }
 };
+
+// M-dispatch of the fused pass C (fp32 only)
+static bool tma_fits_m(int M) {
+    switch (M) {
+    case 512: return RowsInvTma<float, 512>::fits();
+    case 1024: return RowsInvTma<float, 1024>::fits();
+    case 2048: return RowsInvTma<float, 2048>::fits();
+    case 4096: return RowsInvTma<float, 4096>::fits();
+    default: return false;
+    }
+}
+static int run_primal_m(pfb_hess_plan *p, const PrimalArgs &pa, double *out2, cudaStream_t st) {
+    switch (p->h.M) {
+    case 512: return RowsInvTma<float, 512>::run_primal(p, pa, out2, st);
+    case 1024: return RowsInvTma<float, 1024>::run_primal(p, pa, out2, st);
+    case 2048: return RowsInvTma<float, 2048>::run_primal(p, pa, out2, st);
+    case 4096: return RowsInvTma<float, 4096>::run_primal(p, pa, out2, st);
+    default: return fail(PFB_ERR_FFT_SIZE, "fused primal pass: unsupported length %d", p->h.M);
+    }
+}
 #endif
 
 template <class T, int M, int RB>
@@ -706,6 +738,10 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
         p->deint = p->fast;
 #ifndef PFB_EMU
         p->have_tma = (fast && dtype == PFB_F32 && nx % 2 == 0 && make_tma_S(p)) ? 1 : 0;
+        if (p->have_tma && cudaMalloc((void **)&p->pd_part, sizeof(double) * 2 * 4 * p->nsm) != cudaSuccess) {
+            cudaGetLastError();
+            p->pd_part = nullptr;
+        }
 #endif
         // Dynamic distribution costs ~5 % when the GPU is otherwise idle (measured on the
         // column pass) and wins when a concurrent kernel holds SMs (NCCL all-reduce of
@@ -723,6 +759,7 @@ int pfb_hess_plan_destroy(pfb_hess_plan *p) {
     if (p->twr) cudaFree(p->twr);
     if (p->modg) cudaFree(p->modg);
     if (p->ctr) cudaFree(p->ctr);
+    if (p->pd_part) cudaFree(p->pd_part);
     if (p->mtwM) cudaFree(p->mtwM);
     if (p->mtwC) cudaFree(p->mtwC);
     if (p->mroots) cudaFree(p->mroots);
@@ -758,6 +795,45 @@ int pfb_hess_apply(pfb_hess_plan *p, const void *x, const void *beam, int add_x,
     return hess_apply_t<double>(p, (const double *)x, (const double *)beam, (const double *)beam,
                                 add_x ? (const double *)x : nullptr, sigmainv, has_wsum, wsum,
                                 (double *)out, st);
+}
+
+int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *p) {
+#ifndef PFB_EMU
+    if (!p || !p->fast || !p->have_tma || !p->pd_part || p->dtype != PFB_F32 || p->h.nx % 2) return 0;
+    if (getenv("PFB_HESS_NOTMA") || getenv("PFB_HESS_NOPIPE") || getenv("PFB_HESS_NOFUSE")) return 0;
+    return tma_fits_m(p->h.M) ? 1 : 0;
+#else
+    (void)p;
+    return 0;
+#endif
+}
+
+int pfb_hess_apply_primal(pfb_hess_plan *p, const void *xp, const void *w, const void *wprev,
+                          const void *data, double tau, int positivity, void *x, double *out2,
+                          void *stream) {
+#ifndef PFB_EMU
+    if (!p || !xp || !w || !wprev || !data || !x || !out2 || (positivity != 0 && positivity != 1))
+        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: bad argument");
+    if (!p->have_psf) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: psfhat not set");
+    if (!pfb_hess_plan_can_fuse_primal(p))
+        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: not available for this plan "
+                                     "(see pfb_hess_plan_can_fuse_primal)");
+    if (x == xp) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: x must not alias xp");
+    if (((uintptr_t)xp | (uintptr_t)w | (uintptr_t)wprev | (uintptr_t)data | (uintptr_t)x) & 7)
+        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: arrays must be 8-byte aligned");
+    cudaStream_t st = as_stream(stream);
+    if (p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
+    if (int rc = fast_rows_fwd_d<float>(p, (const float *)xp, nullptr, st)) return rc;
+    if (int rc = fast_cols_d<float>(p, st)) return rc;
+    PrimalArgs pa;
+    pa.xp = (const float *)xp; pa.w = (const float *)w; pa.wprev = (const float *)wprev;
+    pa.data = (const float *)data; pa.x = (float *)x; pa.tau = (float)tau; pa.positivity = positivity;
+    pa.part = nullptr;
+    return run_primal_m(p, pa, out2, st);
+#else
+    (void)p; (void)xp; (void)w; (void)wprev; (void)data; (void)tau; (void)positivity; (void)x; (void)out2; (void)stream;
+    return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: not available in the emulator build");
+#endif
 }
 
 }  // extern "C"

@@ -593,11 +593,24 @@ template <int M> __host__ __device__ constexpr int tma_stage_elems() {
     return ((need > lines ? need : lines) + 15) / 16 * 16;
 }
 
-template <int M, bool DYN>
+// PRIMAL: the primal step of primal_dual_optimised (pfb/opt/primal_dual.py:138-150) is the
+// epilogue: with conv = this row of PSF (*) xp still in registers,
+//     x = P+( xp - tau * (2 w - wprev + conv - data) ),   eps terms sum (x-xp)^2, sum x^2,
+// same arithmetic and order as k_pd_primal_vec.  The convolution result is never written, and
+// the separate primal kernel (one more read of it plus a launch) disappears.
+struct PrimalArgs {
+    const float *xp, *w, *wprev, *data;
+    float *x;
+    float tau;
+    int positivity;      // 0 none, 1 clamp
+    double *part;        // gridDim.x * 2 partial sums
+};
+
+template <int M, bool DYN, bool PRIMAL>
 __global__ void __launch_bounds__(M / 8, 1)
 k_hessf_rows_inv_tma(const __grid_constant__ CUtensorMap tmS, float *__restrict__ out,
                      const Cx<float> *__restrict__ tabg, const Cx<float> *__restrict__ twrg,
-                     HessDims h, int nbatch_band, Epilogue<float> ep, int *counter) {
+                     HessDims h, int nbatch_band, Epilogue<float> ep, PrimalArgs pa, int *counter) {
     typedef float T;
     PFB_DYN_SMEM(raw);
     constexpr int SE = tma_stage_elems<M>();
@@ -641,6 +654,7 @@ k_hessf_rows_inv_tma(const __grid_constant__ CUtensorMap tmS, float *__restrict_
     gather(batch, 0, 0);
     int c = 0;
     unsigned par[2] = {0u, 0u};
+    double acc0 = 0.0, acc1 = 0.0;
     while (batch < total) {
         q.request();                             // the item after `nxt`
         const int band = batch / nbatch_band;
@@ -653,6 +667,13 @@ k_hessf_rows_inv_tma(const __grid_constant__ CUtensorMap tmS, float *__restrict_
             if (ph == 0) gather(batch, 1, c ^ 1);
             else gather(nxt, 0, c ^ 1);
             const int row = row0 + 2 * ph + g;
+            if (PRIMAL && row < h.nx) {          // this row of the four primal inputs: DRAM -> L2 now
+                const long ro = ((long)band * h.nx + row) * h.ny;
+                for (int i = t * 32; i < h.ny; i += NT * 32) {
+                    prefetch_l2(pa.xp + ro + i); prefetch_l2(pa.w + ro + i);
+                    prefetch_l2(pa.wprev + ro + i); prefetch_l2(pa.data + ro + i);
+                }
+            }
             Cx<T> *buf = bufs + c * SE + g * ct_stride(M);
             const Cx<T> *stg = bufs + c * SE + g;
             // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m])
@@ -667,7 +688,39 @@ k_hessf_rows_inv_tma(const __grid_constant__ CUtensorMap tmS, float *__restrict_
             }
             __syncthreads();                     // both rows are in registers: the stage becomes the exchange lines
             ct_fft<T, M, +1>(v, t, buf, tab, bar);
-            if (row < h.nx) {
+            if (PRIMAL) {
+                if (row < h.nx) {
+                    const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        const int c0 = 2 * (t + e * NT);
+                        if (c0 < h.ny) {
+                            const float2 p2 = *reinterpret_cast<const float2 *>(pa.xp + ro + c0);
+                            const float2 w2 = *reinterpret_cast<const float2 *>(pa.w + ro + c0);
+                            const float2 q2 = *reinterpret_cast<const float2 *>(pa.wprev + ro + c0);
+                            const float2 d2 = *reinterpret_cast<const float2 *>(pa.data + ro + c0);
+                            const float pv[2] = {p2.x, p2.y}, wv[2] = {w2.x, w2.y}, qv[2] = {q2.x, q2.y};
+                            const float dv[2] = {d2.x, d2.y}, cv[2] = {v[e].x, v[e].y};
+                            float xo[2];
+#pragma unroll
+                            for (int z = 0; z < 2; ++z) {
+                                float ge = 2.0f * wv[z] - qv[z];
+                                const float gr = cv[z] - dv[z];
+                                ge = ge + gr;
+                                float xi = pv[z] - pa.tau * ge;
+                                if (pa.positivity == 1 && xi < 0.0f) xi = 0.0f;
+                                xo[z] = xi;
+                                const float df = xi - pv[z];
+                                acc0 += (double)(df * df);
+                                acc1 += (double)(xi * xi);
+                            }
+                            float2 o;
+                            o.x = xo[0]; o.y = xo[1];
+                            *reinterpret_cast<float2 *>(pa.x + ro + c0) = o;
+                        }
+                    }
+                }
+            } else if (row < h.nx) {
                 const long ro = ((long)band * h.nx + row) * h.ny;
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
@@ -693,6 +746,39 @@ k_hessf_rows_inv_tma(const __grid_constant__ CUtensorMap tmS, float *__restrict_
         batch = nxt;
         nxt = q.publish();
     }
+    if (PRIMAL) {                                // deterministic block sum of the two eps terms
+        __shared__ double s_red[2][32];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            acc0 += __shfl_down_sync(0xffffffffu, acc0, o);
+            acc1 += __shfl_down_sync(0xffffffffu, acc1, o);
+        }
+        const int wid = threadIdx.x >> 5, ln = threadIdx.x & 31;
+        if (ln == 0) { s_red[0][wid] = acc0; s_red[1][wid] = acc1; }
+        __syncthreads();
+        if (wid == 0) {
+            const int nw = blockDim.x >> 5;
+            double a0 = ln < nw ? s_red[0][ln] : 0.0, a1 = ln < nw ? s_red[1][ln] : 0.0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a0 += __shfl_down_sync(0xffffffffu, a0, o);
+                a1 += __shfl_down_sync(0xffffffffu, a1, o);
+            }
+            if (ln == 0) { pa.part[2 * blockIdx.x] = a0; pa.part[2 * blockIdx.x + 1] = a1; }
+        }
+    }
+}
+
+// out2[j] = sum over the n CTAs of part[2 c + j], fixed order
+__global__ void k_hess_red_final(const double *__restrict__ part, int n, double *__restrict__ out2) {
+    double a0 = 0.0, a1 = 0.0;
+    for (int c = threadIdx.x; c < n; c += 32) { a0 += part[2 * c]; a1 += part[2 * c + 1]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a0 += __shfl_down_sync(0xffffffffu, a0, o);
+        a1 += __shfl_down_sync(0xffffffffu, a1, o);
+    }
+    if (threadIdx.x == 0) { out2[0] = a0; out2[1] = a1; }
 }
 #endif  // !PFB_EMU
 

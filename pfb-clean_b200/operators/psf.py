@@ -44,6 +44,17 @@ class HessPlan:
             _dev.ptr(out), _dev.stream()))
         return out
 
+    def can_fuse_primal(self):
+        """True when pfb_hess_apply_primal is available (fp32 fast path, TMA pass C)."""
+        return bool(_lib.lib().pfb_hess_plan_can_fuse_primal(self._h))
+
+    def apply_primal(self, xp, w, wprev, data, tau, positivity, x, out2):
+        """x = P+(xp - tau*(2w - wprev + conv(xp) - data)); out2 = the two eps terms."""
+        _lib.check(_lib.lib().pfb_hess_apply_primal(
+            self._h, _dev.ptr(xp), _dev.ptr(w), _dev.ptr(wprev), _dev.ptr(data), float(tau),
+            int(positivity), _dev.ptr(x), _dev.ptr(out2), _dev.stream()))
+        return out2
+
     def __del__(self):
         if getattr(self, "_h", None) and self._h.value:
             self._destroy(self._h)

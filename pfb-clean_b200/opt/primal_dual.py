@@ -228,6 +228,18 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     if lin:
         wprev = torch.empty_like(xa)
         P.hdot_nat(vprev, wprev)            # w_{-1} = Psi(v_0)
+    # PSF convolution with the primal step as the epilogue of its last pass
+    # (pfb_hess_apply_primal): no convolution result in memory, no separate primal kernel
+    fplan = None
+    if (lin and bound is not None and data is not None and positivity in (0, 1)
+            and not parallel.active() and xa.dtype == torch.float32
+            and not os.environ.get("PFB_PD_NOFUSE")):
+        if str(bound[0].dtype).endswith("complex64"):
+            from ..operators.psf import get_plan
+            cand = get_plan(bound[0], bound[1], tuple(xa.shape), _dev.dcode(xa))
+            if cand.can_fuse_primal():
+                fplan = cand
+    primal_dual_optimised.last_fused = fplan is not None
 
     eps = 1.0
     numreweight = 0
@@ -261,11 +273,15 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             psi(xprev, vcur)
             _dual_step(vprev, vcur, lam, sigma, w, n, bsum)      # vprev now holds 2v - vp
             psiH(vprev, xout)
-        if g is None:
-            g = gradient()
-        if g.dtype != xa.dtype:
-            g = g.to(xa.dtype)
-        _vec.pd_primal(xcur, xprev, xout, g, data, tau, pos_kernel, terms, wprev=wprev)
+        if fplan is not None:
+            fplan.set_dynamic(False)
+            fplan.apply_primal(xprev, xout, wprev, data, tau, positivity, xcur, terms)
+        else:
+            if g is None:
+                g = gradient()
+            if g.dtype != xa.dtype:
+                g = g.to(xa.dtype)
+            _vec.pd_primal(xcur, xprev, xout, g, data, tau, pos_kernel, terms, wprev=wprev)
         if lin:
             xout, wprev = wprev, xout
         if pos_kernel != positivity:   # positivity 2 across band-sharded ranks

@@ -390,6 +390,41 @@ def test_minor_cycle_vs_oracle(dtype, nband, nx):
         assert rel(xs, truth) < 2 * rel(oxs, truth) + 1e-5
 
 
+def test_fused_primal_pass_matches_unfused(monkeypatch):
+    """pfb_hess_apply_primal (primal step as the epilogue of the TMA pass C) against the
+    separate pfb_hess_apply + pfb_pd_primal_lin kernels: same arithmetic in the same order,
+    so the model is bit-identical; both positivity modes the fused pass takes."""
+    from pfb_b200.operators.psf import psf_convolve_cube
+    from pfb_b200.operators.psi import Psi
+    from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
+    nband, nx = 2, 1024
+    psfhat, dirty, _, _ = _problem(nband, nx, np.float32)
+    dev = torch.device("cuda")
+    psfd, dd = torch.from_numpy(psfhat).to(dev), torch.from_numpy(dirty).to(dev)
+    psi = Psi(nband, nx, nx, BASES, 3, 1)
+    shape_v = (nband, 5, psi.Nymax, psi.Nxmax)
+    w = torch.ones(shape_v[1:], dtype=torch.float32, device=dev)
+    lam = 0.5 * float(dd.sum(dim=0).std())
+    res = {}
+    for positivity in (1, 0):
+        for fuse in (True, False):
+            if fuse:
+                monkeypatch.delenv("PFB_PD_NOFUSE", raising=False)
+            else:
+                monkeypatch.setenv("PFB_PD_NOFUSE", "1")
+            xout = torch.empty_like(dd)
+            conv = partial(psf_convolve_cube, None, None, xout, psfd, 2 * nx)
+            x, v = torch.zeros_like(dd), torch.zeros(shape_v, dtype=torch.float32, device=dev)
+            primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, 1.3, None, w, None, Grad21(conv, dd),
+                                  nu=5, tol=0.0, maxit=6, positivity=positivity, verbosity=0)
+            assert primal_dual_optimised.last_fused == fuse
+            res[(positivity, fuse)] = (x.clone(), v.clone())
+        assert res[(positivity, True)][0].any()
+        assert torch.equal(res[(positivity, True)][0], res[(positivity, False)][0])
+        assert torch.equal(res[(positivity, True)][1], res[(positivity, False)][1])
+    assert not torch.equal(res[(1, True)][0], res[(0, True)][0])
+
+
 def test_library_is_the_one_loaded():
     """The GPU tests must run on libpfb_b200.so (no silent fallback)."""
     import pfb_b200._lib as L
