@@ -186,7 +186,7 @@ def short_kernel_name(mangled):
     for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_slab_to_nat", "k_nat_to_slab", "k_dual_partial", "k_dual_apply", "k_dual",
               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
               "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
-              "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv", "k_pd_primal", "k_red_final",
+              "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv", "k_pd_primal", "k_hess_red_final", "k_red_final",
               "k_norm_diff", "k_axpby", "k_dot", "k_prox21", "k_psfhat_prepare"):
         if k in mangled:
             return k
