@@ -190,6 +190,29 @@ def test_hess_mixed_radix_delta_kat_full_size(nx, nxp):
     assert rel(out[0], exp) < 2e-6
 
 
+@pmp("env", ["PFB_HESS_NOTMA", "PFB_HESS_NOPIPE", "PFB_HESS_COLS2G", "PFB_HESS_NOTWS", "PFB_HESS_NOPF",
+             "PFB_HESS_GENERIC"])
+def test_hess_fallback_kernels(monkeypatch, env):
+    """Every kernel variant behind the fast path's selection logic stays correct: the cp.async
+    pass C (no TMA), the un-pipelined pass C, the two-group pass B (with and without its cp.async
+    stages), pass A without the shared-memory twiddles, and the generic power-of-two kernels."""
+    from pfb_b200.operators import psf as P
+    rng = np.random.default_rng(23)
+    nband, nx, ny, nxp, nyp = 2, 600, 1000, 2048, 2048
+    psf = rng.standard_normal((nband, nxp, nyp))
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2)).astype(np.complex64)
+    x = rng.standard_normal((nband, nx, ny)).astype(np.float32)
+    xpad, xhat = np.empty((nband, nxp, nyp), np.float32), np.empty(psfhat.shape, np.complex64)
+    exp = ref.psf_convolve_cube(xpad, xhat, np.empty_like(x), psfhat, nyp, x).copy()
+    if env == "PFB_HESS_NOPF":
+        monkeypatch.setenv("PFB_HESS_COLS2G", "1")
+    monkeypatch.setenv(env, "1")
+    P.clear_plan_cache()                      # PFB_HESS_GENERIC is read at plan creation
+    out = np.full(x.shape, np.nan, np.float32)
+    P.psf_convolve_cube(None, None, out, psfhat, nyp, x)
+    assert rel(out, exp) < TOL[np.float32]
+
+
 def test_hess_dynamic_distribution_matches_static():
     """pfb_hess_plan_set_dynamic: same result bit for bit (items are independent)."""
     from pfb_b200.operators import psf as P
