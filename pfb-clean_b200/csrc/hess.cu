@@ -202,6 +202,7 @@ struct pfb_hess_plan {
     int have_psf;
     // fast path (hess_fast.cuh): nxp = 2H >= 2nx, nyp = 2M >= 2ny, H, M in [512, 4096]
     int fast, RB, nsm;
+    int fastcols;            // fp32, nxp = 16384: pass B on k_hessf_cols1<8192>, rows on the generic kernels
     void *tabM, *tabH;       // ct_fft stage tables for lengths M and H
     void *twr;               // exp(-2 pi i k / nyp), k = 0..M
     void *modg;              // exp(-2 pi i n / nxp), n = 0..H-1
@@ -531,7 +532,7 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
         PFB_CHECK_LAUNCH();
         return PFB_OK;
     }
-    if (p->fast && p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
+    if ((p->fast || p->fastcols) && p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
     if (fast_rows) {
         if (int rc = fast_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
     } else {
@@ -544,6 +545,10 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
     }
     if (p->fast) {
         if (int rc = fast_cols_d<T>(p, st)) return rc;
+    } else if (p->fastcols) {
+        if constexpr (sizeof(T) == 4) {
+            if (int rc = fast_cols1<T, 8192>(p, st)) return rc;
+        }
     } else {
         HessDims h = h0;
         h.R = p->Rcol;
@@ -735,7 +740,31 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
             }
         }
         p->fast = fast ? 1 : 0;
-        p->deint = p->fast;
+        // config 4 (16384^2 PSF, fp32): the column pass -- 57 % of the generic Hessian there --
+        // runs on the one-group compile-time kernel (one 512-thread CTA per SM); the row passes
+        // stay on the generic kernels (a 16384-point row pair does not fit the fast row kernels)
+        bool fastcols = !fast && dtype == PFB_F32 && H == 8192 && nxp == 2 * H && nx <= H &&
+                        !getenv("PFB_HESS_GENERIC") &&
+                        cs * ((size_t)2 * ct_stride(8192) + ct_tab_size(8192)) <= kMaxSmemFast;
+        if (fastcols) {
+            std::vector<float> tb(2 * (size_t)ct_tab_size(8192)), mg(2 * (size_t)H);
+            ct_fill_table(8192, [&](int i, double c, double sn) { tb[2 * i] = (float)c; tb[2 * i + 1] = (float)sn; });
+            for (int i = 0; i < H; ++i) {
+                long double a = -2.0L * 3.14159265358979323846264338327950288L * (long double)i / (long double)nxp;
+                mg[2 * i] = (float)cosl(a); mg[2 * i + 1] = (float)sinl(a);
+            }
+            bool ok3 = cudaMalloc(&p->tabH, tb.size() * 4) == cudaSuccess &&
+                       cudaMemcpy(p->tabH, tb.data(), tb.size() * 4, cudaMemcpyHostToDevice) == cudaSuccess &&
+                       cudaMalloc(&p->modg, mg.size() * 4) == cudaSuccess &&
+                       cudaMemcpy(p->modg, mg.data(), mg.size() * 4, cudaMemcpyHostToDevice) == cudaSuccess &&
+                       cudaMalloc((void **)&p->ctr, 3 * sizeof(int)) == cudaSuccess;
+            if (!ok3) {
+                pfb_hess_plan_destroy(p);
+                return fail(PFB_ERR_ALLOC, "hessian plan (column-pass tables) allocation failed");
+            }
+        }
+        p->fastcols = fastcols ? 1 : 0;
+        p->deint = p->fast | p->fastcols;
 #ifndef PFB_EMU
         p->have_tma = (fast && dtype == PFB_F32 && nx % 2 == 0 && make_tma_S(p)) ? 1 : 0;
         if (p->have_tma && cudaMalloc((void **)&p->pd_part, sizeof(double) * 2 * 4 * p->nsm) != cudaSuccess) {

@@ -213,6 +213,24 @@ def test_hess_fallback_kernels(monkeypatch, env):
     assert rel(out, exp) < TOL[np.float32]
 
 
+def test_hess_delta_kat_config4_band():
+    """One band of BASELINE config 4 (8192^2 image, 16384^2 PSF): generic row passes +
+    k_hessf_cols1<8192> column pass; delta-function known answer."""
+    from pfb_b200.operators.psf import psf_convolve_cube
+    dev = torch.device("cuda")
+    nx, nxp = 8192, 16384
+    g = torch.Generator(device=dev).manual_seed(9)
+    psf = torch.randn((1, nxp, nxp), generator=g, dtype=torch.float32, device=dev)
+    psfhat = torch.fft.rfft2(torch.fft.ifftshift(psf, dim=(1, 2)), dim=(1, 2))
+    x = torch.zeros((1, nx, nx), dtype=torch.float32, device=dev)
+    p, q = 4321, 8001
+    x[0, p, q] = 1.0
+    out = torch.empty_like(x)
+    psf_convolve_cube(None, None, out, psfhat, nxp, x)
+    exp = psf[0, nxp // 2 - p: nxp // 2 - p + nx, nxp // 2 - q: nxp // 2 - q + nx]
+    assert rel(out[0], exp) < 2e-6
+
+
 def test_hess_dynamic_distribution_matches_static():
     """pfb_hess_plan_set_dynamic: same result bit for bit (items are independent)."""
     from pfb_b200.operators import psf as P
