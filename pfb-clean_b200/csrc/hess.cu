@@ -202,7 +202,8 @@ struct pfb_hess_plan {
     int have_psf;
     // fast path (hess_fast.cuh): nxp = 2H >= 2nx, nyp = 2M >= 2ny, H, M in [512, 4096]
     int fast, RB, nsm;
-    int fastcols;            // fp32, nxp = 16384: pass B on k_hessf_cols1<8192>, rows on the generic kernels
+    int fastcols;            // fp32, nxp = 16384: pass B on k_hessf_cols1<8192>
+    int fastrows;            // fp32, nyp = 16384: passes A / C on the one-group row kernels (M = 8192)
     void *tabM, *tabH;       // ct_fft stage tables for lengths M and H
     void *twr;               // exp(-2 pi i k / nyp), k = 0..M
     void *modg;              // exp(-2 pi i n / nxp), n = 0..H-1
@@ -452,6 +453,34 @@ static int fast_cols(pfb_hess_plan *p, cudaStream_t st) {
     return PFB_OK;
 }
 
+// M = 8192 (fp32): one 512-thread transform group per CTA, two rows per batch
+static int fast_rows_fwd_8k(pfb_hess_plan *p, const float *x, const float *beam, cudaStream_t st) {
+    constexpr int M = 8192, RB = 2;
+    const HessDims &h = p->h;
+    const size_t smem = sizeof(Cx<float>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
+    auto kern = p->dyn ? &k_hessf_rows_fwd<float, M, RB, false, true, 1> : &k_hessf_rows_fwd<float, M, RB, false, false, 1>;
+    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int nbb = cdiv(h.nx, RB);
+    int grid = persistent_grid((const void *)kern, M / 16, smem, nbb * h.nband, p->nsm);
+    launch(kern, dim3(grid), dim3(M / 16), smem, st, x, beam, (Cx<float> *)p->S, (const Cx<float> *)p->tabM,
+           (const Cx<float> *)p->twr, h, nbb, p->ctr + 0);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+static int fast_rows_inv_8k(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st) {
+    constexpr int M = 8192, RB = 2;
+    const HessDims &h = p->h;
+    const size_t smem = sizeof(Cx<float>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
+    auto kern = p->dyn ? &k_hessf_rows_inv<float, M, RB, true, 1> : &k_hessf_rows_inv<float, M, RB, false, 1>;
+    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int nbb = cdiv(h.nx, RB);
+    int grid = persistent_grid((const void *)kern, M / 16, smem, nbb * h.nband, p->nsm);
+    launch(kern, dim3(grid), dim3(M / 16), smem, st, (const Cx<float> *)p->S, out, (const Cx<float> *)p->tabM,
+           (const Cx<float> *)p->twr, h, nbb, ep, p->ctr + 2);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
 #define PFB_SIZE_SWITCH(n, CALL)                         \
     switch (n) {                                         \
     case 512: return CALL(512);                          \
@@ -532,9 +561,16 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
         PFB_CHECK_LAUNCH();
         return PFB_OK;
     }
-    if ((p->fast || p->fastcols) && p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
+    const bool rows8k = p->fastrows && sizeof(T) == 4 &&
+                        !(((uintptr_t)x | (uintptr_t)out | (uintptr_t)beam_in | (uintptr_t)beam_out |
+                           (uintptr_t)addx) & al);
+    if ((p->fast || p->fastcols || p->fastrows) && p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
     if (fast_rows) {
         if (int rc = fast_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
+    } else if (rows8k) {
+        if constexpr (sizeof(T) == 4) {
+            if (int rc = fast_rows_fwd_8k(p, x, beam_in, st)) return rc;
+        }
     } else {
         HessDims h = h0;
         h.R = p->Rrow;
@@ -559,6 +595,10 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
     }
     if (fast_rows) {
         if (int rc = fast_rows_inv_d<T>(p, out, ep, st)) return rc;
+    } else if (rows8k) {
+        if constexpr (sizeof(T) == 4) {
+            if (int rc = fast_rows_inv_8k(p, out, ep, st)) return rc;
+        }
     } else {
         HessDims h = h0;
         h.R = p->Rrow;
@@ -765,6 +805,28 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
         }
         p->fastcols = fastcols ? 1 : 0;
         p->deint = p->fast | p->fastcols;
+        // same for the row passes of a 16384-wide PSF: one-group row kernels, two rows per batch
+        bool fastrows = !fast && dtype == PFB_F32 && M == 8192 && ny <= M && ny % 2 == 0 &&
+                        !getenv("PFB_HESS_GENERIC") &&
+                        cs * ((size_t)2 * ct_stride(8192) + ct_tab_size(8192)) <= kMaxSmemFast;
+        if (fastrows) {
+            std::vector<float> tb(2 * (size_t)ct_tab_size(8192)), tr(2 * (size_t)(M + 1));
+            ct_fill_table(8192, [&](int i, double c, double sn) { tb[2 * i] = (float)c; tb[2 * i + 1] = (float)sn; });
+            for (int i = 0; i <= M; ++i) {
+                long double a = -2.0L * 3.14159265358979323846264338327950288L * (long double)i / (long double)nyp;
+                tr[2 * i] = (float)cosl(a); tr[2 * i + 1] = (float)sinl(a);
+            }
+            bool ok4 = cudaMalloc(&p->tabM, tb.size() * 4) == cudaSuccess &&
+                       cudaMemcpy(p->tabM, tb.data(), tb.size() * 4, cudaMemcpyHostToDevice) == cudaSuccess &&
+                       cudaMalloc(&p->twr, tr.size() * 4) == cudaSuccess &&
+                       cudaMemcpy(p->twr, tr.data(), tr.size() * 4, cudaMemcpyHostToDevice) == cudaSuccess &&
+                       (p->ctr || cudaMalloc((void **)&p->ctr, 3 * sizeof(int)) == cudaSuccess);
+            if (!ok4) {
+                pfb_hess_plan_destroy(p);
+                return fail(PFB_ERR_ALLOC, "hessian plan (row-pass tables) allocation failed");
+            }
+        }
+        p->fastrows = fastrows ? 1 : 0;
 #ifndef PFB_EMU
         p->have_tma = (fast && dtype == PFB_F32 && nx % 2 == 0 && make_tma_S(p)) ? 1 : 0;
         if (p->have_tma && cudaMalloc((void **)&p->pd_part, sizeof(double) * 2 * 4 * p->nsm) != cudaSuccess) {

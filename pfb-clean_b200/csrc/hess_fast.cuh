@@ -82,8 +82,10 @@ template <bool DYN> struct ItemQueue {
 // twr[k] = exp(-2 pi i k / nyp), k = 0..M
 // TWS: twr (M + 1 entries) is staged in shared memory (ncu r01k: 13 % of the samples of
 // this kernel sat on the global twr[k] load of the post-processing loop).
-template <class T, int M, int RB, bool TWS, bool DYN>
-__global__ void __launch_bounds__(M / 8, 1)
+// NG = transform groups per CTA: 2 (NT = M/16 threads each), or 1 for M = 8192, whose 512-thread
+// transform leaves no registers for a second group.
+template <class T, int M, int RB, bool TWS, bool DYN, int NG = 2>
+__global__ void __launch_bounds__(NG * M / 16, 1)
 k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__restrict__ S,
                  const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twrg, HessDims h,
                  int nbatch_band, int *counter) {
@@ -120,8 +122,8 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
                 prefetch_l2(src + i);
         }
 #pragma unroll 1
-        for (int ph = 0; ph < RB / 2; ++ph) {
-            const int l = 2 * ph + g, row = row0 + l;
+        for (int ph = 0; ph < RB / NG; ++ph) {
+            const int l = NG * ph + g, row = row0 + l;
             Cx<T> *buf = bufs + l * ct_stride(M);
             Cx<T> v[16];
             const long ro = ((long)band * h.nx + row) * h.ny;
@@ -155,7 +157,7 @@ k_hessf_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
         __syncthreads();
         // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
 #pragma unroll 4
-        for (int i = threadIdx.x; i < (M + 1) * RB; i += 2 * NT) {
+        for (int i = threadIdx.x; i < (M + 1) * RB; i += NG * NT) {
             const int l = i & (RB - 1), k = i / RB;
             const Cx<T> *b2 = bufs + l * ct_stride(M);
             const Cx<T> zk = b2[ct_pad(k & (M - 1))], zm = cconj(b2[ct_pad((M - k) & (M - 1))]);
@@ -286,8 +288,8 @@ k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__
 }
 
 // ------------------------------------------------------------------ pass C
-template <class T, int M, int RB, bool DYN>
-__global__ void __launch_bounds__(M / 8, 1)
+template <class T, int M, int RB, bool DYN, int NG = 2>
+__global__ void __launch_bounds__(NG * M / 16, 1)
 k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
                  const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twr, HessDims h,
                  int nbatch_band, Epilogue<T> ep, int *counter) {
@@ -310,7 +312,7 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
         const int band = batch / nbatch_band;
         const int row0 = (batch - band * nbatch_band) * RB;
 #pragma unroll 8
-        for (int i = threadIdx.x; i < (M + 1) * RB; i += 2 * NT) {
+        for (int i = threadIdx.x; i < (M + 1) * RB; i += NG * NT) {
             const int l = i & (RB - 1), k = i / RB;
             Cx<T> X = cx<T>((T)0, (T)0);
             if (row0 + l < h.nx) X = S[((long)band * h.nyo2 + k) * h.nx + row0 + l];
@@ -318,8 +320,8 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
         }
         __syncthreads();
 #pragma unroll 1
-        for (int ph = 0; ph < RB / 2; ++ph) {
-            const int l = 2 * ph + g, row = row0 + l;
+        for (int ph = 0; ph < RB / NG; ++ph) {
+            const int l = NG * ph + g, row = row0 + l;
             Cx<T> *buf = bufs + l * ct_stride(M);
             // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m])
             Cx<T> v[16];

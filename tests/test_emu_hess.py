@@ -56,6 +56,7 @@ def test_hess_golden(tag):
 @pmp("nx,ny,nxp,nyp", [(8, 6, 16, 32), (20, 40, 64, 128), (100, 64, 256, 128), (30, 200, 32, 512),
                              (6, 10, 4096, 64), (4, 10, 16, 8192), (5, 4, 8192, 32),
                              (5, 4, 16384, 32),                                    # column pass on k_hessf_cols1<8192>
+                             (4, 10, 16, 16384),                                   # row passes on the one-group kernels (M = 8192)
                              (10, 12, 1024, 1024), (7, 30, 2048, 1024)])   # fast path (hess_fast.cuh)
 def test_hess_oracle(dtype, nx, ny, nxp, nyp):
     if nxp == 16384 and dtype == np.float64:
