@@ -121,7 +121,9 @@ def test_psi_errors():
 @pmp("nx,ny,nxp,nyp", [(8, 6, 16, 32), (20, 40, 64, 128), (100, 64, 256, 128), (30, 200, 32, 512),
                         (6, 10, 4096, 64), (4, 10, 16, 8192), (512, 512, 1024, 1024),
                         (300, 500, 1024, 1024), (600, 700, 2048, 2048), (500, 1000, 1024, 2048),
-                        (1000, 300, 4096, 1024)])
+                        (1000, 300, 4096, 1024),
+                        (598, 700, 2048, 2048),      # nx % 4 == 2: last TMA row pair of a batch is out of bounds
+                        (599, 702, 2048, 2048)])     # odd nx: pass C without TMA / 16-byte copies
 def test_hess_vs_oracle(dtype, nx, ny, nxp, nyp):
     from pfb_b200.operators.psf import psf_convolve_cube
     from pfb_b200.operators.hessian import hessian_psf_cube
