@@ -83,6 +83,14 @@ int pfb_dual_update(const void *vp, void *v, const void *weight, void *u,
  * > n lets the caller run the split on one basis slab of a (nband, nbasis, ...)
  * array at a time, so that the all-reduce of basis b overlaps the kernels of
  * basis b+1. */
+/* Band-sharded 21m dual update without a coefficient-sized exchange: by linearity
+ * of Psi^T the cross-band sum is  S = vbar + sigma * ubar  with ubar = Psi^T(sum_b x_b)
+ * (one all-reduced IMAGE, analysed by every rank) and vbar = sum_b v_b of the previous
+ * iteration, which each rank carries itself because  sum_b v_b = f(S) * S.
+ *   v_b <- (vp_b + sigma v_b) f(S) for the nband local bands;  vbar <- f(S) S  (in place).
+ * vbar, ubar, weight: n elements; vp, v: (nband, n). */
+int pfb_dual_update_rec(const void *vp, void *v, void *vbar, const void *ubar, const void *weight,
+                        int nband, long long n, double lam, double sigma, int dtype, void *stream);
 int pfb_dual_partial(const void *vp, const void *v, void *bsum, int nband, long long n,
                      long long band_stride, double sigma, int mode, int dtype, void *stream);
 int pfb_dual_apply(const void *vp, void *v, const void *bsum, const void *weight,

@@ -33,6 +33,7 @@ _SIGS = {
     "pfb_profile_report": (c_int, [c_char_p, c_longlong]),
     "pfb_prox21": (c_int, [_P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
     "pfb_dual_update": (c_int, [_P, _P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
+    "pfb_dual_update_rec": (c_int, [_P, _P, _P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, _P]),
     "pfb_dual_partial": (c_int, [_P, _P, _P, c_int, c_longlong, c_longlong, c_double, c_int, c_int, _P]),
     "pfb_dual_apply": (c_int, [_P, _P, _P, _P, _P, c_int, c_longlong, c_longlong, c_double, c_double, c_int, c_int, _P]),
     "pfb_axpby": (c_int, [_P, c_double, _P, c_double, _P, c_longlong, c_int, _P]),

@@ -312,6 +312,64 @@ k_dual_apply(const T *vp, T *v, const T *__restrict__ bsum,
 }
 
 // ---------------------------------------------------------------------------
+// Band-sharded dual update WITHOUT a coefficient-sized exchange (21m / band-sum mode).
+// The analysis is linear and identical for every band, and the shrink factor f is
+// the same for all bands of a coefficient, so the cross-band sum obeys a recursion
+// every rank can run on its own:
+//     S_k   = sum_b (v_{k-1,b} + sigma Psi^T x_b) = Vbar_{k-1} + sigma Psi^T (sum_b x_b)
+//     Vbar_k = sum_b v_{k,b} = f_k S_k
+// Only xbar = sum_b x_b -- ONE image, nbasis x smaller than the coefficient slab of
+// pfb/prox/prox_21m.py:99 -- is all-reduced; ubar = Psi^T xbar is computed by every
+// rank.  This kernel:  S = vbar + sigma ubar;  f = shrink(S);  v_b <- (vp_b + sigma v_b) f
+// for the local bands;  vbar <- f S.  (The host re-synchronises vbar with an exact
+// all-reduce of sum_b v_b every few dozen iterations to bound rounding drift.)
+template <class T, int V, int NB>
+__global__ void __launch_bounds__(256, 2)
+k_dual_rec(const T *vp, T *v, T *vbar, const T *__restrict__ ubar, const T *__restrict__ w,
+           int nband, long n, double lam, double sigma) {
+    long nv = n / V;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+         i += (long)gridDim.x * blockDim.x) {
+        long k = i * V;
+        Pack<T, V> pa[NB > 0 ? NB : 1], pc[NB > 0 ? NB : 1];
+        if (NB > 0) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                pa[b] = ld<T, V>(vp + b * n + k);
+                pc[b] = ld<T, V>(v + b * n + k);
+            }
+        }
+        Pack<T, V> vb = ld<T, V>(vbar + k), ub = ld<T, V>(ubar + k), wk = ld<T, V>(w + k), so;
+        double f[V];
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            const double S = (double)vb.v[e] + sigma * (double)ub.v[e];
+            f[e] = shrink_factor(S, lam * (double)wk.v[e], 0);
+            so.v[e] = (T)(S * f[e]);
+        }
+        st<T, V>(vbar + k, so);
+        if (NB > 0) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                Pack<T, V> o;
+#pragma unroll
+                for (int e = 0; e < V; ++e)
+                    o.v[e] = (T)(((double)pa[b].v[e] + sigma * (double)pc[b].v[e]) * f[e]);
+                st<T, V>(v + b * n + k, o);
+            }
+        } else {
+            for (int b = 0; b < nband; ++b) {
+                Pack<T, V> a = ld<T, V>(vp + b * n + k), c = ld<T, V>(v + b * n + k), o;
+#pragma unroll
+                for (int e = 0; e < V; ++e)
+                    o.v[e] = (T)(((double)a.v[e] + sigma * (double)c.v[e]) * f[e]);
+                st<T, V>(v + b * n + k, o);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
 // out = a*x + b*y  (numexpr '2.0*v - vp', 'xp - tau*xout' of
 // pfb/opt/primal_dual.py:137,140 and the axpys of pfb/opt/pcg.py:92-104);
 // arithmetic in the array dtype (NumPy weak-scalar promotion).
@@ -642,6 +700,24 @@ static int dual_apply_t(const T *vp, T *v, const T *bsum, const T *w, T *u, int 
 }
 
 template <class T>
+static int dual_rec_t(const T *vp, T *v, T *vbar, const T *ubar, const T *w, int nband, long n,
+                      double lam, double sigma, cudaStream_t st) {
+    const int V = 16 / sizeof(T);
+    bool vec = (n % V == 0) && aligned16<T>(v) && aligned16<T>(vp) && aligned16<T>(vbar) &&
+               aligned16<T>(ubar) && aligned16<T>(w);
+    if (vec) {
+        dim3 g(stream_grid(n / V)), b(256);
+#define PFB_CALL(NB) launch(&k_dual_rec<T, V, NB>, g, b, 0, st, vp, v, vbar, ubar, w, nband, n, lam, sigma)
+        PFB_NB_SWITCH(nband, PFB_CALL)
+#undef PFB_CALL
+    } else {
+        launch(&k_dual_rec<T, 1, 0>, dim3(stream_grid(n)), dim3(256), 0, st, vp, v, vbar, ubar, w, nband, n, lam, sigma);
+    }
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+template <class T>
 static int axpby_t(T *out, double a, const T *x, double b, const T *y, long n, cudaStream_t st) {
     const int V = 16 / sizeof(T);
     bool vec = (n % V == 0) && aligned16<T>(out) && aligned16<T>(x) && aligned16<T>(y);
@@ -761,6 +837,17 @@ int pfb_dual_apply(const void *vp, void *v, const void *bsum, const void *weight
     PFB_DISPATCH(dtype,
                  dual_apply_t<float>((const float *)vp, (float *)v, (const float *)bsum, (const float *)weight, (float *)u, nband, n, band_stride, lam, sigma, mode, st),
                  dual_apply_t<double>((const double *)vp, (double *)v, (const double *)bsum, (const double *)weight, (double *)u, nband, n, band_stride, lam, sigma, mode, st));
+}
+
+int pfb_dual_update_rec(const void *vp, void *v, void *vbar, const void *ubar, const void *weight,
+                        int nband, long long n, double lam, double sigma, int dtype, void *stream) {
+    if (!vp || !v || !vbar || !ubar || !weight || nband < 1 || n < 0)
+        return fail(PFB_ERR_BAD_ARG, "pfb_dual_update_rec: bad argument");
+    if (n == 0) return PFB_OK;
+    cudaStream_t st = as_stream(stream);
+    PFB_DISPATCH(dtype,
+                 dual_rec_t<float>((const float *)vp, (float *)v, (float *)vbar, (const float *)ubar, (const float *)weight, nband, n, lam, sigma, st),
+                 dual_rec_t<double>((const double *)vp, (double *)v, (double *)vbar, (const double *)ubar, (const double *)weight, nband, n, lam, sigma, st));
 }
 
 int pfb_axpby(void *out, double a, const void *x, double b, const void *y, long long n,

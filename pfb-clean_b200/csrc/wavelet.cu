@@ -478,6 +478,16 @@ static int ensure_scratch(const pfb_psi_plan *cp) {
     return PFB_OK;
 }
 
+// Rows of coefficients per chunk of a streaming walk: long chunks amortise the warm-up rows of
+// the register history, but with few bands (one band per GPU when the cube is sharded 8 ways,
+// or the single band-sum image of pfb_dual_update_rec) they leave less than a wave of CTAs;
+// shorten them until there are about two waves.
+static int pick_nj(int c0, long ctas_per_chunk) {
+    int NJ = c0 >= 1024 ? 128 : (c0 >= 256 ? 64 : 32);
+    while (NJ > 32 && ctas_per_chunk * cdiv(c0, NJ) < 8L * kNumSM) NJ >>= 1;
+    return NJ;
+}
+
 // nat = false: alpha is the reference's slab cube; nat = true: alpha is the
 // natural-orientation layout (streaming kernels only).
 template <class T>
@@ -543,8 +553,8 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, bool nat, cuda
                     d.ldn = a.d[b].ldn; d.qs = a.d[b].qs; d.ld_out = a.d[b].ld_out;
                     d.off1 = a.d[b].off1;
                 }
-                int NJ = wC0 >= 1024 ? 128 : (wC0 >= 256 ? 64 : 32);
                 int SW = getenv("PFB_DWT_SW") ? atoi(getenv("PFB_DWT_SW")) : kStripNat;   // experiments only
+                int NJ = pick_nj(wC0, (long)p->nband * cdiv(cdiv(wC1, SW), kStreamWarps));
                 int dbg = getenv("PFB_DWT_DBG") ? atoi(getenv("PFB_DWT_DBG")) : 0;
                 int nstrip = cdiv(wC1, SW), nchunk = cdiv(wC0, NJ);
                 size_t sm2 = sizeof(T) * stream_ring_elems() * kStreamWarps;
@@ -562,8 +572,8 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, bool nat, cuda
                     }
             }
             if (wC0 == 0) continue;
-            int NJ = wC0 >= 1024 ? 128 : (wC0 >= 256 ? 64 : 32);
             const int SW = nat ? kStripNat : kStripOut;
+            int NJ = pick_nj(wC0, (long)p->nbasis * p->nband * cdiv(cdiv(wC1, SW), kStreamWarps));
             int nstrip = cdiv(wC1, SW), nchunk = cdiv(wC0, NJ);
             long ntask = (long)p->nband * nstrip * nchunk;      // per basis
             int dbg = getenv("PFB_DWT_DBG") ? atoi(getenv("PFB_DWT_DBG")) : 0;   // experiments only
@@ -678,9 +688,9 @@ static int psi_hdot_nat_t(const pfb_psi_plan *p, const T *cn, const T *cn2, T *x
         }
         if (l == 0) { mn0 = p->nx; mn1 = p->ny; }
         const int h0 = mn0 / 2, h1 = mn1 / 2;
-        const int NJ = h0 >= 1024 ? 128 : (h0 >= 256 ? 64 : 32);
-        const int nstrip = cdiv(h1, kSynStrip), nchunk = cdiv(h0, NJ);
         const int per_basis = l > 0;
+        const int NJ = pick_nj(h0, (long)(per_basis ? kSynSlots : 1) * p->nband * cdiv(cdiv(h1, kSynStrip), kSynWarps));
+        const int nstrip = cdiv(h1, kSynStrip), nchunk = cdiv(h0, NJ);
         const long nblk = (long)(per_basis ? kSynSlots : 1) * p->nband * nchunk * cdiv(nstrip, kSynWarps);
         const T *in = ((L - 1 - l) % 2 == 1) ? A : B;
         T *out = l == 0 ? xo : (((L - 1 - l) % 2 == 0) ? A : B);

@@ -140,6 +140,22 @@ def _dual_step(vp, v, lam, sigma, w, n, bsum, write_u=True):
                                               _dev.stream()))
 
 
+def _band_sum(t, out):
+    """out = sum over the local bands of t (nb, ...) -- pfb_dual_partial with sigma = 0."""
+    nb = t.shape[0]
+    m = t.numel() // nb
+    _lib.check(_lib.lib().pfb_dual_partial(_dev.ptr(t), _dev.ptr(t), _dev.ptr(out), nb, m, m, 0.0,
+                                           _lib.BAND_SUM, _dev.dcode(t), _dev.stream()))
+    return out
+
+
+def _dual_rec(vp, v, vbar, ubar, w, n, lam, sigma):
+    """pfb_dual_update_rec: local dual update from the recursively carried band sum."""
+    _lib.check(_lib.lib().pfb_dual_update_rec(_dev.ptr(vp), _dev.ptr(v), _dev.ptr(vbar), _dev.ptr(ubar),
+                                              _dev.ptr(w), v.shape[0], n, float(lam), float(sigma),
+                                              _dev.dcode(v), _dev.stream()))
+
+
 def _gap_index(psi_obj, device):
     """Flat indices (into nbasis*Nymax*Nxmax) of the slab cells Psi.dot never
     writes.  Found by running a 1-band analysis over a NaN-filled slab once."""
@@ -240,6 +256,25 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             if cand.can_fuse_primal():
                 fplan = cand
     primal_dual_optimised.last_fused = fplan is not None
+    # Band-sharded ranks, 21m prox: the cross-band sum of the dual update is carried by a
+    # recursion (include/pfb_b200.h, pfb_dual_update_rec) that needs the all-reduce of ONE image,
+    # sum_b xp_b, per iteration instead of the (nbasis x larger) coefficient slab; every rank
+    # analyses that image itself.  The exchange is issued right behind the primal step and hidden
+    # by the next PSF convolution.  The carried sum is re-synchronised exactly every
+    # PFB_PAR_RESYNC (default 64) iterations to bound rounding drift.
+    rec = nat and lin and parallel.active() and not os.environ.get("PFB_PAR_NOREC")
+    primal_dual_optimised.last_rec = bool(rec)
+    xbar_work = None
+    if rec:
+        P1 = getattr(P, "_one_band", None)
+        if P1 is None:
+            P1 = P._one_band = Psi(1, P.nx, P.ny, P.bases, P.nlevel, 1)
+        assert P1.nat_stride(_dev.dcode(va)) == vcur.shape[2]
+        xbar = torch.empty_like(xa[0])
+        ubar = torch.empty((1,) + tuple(vcur.shape[1:]), dtype=va.dtype, device=va.device)
+        vbar = torch.empty(tuple(vcur.shape[1:]), dtype=va.dtype, device=va.device)
+        parallel.allreduce_sum(_band_sum(vprev, vbar))
+        resync = int(os.environ.get("PFB_PAR_RESYNC", "64"))
 
     eps = 1.0
     numreweight = 0
@@ -254,10 +289,21 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         if nat:
             # not lin: the dual kernel leaves 2v - vp in the (dead) vp buffer: one coefficient
             # set for the synthesis to read, which is instruction-issue bound
+            if rec and xbar_work is None:
+                xbar_work = parallel.allreduce_sum_async(_band_sum(xprev, xbar))
             if not have_dot:
                 P.dot_nat(xprev, vcur)
             have_dot = False
-            if parallel.active() and not os.environ.get("PFB_PAR_NOOVERLAP"):
+            if rec:
+                g = gradient()                   # hides the exchange of xbar
+                if xbar_work is not None:
+                    xbar_work.wait()
+                xbar_work = None
+                P1.dot_nat(xbar[None], ubar)
+                if resync > 0 and k > 0 and k % resync == 0:
+                    parallel.allreduce_sum(_band_sum(vprev, vbar))
+                _dual_rec(vprev, vcur, vbar, ubar, w, n, lam, sigma)
+            elif parallel.active() and not os.environ.get("PFB_PAR_NOOVERLAP"):
                 # the PSF convolution hides the all-reduce of the band sums
                 works = _dual_begin(vprev, vcur, sigma, n, bsum)
                 g = gradient()
@@ -289,6 +335,9 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             parallel.allreduce_max(neg)
             xcur[:, neg.bool()] = 0
             norm_diff_terms(xcur, xprev, out=terms)
+        if rec and k + 1 < maxit:
+            # next iteration's exchange: sum of the new model over the local bands
+            xbar_work = parallel.allreduce_sum_async(_band_sum(xcur, xbar))
         if ahead and pos_kernel == positivity:
             ev.record()
             if k + 1 < maxit:
@@ -330,6 +379,8 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         if not k % report_freq and verbosity > 1:
             print(f"At iteration {k} eps = {eps:.3e}")
 
+    if xbar_work is not None:
+        xbar_work.wait()
     if verbosity:
         if k == maxit - 1 and not broke:
             print(f"Max iters reached. eps = {eps:.3e}")

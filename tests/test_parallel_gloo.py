@@ -58,12 +58,15 @@ def _worker(rank, world, port, q):
         res["pm_b"] = rel(b, g["pm_b"][sl])
         psi = Psi(nbl, nx, ny, bases, int(g["nlevel"]), 1)
         for pos in (1, 2):
+            # second run: exact re-synchronisation of the carried band sum every 3 iterations
+            os.environ["PFB_PAR_RESYNC"] = "64" if pos == 1 else "3"
             x = np.zeros_like(dirty)
             v = np.zeros((nbl, len(bases), psi.Nymax, psi.Nxmax))
             w = np.ones(v.shape[1:])
             primal_dual_optimised(x, v, float(g["lam"]), psi.hdot, psi.dot, float(g["hessnorm"]), None,
                                   w, None, Grad21(conv, dirty), nu=len(bases), tol=0.0, maxit=10,
                                   positivity=pos, verbosity=0)
+            res[f"rec{pos}"] = primal_dual_optimised.last_rec     # image-sized exchange (pfb_dual_update_rec)
             res[f"pd_x{pos}"] = rel(x, g[f"pdo_x_pos{pos}"][sl])
             res[f"pd_v{pos}"] = rel(v, g[f"pdo_v_pos{pos}"][sl])
         A = partial(hessian_psf_cube, None, None, None, None, psfhat, nyp, sigmainv=1e-3, wsum=None)
@@ -99,6 +102,7 @@ def test_band_sharded_two_ranks():
         assert "error" not in out[r], out[r].get("error")
         assert out[r]["pm_beta"] < 1e-12 and out[r]["pm_b"] < 1e-10, out[r]
         for pos in (1, 2):
+            assert out[r][f"rec{pos}"], out[r]
             assert out[r][f"pd_x{pos}"] < 1e-11, out[r]
             assert out[r][f"pd_v{pos}"] < 1e-11, out[r]
         assert out[r]["pcg_x"] < 1e-10, out[r]
