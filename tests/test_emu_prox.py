@@ -58,6 +58,19 @@ def test_prox_dual(dtype, nband, shape, mode):
             ok(L.pfb_dual_apply(ptr(vp[h:].copy()), ptr(vb), ptr(s), ptr(w), ptr(ub), nband - h, n, 0, lam, sigma, mode, dt(v), None))
             tol2 = tol if dtype == np.float64 else 5e-6   # fp32 slab sum
             assert rel(np.concatenate([va, vb]), exp) < tol2
+            # recursive form (pfb_dual_update_rec): the ranks share only vbar = sum_b vp_b and
+            # ubar = sum_b u_b (what Psi^T of the all-reduced band-sum image gives); afterwards
+            # the carried sum equals sum_b v_b of the updated dual
+            if mode == 0:
+                vbar0 = vp.astype(np.float64).sum(axis=0).astype(dtype)
+                ubar = v.astype(np.float64).sum(axis=0).astype(dtype)
+                va, vb = v[:h].copy(), v[h:].copy()
+                ba, bb = vbar0.copy(), vbar0.copy()
+                ok(L.pfb_dual_update_rec(ptr(vp[:h].copy()), ptr(va), ptr(ba), ptr(ubar), ptr(w), h, n, lam, sigma, dt(v), None))
+                ok(L.pfb_dual_update_rec(ptr(vp[h:].copy()), ptr(vb), ptr(bb), ptr(ubar), ptr(w), nband - h, n, lam, sigma, dt(v), None))
+                assert rel(np.concatenate([va, vb]), exp) < tol2
+                assert np.array_equal(ba, bb)
+                assert rel(ba, exp.astype(np.float64).sum(axis=0)) < (1e-12 if dtype == np.float64 else 5e-6)
             assert rel(np.concatenate([ua, ub]), 2 * exp - vp) < 10 * tol2
 
 

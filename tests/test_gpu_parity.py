@@ -60,6 +60,27 @@ def test_prox_dual_vs_oracle(dtype, nband, shape, mode):
         exp = v.copy()
         (ref.dual_update_numba_l2 if mode else ref.dual_update_numba)(vp, exp, lam, sigma=sigma, weight=w)
         assert rel(v2, exp) < tol
+        if mode == 0 and nband >= 2:
+            # recursive band-sharded form (pfb_dual_update_rec): two "ranks" that share only
+            # vbar = sum_b vp_b and ubar = sum_b u_b; the carried sum becomes sum_b v_b
+            from pfb_b200.opt.primal_dual import _dual_rec
+            dev = torch.device("cuda")
+            h, n = nband // 2, int(np.prod(shape))
+            vbar0 = torch.from_numpy(vp.astype(np.float64).sum(axis=0).astype(dtype)).to(dev)
+            ubar = torch.from_numpy(v.astype(np.float64).sum(axis=0).astype(dtype)).to(dev)
+            wd = torch.from_numpy(w).to(dev)
+            outs, bars = [], []
+            for sl in (slice(0, h), slice(h, nband)):
+                vpd = torch.from_numpy(np.ascontiguousarray(vp[sl])).to(dev)
+                vd = torch.from_numpy(np.ascontiguousarray(v[sl])).to(dev)
+                bar = vbar0.clone()
+                _dual_rec(vpd, vd, bar, ubar, wd, n, lam, sigma)
+                outs.append(vd.cpu().numpy())
+                bars.append(bar)
+            tol2 = tol if dtype == np.float64 else 5e-6        # fp32 band sums
+            assert rel(np.concatenate(outs), exp) < tol2
+            assert torch.equal(bars[0], bars[1])
+            assert rel(bars[0], exp.astype(np.float64).sum(axis=0)) < tol2
 
 
 def test_prox_zero_threshold_identity():
