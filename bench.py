@@ -315,6 +315,29 @@ def run_ours(a):
     stop.set()
     buf = ctypes.create_string_buffer(1 << 16)
     _lib.check(L.pfb_profile_report(buf, len(buf)))
+    # ---- secondary metric: PCG iterations/s on the same cube, outside the timed
+    # region: A = hessian_psf_cube(sigmainv = 1e-3), b = dirty, x0 = 0, fixed count, backtracking on
+    pcg_line = None
+    if not a.no_e2e:
+        from pfb_b200.operators.hessian import hessian_psf_cube
+        from pfb_b200.opt.pcg import pcg
+        A = partial(hessian_psf_cube, None, None, None, None, psfhat, nxp, sigmainv=1e-3)
+        x0 = torch.zeros_like(dirty)
+        npcg = 10
+        pcg(A, dirty, x0, tol=0.0, maxit=3, minit=3, verbosity=0)          # warm-up
+        barrier()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        pcg(A, dirty, x0, tol=0.0, maxit=npcg, minit=npcg, verbosity=0)
+        p1.record()
+        barrier()
+        pms = torch.tensor([p0.elapsed_time(p1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(pms, op=dist.ReduceOp.MAX)
+        pcg_line = {"metric": "pfb_pcg_iters_per_sec", "value": round(npcg / (float(pms) * 1e-3), 2),
+                    "unit": "iter/s", "iters": npcg, "ms_per_iter": round(float(pms) / npcg, 4),
+                    "note": "pcg(hessian_psf_cube sigmainv=1e-3, b=dirty, x0=0), device-resident, incl. setup A(x0)"}
+        del x0
     kern = {}
     for line in buf.value.decode().splitlines():
         nm, n, t = line.split("\t")
@@ -452,7 +475,7 @@ def finish_ours(a, env):
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
         "step_roofline": {"fused_compulsory_bytes_per_step_per_gpu": fused_iter,
                           "frac_of_hbm_peak": round(step_frac, 4)},
-        "kernels": kernels, "ops": ops, "cpu_baseline": cpu,
+        "kernels": kernels, "ops": ops, "pcg": g.get("pcg_line"), "cpu_baseline": cpu,
     }
     return line
 
