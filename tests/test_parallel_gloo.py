@@ -69,6 +69,20 @@ def _worker(rank, world, port, q):
             res[f"rec{pos}"] = primal_dual_optimised.last_rec     # image-sized exchange (pfb_dual_update_rec)
             res[f"pd_x{pos}"] = rel(x, g[f"pdo_x_pos{pos}"][sl])
             res[f"pd_v{pos}"] = rel(v, g[f"pdo_v_pos{pos}"][sl])
+        # fp32: the recursively carried band sum in single precision, 10 iterations
+        os.environ["PFB_PAR_RESYNC"] = "64"
+        g32 = np.load(os.path.join(HERE, "golden", "solve_f32.npz"))
+        psfhat32 = np.ascontiguousarray(g32["psfhat"][sl])
+        dirty32 = np.ascontiguousarray(g32["dirty"][sl])
+        conv32 = partial(psf_convolve_cube, None, None, np.empty_like(dirty32), psfhat32, nyp)
+        x = np.zeros_like(dirty32)
+        v = np.zeros((nbl, len(bases), psi.Nymax, psi.Nxmax), np.float32)
+        primal_dual_optimised(x, v, float(g32["lam"]), psi.hdot, psi.dot, float(g32["hessnorm"]), None,
+                              np.ones(v.shape[1:], np.float32), None, Grad21(conv32, dirty32),
+                              nu=len(bases), tol=0.0, maxit=10, positivity=1, verbosity=0)
+        res["rec32"] = primal_dual_optimised.last_rec
+        res["pd32_x"] = rel(x, g32["pdo_x_pos1"][sl])
+        res["pd32_v"] = rel(v, g32["pdo_v_pos1"][sl])
         A = partial(hessian_psf_cube, None, None, None, None, psfhat, nyp, sigmainv=1e-3, wsum=None)
         xs = pcg(A, dirty, np.zeros_like(dirty), M=None, tol=0.0, maxit=10, minit=10, verbosity=0)
         res["pcg_x"] = rel(xs, g["pcg_x"][sl])
@@ -106,3 +120,4 @@ def test_band_sharded_two_ranks():
             assert out[r][f"pd_x{pos}"] < 1e-11, out[r]
             assert out[r][f"pd_v{pos}"] < 1e-11, out[r]
         assert out[r]["pcg_x"] < 1e-10, out[r]
+        assert out[r]["rec32"] and out[r]["pd32_x"] < 1e-5 and out[r]["pd32_v"] < 1e-5, out[r]
