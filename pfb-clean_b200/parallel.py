@@ -11,8 +11,6 @@ The reference's distributed analogue is primal_dual_dist / get_ratio
 enable() switches the solvers in pfb_b200.opt to the sharded code path; every
 rank then passes its LOCAL bands to the solver.
 """
-import os
-
 import torch
 import torch.distributed as dist
 
@@ -55,8 +53,6 @@ def allreduce_sum_async(t):
     the work already queued on the current stream); returns a work handle whose
     .wait() makes the current stream wait for the result, or None when inactive."""
     if not active():
-        return None
-    if os.environ.get("PFB_PAR_NOAR"):      # timing experiments only (results are wrong)
         return None
     return dist.all_reduce(t, op=dist.ReduceOp.SUM, group=_STATE["group"], async_op=True)
 
