@@ -49,6 +49,11 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-bands", type=int, default=1)
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="skip the secondary lines (config 2 f32/f64, config 3 f64) of the N=1 run")
+    ap.add_argument("--no-parity", action="store_true",
+                    help="N>1: skip the sharded-vs-single-GPU parity check (parity_vs_n1)")
+    ap.add_argument("--parity-iters", type=int, default=10)
     ap.add_argument("--ncu-step", action="store_true",
                     help="profiling aid: run ONE iteration between cudaProfilerStart/Stop and exit "
                          "(use with ncu --profile-from-start off); prints no bench line")
@@ -157,6 +162,8 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi, fused=False):
         "k_dual": nb_local * (4 - lin) * C1 + C1,     # read vp,v ; write v (and u = 2v-vp if not lin) ; weight once
         "k_dual_partial": nb_local * 3 * C1 + C1,
         "k_dual_apply": nb_local * (4 - lin) * C1 + 2 * C1,   # read vp,v,bsum,w ; write v (,u)
+        # band-sharded recursion: read vp_b, u_b ; write v_b ; read Vbar, ubar, w ; write Vbar
+        "k_dual_rec": nb_local * 3 * C1 + 4 * C1,
         "k_hess_rows_fwd": nb_local * (P1 + S),
         "k_hess_cols": nb_local * (2 * S + psfhat),
         "k_hess_rows_inv": nb_local * (S + P1),
@@ -183,7 +190,7 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi, fused=False):
 
 
 def short_kernel_name(mangled):
-    for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_slab_to_nat", "k_nat_to_slab", "k_dual_partial", "k_dual_apply", "k_dual",
+    for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_slab_to_nat", "k_nat_to_slab", "k_dual_partial", "k_dual_apply", "k_dual_rec", "k_dual",
               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
               "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
               "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv", "k_pd_primal", "k_hess_red_final", "k_red_final",
@@ -202,6 +209,157 @@ def peaks():
 
 
 # ----------------------------------------------------------------- our arm
+class Problem:
+    """Synthetic minor-cycle problem for `bands` (global band indices) of an
+    nband x nx x nx cube on `dev`: psfhat, dirty, Psi plan, hessnorm, lam, weights.
+    Set-up only -- nothing here is inside a timed region."""
+
+    def __init__(self, torch, nband, nx, dtype, bands, dev, rank=0, world=1, hessnorm=None, lam=None):
+        from functools import partial
+        import numpy as np
+        import torch.distributed as dist
+        from pfb_b200.operators.psf import psf_convolve_cube
+        from pfb_b200.operators.psi import Psi
+        from pfb_b200.opt.primal_dual import Grad21
+        from pfb_b200.opt.power_method import power_method
+        self.torch = torch
+        self.rdt = rdt = torch.float32 if dtype == "f32" else torch.float64
+        self.s = 4 if dtype == "f32" else 8
+        self.nband, self.nx, self.nxp = nband, nx, 2 * nx
+        self.nbl = nbl = len(bands)
+        nxp = 2 * nx
+        cdt = torch.complex64 if self.s == 4 else torch.complex128
+        self.psfhat = torch.empty((nbl, nxp, nxp // 2 + 1), dtype=cdt, device=dev)
+        model = torch.empty((nbl, nx, nx), dtype=rdt, device=dev)
+        for i, b in enumerate(bands):
+            self.psfhat[i], model[i] = make_band_inputs(torch, b, nband, nx, rdt, dev)
+        torch.cuda.empty_cache()
+        self.xout = torch.empty_like(model)
+        self.conv = partial(psf_convolve_cube, None, None, self.xout, self.psfhat, nxp)
+        self.dirty = self.conv(model).clone()
+        dmax = self.dirty.max()
+        if world > 1:
+            dist.all_reduce(dmax, op=dist.ReduceOp.MAX)
+        for i, b in enumerate(bands):     # noise seeded per GLOBAL band: same cube whatever the sharding
+            gn = torch.Generator(device=dev).manual_seed(1000 + b)
+            self.dirty[i] += 1e-3 * dmax * torch.randn(self.dirty[i].shape, generator=gn, device=dev, dtype=rdt)
+        del model
+        self.psi = Psi(nbl, nx, nx, BASES, NLEVEL, 1, dtype=np.float32 if self.s == 4 else np.float64)
+        self.nbasis = len(BASES)
+        self.shape_v = (nbl, self.nbasis, self.psi.Nymax, self.psi.Nxmax)
+        if hessnorm is None:
+            # hessnorm = 1.05 * power_method(psf_convolve)  (pfb/workers/spotless.py:187-193)
+            b0 = torch.empty(self.dirty.shape, device=dev, dtype=rdt)
+            for i, b in enumerate(bands):
+                gb = torch.Generator(device=dev).manual_seed(7 + b)
+                b0[i] = torch.randn(b0[i].shape, generator=gb, device=dev, dtype=rdt)
+            beta, _ = power_method(self.conv, self.dirty.shape, b0=b0, tol=1e-3, maxit=100, verbosity=0)
+            del b0
+            hessnorm = 1.05 * float(beta)
+        self.hessnorm = hessnorm
+        if lam is None:
+            mfs = self.dirty.sum(dim=0)
+            if world > 1:
+                dist.all_reduce(mfs)
+            lam = 0.5 * float(mfs.std())
+            del mfs
+        self.lam = lam
+        self.w = torch.ones(self.shape_v[1:], dtype=rdt, device=dev)
+        self.grad = Grad21(self.conv, self.dirty)
+
+    def pd(self, x, v, nit, positivity=1):
+        from pfb_b200.opt.primal_dual import primal_dual_optimised
+        return primal_dual_optimised(x, v, self.lam, self.psi.hdot, self.psi.dot, self.hessnorm, None,
+                                     self.w, None, self.grad, nu=self.nbasis, tol=0.0, maxit=nit,
+                                     positivity=positivity, verbosity=0)
+
+    def zeros(self):
+        t = self.torch
+        return (t.zeros_like(self.dirty), t.zeros(self.shape_v, dtype=self.rdt, device=self.dirty.device))
+
+
+def secondary_config(torch, nband, nx, dtype, dev, steps, warmup):
+    """Device-resident PD it/s of another BASELINE.json configuration (N=1, outside the headline's
+    timed region): reported under "secondary"."""
+    from pfb_b200.operators import psf as _psf
+    _psf.clear_plan_cache()
+    torch.cuda.empty_cache()
+    P = Problem(torch, nband, nx, dtype, list(range(nband)), dev)
+    x, v = P.zeros()
+    P.pd(x, v, max(3, warmup))
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    P.pd(x, v, steps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    _, _, fused_iter = byte_model(nband, nx, P.s, P.psi.Nxmax, P.nbasis, False)
+    hbm, _ = peaks()
+    out = {"workload": f"{nband} bands {nx}x{nx}, PSF {2 * nx}x{2 * nx}", "dtype": dtype,
+           "value": round(1e3 / ms, 2), "unit": UNIT, "ms_per_step": round(ms, 4), "steps": steps,
+           "step_frac_of_hbm_peak": round(fused_iter / (ms * 1e-3) / 1e9 / hbm, 4)}
+    del P, x, v
+    _psf.clear_plan_cache()
+    torch.cuda.empty_cache()
+    return out
+
+
+def parity_vs_n1(torch, dist, a, P, rank, world, dev):
+    """N>1, outside the timed region: `iters` iterations from x0 = v0 = 0 on the band-sharded
+    path, gathered to rank 0, against the same iterations of the single-GPU path on the whole
+    cube on rank 0 (same psfhat / dirty / hessnorm / lam).  Relative L2 of model and dual."""
+    from pfb_b200 import parallel
+    from pfb_b200.opt.primal_dual import primal_dual_optimised
+    nit = a.parity_iters
+    x, v = P.zeros()
+    P.pd(x, v, nit)
+    path = "rec" if getattr(primal_dual_optimised, "last_rec", False) else "slab"
+
+    def gather(t):
+        out = torch.empty((world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=dev) if rank == 0 else None
+        parts = list(out.split(t.shape[0])) if rank == 0 else None
+        dist.gather(t.contiguous(), parts, dst=0)
+        return out
+    xs, vs = gather(x), gather(v)
+    psf_all = gather(torch.view_as_real(P.psfhat))
+    if rank == 0:
+        psf_all = torch.view_as_complex(psf_all)
+    dirty_all = gather(P.dirty)
+    del x, v
+    res = None
+    if rank == 0:
+        from functools import partial
+        import numpy as np
+        from pfb_b200.operators.psf import psf_convolve_cube
+        from pfb_b200.operators.psi import Psi
+        from pfb_b200.opt.primal_dual import Grad21
+        parallel.disable()
+        try:
+            nb = a.nband
+            psi = Psi(nb, a.nx, a.nx, BASES, NLEVEL, 1, dtype=np.float32 if P.s == 4 else np.float64)
+            xo = torch.empty_like(dirty_all)
+            conv = partial(psf_convolve_cube, None, None, xo, psf_all, 2 * a.nx)
+            x1 = torch.zeros_like(dirty_all)
+            v1 = torch.zeros((nb,) + tuple(P.shape_v[1:]), dtype=P.rdt, device=dev)
+            w1 = torch.ones(P.shape_v[1:], dtype=P.rdt, device=dev)
+            primal_dual_optimised(x1, v1, P.lam, psi.hdot, psi.dot, P.hessnorm, None, w1, None,
+                                  Grad21(conv, dirty_all), nu=P.nbasis, tol=0.0, maxit=nit,
+                                  positivity=1, verbosity=0)
+            torch.cuda.synchronize()
+
+            def rel(p, q):
+                return float(torch.linalg.vector_norm((p.double() - q.double()).view(-1)) /
+                             torch.linalg.vector_norm(q.double().view(-1)))
+            res = {"rel_l2_x": rel(xs, x1), "rel_l2_v": rel(vs, v1), "iters": nit, "path": path,
+                   "tol": 1e-5, "x_nonzero": bool(x1.any()),
+                   "note": "sharded primal_dual_optimised vs the single-GPU path on the whole cube (rank 0)"}
+        finally:
+            parallel.enable()
+    dist.barrier()
+    return res
+
+
 def run_ours(a):
     import ctypes
     from functools import partial
@@ -222,59 +380,20 @@ def run_ours(a):
 
     import pfb_b200  # noqa: F401
     from pfb_b200 import _lib, parallel
-    from pfb_b200.operators.psf import psf_convolve_cube
-    from pfb_b200.operators.psi import Psi
-    from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
-    from pfb_b200.opt.power_method import power_method
     L = _lib.lib()          # raises if libpfb_b200.so is missing: no fallback
     if world > 1:
         parallel.enable()
 
-    rdt = torch.float32 if a.dtype == "f32" else torch.float64
-    s = 4 if a.dtype == "f32" else 8
     nb, nx = a.nband, a.nx
     nxp = 2 * nx
     if nb % world:
         raise SystemExit("nband must be divisible by the number of GPUs")
     nbl = nb // world
-    bands = range(rank * nbl, (rank + 1) * nbl)
-
-    # ---- inputs (synthetic, seeded; generated per band to bound memory)
-    psfhat = torch.empty((nbl, nxp, nxp // 2 + 1), dtype=torch.complex64 if s == 4 else torch.complex128, device=dev)
-    model = torch.empty((nbl, nx, nx), dtype=rdt, device=dev)
-    for i, b in enumerate(bands):
-        psfhat[i], model[i] = make_band_inputs(torch, b, nb, nx, rdt, dev)
-    torch.cuda.empty_cache()
-    xout = torch.empty_like(model)
-    conv = partial(psf_convolve_cube, None, None, xout, psfhat, nxp)
-    dirty = conv(model).clone()
-    gn = torch.Generator(device=dev).manual_seed(1000 + rank)
-    dmax = dirty.max()
-    if world > 1:
-        dist.all_reduce(dmax, op=dist.ReduceOp.MAX)
-    dirty += 1e-3 * dmax * torch.randn(dirty.shape, generator=gn, device=dev, dtype=rdt)
-    del model
-
-    psi = Psi(nbl, nx, nx, BASES, NLEVEL, 1, dtype=np.float32 if s == 4 else np.float64)
-    nbasis = len(BASES)
-    shape_v = (nbl, nbasis, psi.Nymax, psi.Nxmax)
-    # hessnorm = 1.05 * power_method(psf_convolve)  (pfb/workers/spotless.py:187-193)
-    gb = torch.Generator(device=dev).manual_seed(7 + rank)
-    b0 = torch.randn(dirty.shape, generator=gb, device=dev, dtype=rdt)
-    beta, _ = power_method(conv, dirty.shape, b0=b0, tol=1e-3, maxit=100, verbosity=0)
-    del b0
-    hessnorm = 1.05 * float(beta)
-    mfs = dirty.sum(dim=0)
-    if world > 1:
-        dist.all_reduce(mfs)
-    lam = 0.5 * float(mfs.std())
-    del mfs
-    w = torch.ones(shape_v[1:], dtype=rdt, device=dev)
-    grad = Grad21(conv, dirty)
-
-    def pd(x, v, nit):
-        return primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, w, None, grad,
-                                     nu=nbasis, tol=0.0, maxit=nit, positivity=1, verbosity=0)
+    bands = list(range(rank * nbl, (rank + 1) * nbl))
+    P = Problem(torch, nb, nx, a.dtype, bands, dev, rank, world)
+    rdt, s, psi, nbasis, shape_v = P.rdt, P.s, P.psi, P.nbasis, P.shape_v
+    psfhat, dirty, hessnorm, lam = P.psfhat, P.dirty, P.hessnorm, P.lam
+    pd = P.pd
 
     def barrier():
         torch.cuda.synchronize()
@@ -283,8 +402,7 @@ def run_ours(a):
             torch.cuda.synchronize()
 
     # ---- device-resident timing (`value`)
-    x = torch.zeros_like(dirty)
-    v = torch.zeros(shape_v, dtype=rdt, device=dev)
+    x, v = P.zeros()
     pd(x, v, max(a.warmup, 3))                       # warm-up iterations (untimed)
     if a.ncu_step:
         torch.cuda.synchronize()
@@ -336,6 +454,7 @@ def run_ours(a):
             dist.all_reduce(pms, op=dist.ReduceOp.MAX)
         pcg_line = {"metric": "pfb_pcg_iters_per_sec", "value": round(npcg / (float(pms) * 1e-3), 2),
                     "unit": "iter/s", "iters": npcg, "ms_per_iter": round(float(pms) / npcg, 4),
+                    "path": getattr(pcg, "last_path", "host-loop"),
                     "note": "pcg(hessian_psf_cube sigmainv=1e-3, b=dirty, x0=0), device-resident, incl. setup A(x0)"}
         del x0
     kern = {}
@@ -345,6 +464,13 @@ def run_ours(a):
         c = kern.setdefault(k, [0, 0.0])
         c[0] += int(n)
         c[1] += float(t)
+    # ---- N>1: what the sharded path computes, against the single-GPU path (outside timing)
+    parity = None
+    if world > 1 and not a.no_parity:
+        del x, v
+        torch.cuda.empty_cache()
+        parity = parity_vs_n1(torch, dist, a, P, rank, world, dev)
+        x, v = P.zeros()
     return finish_ours(a, locals())
 
 
@@ -358,6 +484,7 @@ def finish_ours(a, env):
     world, rank, dev, rdt, s = g["world"], g["rank"], g["dev"], g["rdt"], g["s"]
     nb, nbl, nx, psi, nbasis = g["nb"], g["nbl"], g["nx"], g["psi"], g["nbasis"]
     pd, barrier, shape_v, dirty = g["pd"], g["barrier"], g["shape_v"], g["dirty"]
+    torch_ = torch
     ms_total, kern, launches = g["ms_total"], g["kern"], g["launches"]
     K = a.steps
     value = K / (ms_total * 1e-3)
@@ -408,9 +535,13 @@ def finish_ours(a, env):
     hbm, peak_src = peaks()
     fused_primal = "k_pd_primal" not in kern       # pfb_hess_apply_primal ran (primal step inside pass C)
     per_kernel, per_op, fused_iter = byte_model(nbl, nx, s, psi.Nxmax, nbasis, world > 1, fused_primal)
+    if "k_dual_rec" in kern:       # rec path: k_dual_partial is only the band-sum helper (no byte model)
+        per_kernel["k_dual_partial"] = None
     # dominant kernel = largest total device time in the timed region
     tot_k = sum(t for _, t in kern.values())
-    dom = max(kern.items(), key=lambda kv: kv[1][1])
+    modelled = {k: v for k, v in kern.items() if per_kernel.get(k) is not None or k in
+                ("k_dwt_level", "k_dwt_stream", "k_idwt_level", "k_idwt_stream")}
+    dom = max((modelled or kern).items(), key=lambda kv: kv[1][1])
     dname, (dn, dt_ms) = dom[0], dom[1]
     if per_kernel.get(dname) is not None:
         balg = per_kernel[dname]
@@ -447,7 +578,8 @@ def finish_ours(a, env):
               "psf_convolve": ["k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
                                "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
                                "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv"],
-              "dual_update": ["k_dual", "k_dual_partial", "k_dual_apply"],
+              "dual_update": (["k_dual", "k_dual_rec"] if "k_dual_rec" in kern
+                              else ["k_dual", "k_dual_partial", "k_dual_apply"]),
               "primal_update+eps": ["k_pd_primal"]}
     if fused_primal:
         groups["psf_convolve+primal_update"] = groups.pop("psf_convolve")
@@ -458,9 +590,23 @@ def finish_ours(a, env):
                        "frac": round(per_op[op] / (t * 1e-3) / 1e9 / hbm, 4)}
     step_frac = fused_iter / (ms_total * 1e-3 / K) / 1e9 / hbm
 
+    secondary = None
+    if world == 1 and not a.no_secondary and (nb, nx, a.dtype) == (8, 4096, "f32"):
+        for k_ in ("x", "v", "P", "psfhat", "dirty", "pd", "psi"):
+            g.pop(k_, None)
+        del pd, dirty, psi
+        import gc
+        gc.collect()
+        secondary = {}
+        for name, (nb2, nx2, dt2, st2) in {"config2_f32": (4, 2048, "f32", 50), "config2_f64": (4, 2048, "f64", 50),
+                                           "config3_f64": (8, 4096, "f64", 10)}.items():
+            try:
+                secondary[name] = secondary_config(torch_, nb2, nx2, dt2, dev, st2, 3)
+            except Exception as e:      # a secondary line must never cost the headline
+                secondary[name] = {"error": f"{type(e).__name__}: {e}"}
     cpu = None
     if not a.no_cpu_baseline and world == 1:
-        cpu = cpu_reference(a, steps=2, warmup=1)
+        cpu = cpu_reference(a, steps=2, warmup=1, nbs=a.cpu_sample_bands)
 
     clocks = summarise_clocks(g["rows"])
     line = {
@@ -476,54 +622,70 @@ def finish_ours(a, env):
         "step_roofline": {"fused_compulsory_bytes_per_step_per_gpu": fused_iter,
                           "frac_of_hbm_peak": round(step_frac, 4)},
         "kernels": kernels, "ops": ops, "pcg": g.get("pcg_line"), "cpu_baseline": cpu,
+        "secondary": secondary, "parity_vs_n1": g.get("parity"),
     }
     return line
 
 
 # ------------------------------------------------------- CPU reference arm
-def cpu_reference(a, steps, warmup):
+def cpu_reference(a, steps, warmup, nbs=1, full=False):
     """The reference's CPU algorithm for the same minor iteration, timed on the
     host cores: oracle/ref.py (numpy + OpenMP C restatement of the numba
     kernels, scipy.fft/pocketfft standing in for ducc0.fft) with every host
-    thread.  Bounded sample: `cpu_sample_bands` band(s) of the workload, scaled
-    by nband/sample (bands are independent apart from the cross-band sum)."""
+    thread.  `nbs` bands of the workload are timed (the bounded sample of the
+    cpu_baseline leg: 1 band, scaled by nband/nbs -- bands are independent apart
+    from the cross-band sum); `full` (the --impl reference arm) times ALL bands,
+    with the GPU arm's own input generator and a power-method hessnorm."""
     from functools import partial
     import numpy as np
-    import scipy.fft as sfft
+    import torch
     from oracle import ref
     ncores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(ncores))
-    nbs = max(1, min(a.cpu_sample_bands, a.nband))
+    # torchrun presets OMP_NUM_THREADS=1: force the thread count of the OpenMP oracle
+    # kernels explicitly (main() also re-executes the reference arm with the variable set,
+    # because libgomp and pocketfft's pool read it when they are loaded)
+    os.environ["OMP_NUM_THREADS"] = str(ncores)
+    torch.set_num_threads(ncores)
+    nbs = a.nband if full else max(1, min(nbs, a.nband))
     nx, nxp = a.nx, 2 * a.nx
     dt = np.float32 if a.dtype == "f32" else np.float64
     cdt = np.complex64 if a.dtype == "f32" else np.complex128
-    rng = np.random.default_rng(420)
-    u = sfft.fftfreq(nxp)[:, None] * nxp
-    vv = sfft.rfftfreq(nxp)[None, :] * nxp
+    rdt = torch.float32 if a.dtype == "f32" else torch.float64
     psfhat = np.empty((nbs, nxp, nxp // 2 + 1), cdt)
-    for b in range(nbs):
-        W = (1.0 + (np.sqrt(u * u + vv * vv) / (1 + 0.1 * b) / (0.05 * nxp)) ** 2) ** -1.5
-        W *= rng.random(W.shape) < 0.3
-        psf = sfft.irfft2(W, s=(nxp, nxp), workers=ncores)
-        psf /= psf[0, 0] * a.nband
-        psfhat[b] = sfft.rfft2(psf, workers=ncores)
-    del W, psf
-    model = np.zeros((nbs, nx, nx), dt)
-    idx = rng.integers(nx // 8, 7 * nx // 8, (75, 2))
-    model[:, idx[:, 0], idx[:, 1]] = (1 + np.exp(rng.standard_normal(75))).astype(dt)
+    model = np.empty((nbs, nx, nx), dt)
+    cpu = torch.device("cpu")
+    for b in range(nbs):           # same generator as the GPU arm (make_band_inputs), on the host
+        ph, m = make_band_inputs(torch, b, a.nband, nx, rdt, cpu)
+        psfhat[b], model[b] = ph.numpy(), m.numpy()
+        del ph, m
+    # torch's intra-op pool is not needed any more; it shares libgomp's global thread-count
+    # setting with the oracle, so the oracle's count is (re)set last
+    torch.set_num_threads(1)
+    ref.lib().orc_set_num_threads(ncores)
     xpad, xhat = np.empty((nbs, nxp, nxp), dt), np.empty(psfhat.shape, cdt)
     xo = np.empty_like(model)
     conv = partial(ref.psf_convolve_cube, xpad, xhat, xo, psfhat, nxp, nthreads=ncores)
     dirty = conv(model).copy()
+    rng = np.random.default_rng(420)
     dirty += (1e-3 * dirty.max() * rng.standard_normal(dirty.shape)).astype(dt)
+    del model
     psi = ref.Psi(nbs, nx, nx, BASES, NLEVEL, nthreads=ncores)
     shape_v = (nbs, len(BASES), psi.Nymax, psi.Nxmax)
     x, v = np.zeros_like(dirty), np.zeros(shape_v, dt)
     w = np.ones(shape_v[1:], dt)
     lam = 0.5 * float(np.std(dirty.sum(axis=0)))
+    if full:
+        # hessnorm = 1.05 * power_method(psf_convolve) as in the GPU arm (pfb/workers/spotless.py:187-193);
+        # capped at 20 iterations to bound the CPU time of the arm
+        b0 = rng.standard_normal(dirty.shape).astype(dt)
+        beta, _ = ref.power_method(lambda z: conv(z).copy(), dirty.shape, b0=b0, tol=1e-3, maxit=20, verbosity=0)
+        hessnorm, hn_src = 1.05 * float(beta), "1.05 * power_method(tol 1e-3, maxit 20)"
+        del b0
+    else:
+        hessnorm, hn_src = 1.05 * nbs / a.nband, "1.05 * nbs/nband (PSF peaks at 1/nband per band)"
 
     def run(nit):
-        ref.primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, 1.05 * nbs / a.nband, None, w, None,
+        ref.primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, w, None,
                                   lambda z: conv(z) - dirty, nu=len(BASES), tol=0.0, maxit=nit)
     run(max(1, warmup))
     t0 = time.perf_counter()
@@ -534,28 +696,32 @@ def cpu_reference(a, steps, warmup):
         nthr = int(ref.lib().orc_num_threads())
     except Exception:
         nthr = ncores
+    scaled = "" if nbs == a.nband else f", scaled x{nbs}/{a.nband}"
     return {"value": round(val, 5), "unit": UNIT, "cores": nthr, "kind": "port",
             "sample": (f"{steps} timed primal-dual iterations (after {max(1, warmup)} warm-up) on {nbs} of the "
-                       f"{a.nband} bands at full size {nx}x{nx}/PSF {nxp}x{nxp}, scaled x{nbs}/{a.nband}; "
-                       f"{dt_s:.2f} s per sampled iteration; oracle port (OpenMP C wavelets/prox, "
-                       f"scipy.fft workers={ncores} for ducc0.fft), host has {ncores} logical cores"),
-            "sec_per_sample_iter": round(dt_s, 3)}
+                       f"{a.nband} bands at full size {nx}x{nx}/PSF {nxp}x{nxp}{scaled}; "
+                       f"{dt_s:.2f} s per sampled iteration; oracle port (OpenMP C wavelets/prox on {nthr} threads, "
+                       f"scipy.fft workers={ncores} for ducc0.fft), host has {ncores} logical cores; "
+                       f"inputs from the GPU arm's generator; hessnorm = {hn_src}"),
+            "sec_per_sample_iter": round(dt_s, 3), "bands_timed": nbs, "extrapolated": nbs != a.nband}
 
 
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return None
-    steps = max(1, min(a.steps, 3))
-    warm = max(1, min(a.warmup, 1))
-    cpu = cpu_reference(a, steps=steps, warmup=warm)
+    steps = max(1, min(a.steps, 2))
+    warm = 1
+    cpu = cpu_reference(a, steps=steps, warmup=warm, full=True)
     return {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT,
             "n_gpus": a.gpus, "steps": steps, "warmup": warm,
             "ms_per_step": round(1e3 / cpu["value"], 2), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
             "config": {"workload": workload_name(a), "nband": a.nband, "nx": a.nx, "ny": a.nx,
-                       "nxp": 2 * a.nx, "nyp": 2 * a.nx, "bases": BASES, "nlevels": NLEVEL,
-                       "note": "steps/warmup capped at 3/1: one CPU iteration of the full cube takes tens of seconds"},
+                       "nxp": 2 * a.nx, "nyp": 2 * a.nx, "bases": BASES, "nlevels": NLEVEL, "positivity": 1,
+                       "init": "x0=0, v0=0, l1weight=1, tol=0 (fixed iteration count)",
+                       "note": ("all bands timed (no extrapolation); steps/warmup capped at 2/1: one CPU "
+                                "iteration of the full cube takes about 15 s")},
             "cpu_baseline": cpu,
             "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -563,6 +729,16 @@ def run_reference(a):
 
 def main():
     a = parse_args()
+    if a.impl == "reference":
+        # torchrun presets OMP_NUM_THREADS=1, which libgomp, pocketfft's pool and torch read when
+        # they are loaded: restart this process with the host's core count before importing them
+        if int(os.environ.get("RANK", "0")) != 0:
+            return
+        ncores = str(os.cpu_count() or 1)
+        if os.environ.get("OMP_NUM_THREADS") != ncores and not os.environ.get("PFB_BENCH_REEXEC"):
+            env = dict(os.environ, OMP_NUM_THREADS=ncores, PFB_BENCH_REEXEC="1")
+            sys.stdout.flush()
+            os.execve(sys.executable, [sys.executable] + sys.argv, env)
     # libraries (NCCL prints its version banner) must not pollute the one-line stdout contract:
     # everything written to fd 1 during the run goes to stderr, the JSON line to the real stdout
     sys.stdout.flush()
@@ -573,6 +749,10 @@ def main():
     os.dup2(real_stdout, 1)
     if line is not None:
         print(json.dumps(line), flush=True)
+    bad_parity = False
+    if line is not None and line.get("parity_vs_n1"):
+        pv = line["parity_vs_n1"]
+        bad_parity = not (max(pv["rel_l2_x"], pv["rel_l2_v"]) <= pv["tol"])
     try:
         import torch.distributed as dist
         if dist.is_initialized():
@@ -580,6 +760,9 @@ def main():
             dist.destroy_process_group()
     except Exception:
         pass
+    if bad_parity:
+        print("bench.py: the band-sharded result differs from the single-GPU result beyond 1e-5", file=sys.stderr)
+        sys.exit(3)
 
 
 if __name__ == "__main__":
