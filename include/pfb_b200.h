@@ -219,6 +219,17 @@ int pfb_hess_apply(pfb_hess_plan *plan, const void *x, const void *beam, int add
                    double sigmainv, int has_wsum, double wsum, void *out,
                    void *stream);
 
+/* PSFHAT creation on the device, pfb/operators/gridder.py:712-714:
+ *   psfhat = r2c(iFs(psf, axes=(0,1)), axes=(0,1), forward=True, inorm=0)   per band
+ * psf: (nband, nxp, nyp) real, peak at (nxp/2, nyp/2); psfhat: (nband, nxp, nyp/2+1) complex
+ * (reference layout, ready for pfb_hess_plan_set_psfhat).  nxp, nyp even (what
+ * pfb/workers/grid.py:276-284 produces) with the same factorisation limits as the Hessian
+ * plans.  The forward row / column passes of the Hessian kernels are reused; the ifftshift
+ * is applied as the exact sign (-1)^(kx+ky) on the spectrum.  Allocates and releases its own
+ * scratch (nband*nxp*(nyp/2+1) complex) and therefore synchronises the stream. */
+int pfb_psfhat_from_psf(const void *psf, int nband, int nxp, int nyp, int dtype, void *psfhat,
+                        void *stream);
+
 /* PSF convolution with the primal step of primal_dual_optimised
  * (pfb/opt/primal_dual.py:138-150) fused into its last pass:
  *   x = P+( xp - tau * (2 w - wprev + psf_convolve(xp) - data) ),  out2 as pfb_norm_diff
@@ -230,6 +241,23 @@ int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *plan);
 int pfb_hess_apply_primal(pfb_hess_plan *plan, const void *xp, const void *w, const void *wprev,
                           const void *data, double tau, int positivity, void *x, double *out2,
                           void *stream);
+
+/* ------------------------------------------------ worker glue (device) --
+ * Pieces of the spotless major cycle between two minor cycles
+ * (pfb/workers/spotless.py:217-260, 343-371), kept on the device so that model,
+ * residual and dual never bounce through the host.                           */
+
+/* stats3[3 s + {0,1,2}] = {mean, population std, max |x|} of segment s of x,
+ * x = (nseg, m); fp64 accumulation, fixed order, two passes for the std like
+ * numpy.  np.std(np.sum(psiHoutvar, axis=0), axis=(-1,-2)) = rms_comps with one
+ * segment per basis (spotless.py:219-223, 360-363); np.std / np.abs().max() of
+ * residual_mfs with one segment (spotless.py:229-230, 343-344). */
+int pfb_seg_stats(const void *x, int nseg, long long m, double *stats3, int dtype, void *stream);
+/* l1reweight_func, pfb/utils/misc.py:1070-1080, after the band sum:
+ * weight[b][i] = (1 + rmsfactor) / (1 + |bsum[b][i]|^alpha / rms_comps[b]^alpha),
+ * bsum, weight = (nbasis, nslab), rms_comps = (nbasis) in the array precision. */
+int pfb_l1reweight(const void *bsum, const void *rms_comps, int nbasis, long long nslab,
+                   double rmsfactor, double alpha, void *weight, int dtype, void *stream);
 
 #ifdef __cplusplus
 }

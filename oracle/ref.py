@@ -480,3 +480,36 @@ def l1reweight_func(psiH, outvar, rmsfactor, rms_comps, model, alpha=4):
     psiH(model, outvar)
     mcomps = np.abs(np.sum(outvar, axis=0))
     return (1 + rmsfactor) / (1 + mcomps**alpha / rms_comps**alpha)
+
+
+# ------------------------------------------------- worker glue
+def psfhat_from_psf(psf, nthreads=1):
+    """pfb/operators/gridder.py:712-714: psfhat = r2c(iFs(psf, axes=(0,1)), axes=(0,1),
+    forward=True, inorm=0) per band; psf (nband, nxp, nyp) real."""
+    out = sfft.rfftn(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2), workers=nthreads)
+    return out.astype(np.complex64 if _is32(psf) else np.complex128)
+
+
+def make_data(residual, model, psf_convolve):
+    """pfb/workers/spotless.py:259: data = residual + psf_convolve(model)"""
+    return residual + psf_convolve(model)
+
+
+def residual_stats(residual):
+    """pfb/workers/spotless.py:153-157, 229-230, 343-344"""
+    residual_mfs = np.sum(residual, axis=0)
+    return np.std(residual_mfs), np.abs(residual_mfs).max(), residual_mfs
+
+
+def rms_comps(psi, residual, wsum, wsums, pix_per_beam, psiHoutvar):
+    """pfb/workers/spotless.py:214-223 (and :356-363)"""
+    fsel = wsums > 0
+    tmp2 = residual.copy()
+    tmp2[fsel] *= wsum / wsums[fsel, None, None]
+    psi.dot((tmp2 / pix_per_beam).astype(residual.dtype), psiHoutvar)
+    return np.std(np.sum(psiHoutvar, axis=0), axis=(-1, -2))[:, None, None]
+
+
+def model_eps(model, modelp):
+    """pfb/workers/spotless.py:345"""
+    return np.linalg.norm(model - modelp) / np.linalg.norm(model)

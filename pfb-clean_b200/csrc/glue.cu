@@ -1,0 +1,173 @@
+// Worker glue of the spotless major cycle on the device:
+// the pieces of pfb/workers/spotless.py that sit between two minor cycles and
+// would otherwise bounce the cube through the host.
+//
+//   pfb_l1reweight : w = (1 + rmsfactor) / (1 + |S|^alpha / rms_b^alpha)
+//                    pfb/utils/misc.py:1070-1080 (S = band-summed coefficients)
+//   pfb_seg_stats  : per segment mean, population std and max |x| in fp64
+//                    (np.std(..., axis=(-1,-2)) of rms_comps, spotless.py:219-223;
+//                    np.std / np.abs().max() of residual_mfs, spotless.py:229-230,343-344)
+//
+// Streaming reductions (two passes for the std, like numpy): grid = multiple of
+// the SM count, fp64 accumulation in a fixed order (deterministic).
+#include "common.cuh"
+
+namespace pfb {
+
+#ifdef PFB_EMU
+static const int kSegBlocks = 2;
+#else
+static const int kSegBlocks = kNumSM * 2;     // CTAs per segment
+#endif
+
+__device__ __forceinline__ double g_warp_sum(double x) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    return x;
+}
+__device__ __forceinline__ double g_warp_max(double x) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x = fmax(x, __shfl_down_sync(0xffffffffu, x, o));
+    return x;
+}
+
+// pass 1 (PASS = 0): part[seg][blk] = {sum x, max |x|}
+// pass 2 (PASS = 1): part[seg][blk] = {sum (x - mean_seg)^2, unused}; mean from stats[3 seg]
+template <class T, int PASS>
+__global__ void __launch_bounds__(256)
+k_seg_stats(const T *__restrict__ x, long m, const double *__restrict__ stats, double *part) {
+    const int seg = blockIdx.y;
+    const T *xs = x + (long)seg * m;
+    const double mean = PASS ? stats[3 * seg] : 0.0;
+    double a = 0.0, b = 0.0;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long)gridDim.x * blockDim.x) {
+        const double v = (double)xs[i];
+        if (PASS == 0) { a += v; b = fmax(b, fabs(v)); }
+        else { const double d = v - mean; a += d * d; }
+    }
+    __shared__ double sh[2][32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    a = g_warp_sum(a);
+    b = g_warp_max(b);
+    if (lane == 0) { sh[0][wid] = a; sh[1][wid] = b; }
+    __syncthreads();
+    if (wid == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        a = lane < nw ? sh[0][lane] : 0.0;
+        b = lane < nw ? sh[1][lane] : 0.0;
+        a = g_warp_sum(a);
+        b = g_warp_max(b);
+        if (lane == 0) {
+            part[2 * ((long)seg * gridDim.x + blockIdx.x)] = a;
+            part[2 * ((long)seg * gridDim.x + blockIdx.x) + 1] = b;
+        }
+    }
+}
+
+// one warp per segment, fixed order.  PASS 0: stats[3s] = mean, stats[3s+2] = absmax;
+// PASS 1: stats[3s+1] = sqrt(sum / m)
+template <int PASS>
+__global__ void k_seg_final(const double *__restrict__ part, int nblk, long m, double *stats) {
+    const int seg = blockIdx.x;
+    double a = 0.0, b = 0.0;
+    for (int c = threadIdx.x; c < nblk; c += 32) {
+        a += part[2 * ((long)seg * nblk + c)];
+        b = fmax(b, part[2 * ((long)seg * nblk + c) + 1]);
+    }
+    a = g_warp_sum(a);
+    b = g_warp_max(b);
+    if (threadIdx.x == 0) {
+        if (PASS == 0) { stats[3 * seg] = a / (double)m; stats[3 * seg + 2] = b; }
+        else stats[3 * seg + 1] = sqrt(a / (double)m);
+    }
+}
+
+__device__ __forceinline__ float tpow(float a, float b) { return powf(a, b); }
+__device__ __forceinline__ double tpow(double a, double b) { return pow(a, b); }
+
+// w[b][i] = (1 + rmsfactor) / (1 + |s[b][i]|^alpha / rms[b]^alpha); arithmetic in the array
+// precision like numpy (`mcomps**alpha / rms_comps**alpha` on fp32 arrays stays fp32)
+template <class T>
+__global__ void __launch_bounds__(256)
+k_l1reweight(const T *__restrict__ s, const T *__restrict__ rms, long nslab, T rmsfactor, T alpha,
+             T *__restrict__ w) {
+    const int basis = blockIdx.y;
+    const T ra = tpow(rms[basis], alpha);
+    const T *sb = s + (long)basis * nslab;
+    T *wb = w + (long)basis * nslab;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nslab; i += (long)gridDim.x * blockDim.x) {
+        const T mc = fabs(sb[i]);
+        wb[i] = ((T)1 + rmsfactor) / ((T)1 + tpow(mc, alpha) / ra);
+    }
+}
+
+static double *g_spart = nullptr;
+static long g_spart_n = 0;
+
+static int ensure_spart(long n) {
+    if (g_spart_n < n) {
+        if (g_spart) cudaFree(g_spart);
+        g_spart = nullptr;
+        g_spart_n = 0;
+        if (cudaMalloc((void **)&g_spart, sizeof(double) * n) != cudaSuccess)
+            return fail(PFB_ERR_ALLOC, "cudaMalloc of the statistics workspace failed");
+        g_spart_n = n;
+    }
+    return PFB_OK;
+}
+
+template <class T>
+static int seg_stats_t(const T *x, int nseg, long m, double *stats, cudaStream_t st) {
+    long nb = (m + 255) / 256;
+    const int blk = (int)(nb < kSegBlocks ? (nb < 1 ? 1 : nb) : kSegBlocks);
+    if (int rc = ensure_spart(2L * nseg * blk)) return rc;
+    launch(&k_seg_stats<T, 0>, dim3(blk, nseg), dim3(256), 0, st, x, m, (const double *)stats, g_spart);
+    PFB_CHECK_LAUNCH();
+    launch(&k_seg_final<0>, dim3(nseg), dim3(32), 0, st, (const double *)g_spart, blk, m, stats);
+    PFB_CHECK_LAUNCH();
+    launch(&k_seg_stats<T, 1>, dim3(blk, nseg), dim3(256), 0, st, x, m, (const double *)stats, g_spart);
+    PFB_CHECK_LAUNCH();
+    launch(&k_seg_final<1>, dim3(nseg), dim3(32), 0, st, (const double *)g_spart, blk, m, stats);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+template <class T>
+static int l1reweight_t(const T *s, const T *rms, int nbasis, long nslab, double rmsfactor, double alpha,
+                        T *w, cudaStream_t st) {
+    long nb = (nslab + 255) / 256;
+    const int blk = (int)(nb < kNumSM * 8 ? (nb < 1 ? 1 : nb) : kNumSM * 8);
+    launch(&k_l1reweight<T>, dim3(blk, nbasis), dim3(256), 0, st, s, rms, nslab, (T)rmsfactor, (T)alpha, w);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+}  // namespace pfb
+
+using namespace pfb;
+
+extern "C" {
+
+int pfb_seg_stats(const void *x, int nseg, long long m, double *stats3, int dtype, void *stream) {
+    if (!x || !stats3 || nseg < 1 || m < 1) return fail(PFB_ERR_BAD_ARG, "pfb_seg_stats: bad argument");
+    cudaStream_t st = as_stream(stream);
+    if (dtype == PFB_F32) return seg_stats_t<float>((const float *)x, nseg, (long)m, stats3, st);
+    if (dtype == PFB_F64) return seg_stats_t<double>((const double *)x, nseg, (long)m, stats3, st);
+    return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+}
+
+int pfb_l1reweight(const void *bsum, const void *rms_comps, int nbasis, long long nslab, double rmsfactor,
+                   double alpha, void *weight, int dtype, void *stream) {
+    if (!bsum || !rms_comps || !weight || nbasis < 1 || nslab < 1)
+        return fail(PFB_ERR_BAD_ARG, "pfb_l1reweight: bad argument");
+    cudaStream_t st = as_stream(stream);
+    if (dtype == PFB_F32)
+        return l1reweight_t<float>((const float *)bsum, (const float *)rms_comps, nbasis, (long)nslab, rmsfactor,
+                                   alpha, (float *)weight, st);
+    if (dtype == PFB_F64)
+        return l1reweight_t<double>((const double *)bsum, (const double *)rms_comps, nbasis, (long)nslab,
+                                    rmsfactor, alpha, (double *)weight, st);
+    return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+}
+
+}  // extern "C"

@@ -164,6 +164,60 @@ __global__ void __launch_bounds__(MAXT) k_hess_rows_inv(const Cx<T> *__restrict_
     }
 }
 
+// PSFHAT creation (pfb/operators/gridder.py:712-714, psfhat = r2c(iFs(psf))): column pass,
+// forward only.  S holds the row transforms of the UNSHIFTED psf (pass A over all nxp rows);
+// the ifftshift by (nxp/2, nyp/2) is the sign (-1)^(kx + ky) on the spectrum (both sizes even),
+// which is exact.  In place: line[kx] = sign * FFT_nxp(line)[kx].
+template <class T, int MAXT>
+__global__ void __launch_bounds__(MAXT) k_psf_cols_fwd(Cx<T> *S, const Cx<T> *__restrict__ tw,
+                                                       FftDesc d, HessDims h) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *smem = reinterpret_cast<Cx<T> *>(raw);
+    const int NT = d.NT;
+    const int lc = threadIdx.x / NT, t = threadIdx.x - lc * NT;
+    const int band = blockIdx.y;
+    const int col = blockIdx.x * h.R + lc;
+    const bool live = col < h.nyo2;
+    Cx<T> *buf = smem + (long)lc * fft_smem_elems(h.nxp);
+    Cx<T> *line = S + ((long)band * h.nyo2 + (live ? col : 0)) * h.nx;
+    Cx<T> v[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        int i = t + e * NT;
+        v[e] = (live && i < h.nx) ? line[i] : cx<T>((T)0, (T)0);
+    }
+    fft_run<T, -1>(v, d, t, buf, tw);
+    if (live) {
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            int i = t + e * NT;
+            const T sg = ((i + col) & 1) ? (T)-1 : (T)1;
+            if (i < h.nx) line[i] = cx<T>(sg * v[e].x, sg * v[e].y);
+        }
+    }
+}
+
+// same for padded sizes that are not powers of two (hess_mixed.cuh machinery, N = nxp)
+template <class T>
+__global__ void __launch_bounds__(512)
+k_psfm_cols_fwd(Cx<T> *S, const Cx<T> *__restrict__ tw, const Cx<T> *__restrict__ roots, MxDesc d,
+                HessDims h) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
+    const int N = d.N;
+    Cx<T> *A = rt + kMxHead, *B = A + N;
+    const int band = blockIdx.y, col = blockIdx.x;
+    Cx<T> *line = S + ((long)band * h.nyo2 + col) * h.nx;
+    mx_load_tables(rt, roots, tw, N);
+    for (int n = threadIdx.x; n < N; n += blockDim.x) A[n] = n < h.nx ? line[n] : cx<T>((T)0, (T)0);
+    __syncthreads();
+    const Cx<T> *c = mx_fft<T, -1>(A, B, 1, d, rt + 40, rt);
+    for (int n = threadIdx.x; n < h.nx; n += blockDim.x) {
+        const T sg = ((n + col) & 1) ? (T)-1 : (T)1;
+        line[n] = cx<T>(sg * c[n].x, sg * c[n].y);
+    }
+}
+
 // psfhat (nband, nxp, nyo2) -> psfT (nband, nyo2, nxp) * scale
 template <class T>
 __global__ void k_psfhat_prepare(const Cx<T> *__restrict__ in, Cx<T> *__restrict__ out,
@@ -246,6 +300,14 @@ static int hess_set_psf_t(pfb_hess_plan *p, const void *psfhat, cudaStream_t st)
     const HessDims &h = p->h;
     dim3 grid(cdiv(h.nyo2, 32), cdiv(h.nxp, 32), h.nband), block(32, 8);
     T scale = (T)(1.0 / ((double)h.nxp * (double)h.nyp));
+    if (!p->psfT) {      // allocated on first use: a plan made only for pfb_psfhat_from_psf never needs it
+        const size_t sP = 2 * sizeof(T) * (size_t)h.nband * h.nyo2 * h.nxp;
+        if (cudaMalloc(&p->psfT, sP) != cudaSuccess) {
+            cudaGetLastError();
+            p->psfT = nullptr;
+            return fail(PFB_ERR_ALLOC, "hessian plan: allocation of the transposed psfhat failed (%zu bytes)", sP);
+        }
+    }
     launch(&k_psfhat_prepare<T>, grid, block, 0, st, (const Cx<T> *)psfhat, (Cx<T> *)p->psfT,
            h.nxp, h.nyo2, scale, p->deint);
     PFB_CHECK_LAUNCH();
@@ -674,12 +736,57 @@ static int hess_plan_create_mixed(pfb_hess_plan **out, int nband, int nx, int ny
     bool good = upload(&p->mtwM, mx_tw_entries(M), two(M)) && upload(&p->mtwC, mx_tw_entries(Nc), two(Nc)) &&
                 upload(&p->twr, M + 1, lin(nyp)) && upload(&p->modg, std::max(H, 1), lin(nxp)) &&
                 upload(&p->mroots, kMxRoots, root) &&
-                cudaMalloc(&p->S, sS) == cudaSuccess && cudaMalloc(&p->psfT, sP) == cudaSuccess;
+                cudaMalloc(&p->S, sS) == cudaSuccess;
     if (!good) {
         pfb_hess_plan_destroy(p);
         return fail(PFB_ERR_ALLOC, "hessian plan (mixed radix) allocation failed (%zu + %zu bytes)", sS, sP);
     }
     *out = p;
+    return PFB_OK;
+}
+
+// psfhat = r2c(ifftshift(psf)) on a plan created with nx = nxp, ny = nyp (all rows / columns live)
+template <class T>
+static int psfhat_from_psf_t(pfb_hess_plan *p, const T *psf, Cx<T> *out, cudaStream_t st) {
+    const HessDims &h0 = p->h;
+    Cx<T> *S = (Cx<T> *)p->S;
+    if (p->mixed) {
+        HessDims h = h0;
+        h.R = p->Lrow;
+        const size_t cs = sizeof(Cx<T>);
+        const size_t smr = mx_smem_bytes(h.M, h.R, cs), smc = mx_smem_bytes(p->mcol.N, 1, cs);
+        auto nthr = [](long work) { return work >= 2048 ? 512 : work >= 512 ? 256 : 128; };
+        const int tr = nthr((long)h.M * h.R / 4), tc = nthr(p->mcol.N / 4);
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_fwd<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
+        launch(&k_hessm_rows_fwd<T>, dim3(cdiv(h.nx, h.R), h.nband), dim3(tr), smr, st, psf, (const T *)nullptr, S,
+               (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h);
+        PFB_CHECK_LAUNCH();
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_psfm_cols_fwd<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));
+        launch(&k_psfm_cols_fwd<T>, dim3(h.nyo2, h.nband), dim3(tc), smc, st, S, (const Cx<T> *)p->mtwC,
+               (const Cx<T> *)p->mroots, p->mcol, h);
+        PFB_CHECK_LAUNCH();
+    } else {
+        const Cx<T> *tw = (const Cx<T> *)p->tw;
+        {
+            HessDims h = h0;
+            h.R = p->Rrow;
+            size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.M) * h.R;
+            int nthr = p->drow.NT * h.R;
+            PFB_BY_THREADS(nthr, k_hess_rows_fwd, smem, dim3(cdiv(h.nx, h.R), h.nband), st,
+                           psf, (const T *)nullptr, S, tw, p->drow, h);
+        }
+        {
+            HessDims h = h0;
+            h.R = p->Rcol;
+            size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.nxp) * h.R;
+            int nthr = p->dcol.NT * h.R;
+            PFB_BY_THREADS(nthr, k_psf_cols_fwd, smem, dim3(cdiv(h.nyo2, h.R), h.nband), st, S, tw, p->dcol, h);
+        }
+    }
+    // S (nband, nyo2, nxp) -> psfhat (nband, nxp, nyo2): the transposing kernel with the roles swapped
+    dim3 grid(cdiv(h0.nxp, 32), cdiv(h0.nyo2, 32), h0.nband), block(32, 8);
+    launch(&k_psfhat_prepare<T>, grid, block, 0, st, (const Cx<T> *)S, out, h0.nyo2, h0.nxp, (T)1, 0);
+    PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
 
@@ -721,15 +828,14 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
         else { ((double *)twh.data())[2 * m] = c; ((double *)twh.data())[2 * m + 1] = s; }
     }
     size_t sS = cs * (size_t)nband * h.nyo2 * nx, sP = cs * (size_t)nband * h.nyo2 * nxp;
-    if (cudaMalloc(&p->tw, twh.size()) != cudaSuccess || cudaMalloc(&p->S, sS) != cudaSuccess ||
-        cudaMalloc(&p->psfT, sP) != cudaSuccess) {
+    if (cudaMalloc(&p->tw, twh.size()) != cudaSuccess || cudaMalloc(&p->S, sS) != cudaSuccess) {
         if (p->tw) cudaFree(p->tw);
         if (p->S) cudaFree(p->S);
         delete p;
         return fail(PFB_ERR_ALLOC, "hessian plan allocation failed (%zu + %zu bytes)", sS, sP);
     }
     if (cudaMemcpy(p->tw, twh.data(), twh.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
-        cudaFree(p->tw); cudaFree(p->S); cudaFree(p->psfT);
+        cudaFree(p->tw); cudaFree(p->S);
         delete p;
         return fail(PFB_ERR_CUDA, "twiddle upload failed");
     }
@@ -886,6 +992,24 @@ int pfb_hess_apply(pfb_hess_plan *p, const void *x, const void *beam, int add_x,
     return hess_apply_t<double>(p, (const double *)x, (const double *)beam, (const double *)beam,
                                 add_x ? (const double *)x : nullptr, sigmainv, has_wsum, wsum,
                                 (double *)out, st);
+}
+
+int pfb_psfhat_from_psf(const void *psf, int nband, int nxp, int nyp, int dtype, void *psfhat,
+                        void *stream) {
+    if (!psf || !psfhat || nband < 1 || nxp < 2 || nyp < 2 || (dtype != PFB_F32 && dtype != PFB_F64))
+        return fail(PFB_ERR_BAD_ARG, "pfb_psfhat_from_psf: bad argument");
+    if ((nxp | nyp) & 1)
+        return fail(PFB_ERR_FFT_SIZE, "pfb_psfhat_from_psf: padded sizes (%d,%d) must be even", nxp, nyp);
+    pfb_hess_plan *p = nullptr;
+    if (int rc = pfb_hess_plan_create(&p, nband, nxp, nyp, nxp, nyp, dtype)) return rc;
+    cudaStream_t st = as_stream(stream);
+    int rc = dtype == PFB_F32 ? psfhat_from_psf_t<float>(p, (const float *)psf, (Cx<float> *)psfhat, st)
+                              : psfhat_from_psf_t<double>(p, (const double *)psf, (Cx<double> *)psfhat, st);
+    // the plan's scratch is released here, so the stream is drained first
+    if (rc == PFB_OK && cudaStreamSynchronize(st) != cudaSuccess)
+        rc = fail(PFB_ERR_CUDA, "pfb_psfhat_from_psf: stream synchronise failed");
+    pfb_hess_plan_destroy(p);
+    return rc;
 }
 
 int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *p) {

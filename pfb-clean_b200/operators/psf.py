@@ -132,3 +132,22 @@ def psf_convolve_slice(xpad, xhat, xout, psfhat, lastsize, x, nthreads=1):
 def psf_convolve_cube(xpad, xhat, xout, psfhat, lastsize, x, nthreads=1):
     """pfb/operators/psf.py:32-56: xout = crop(irfft2(rfft2(pad(x)) * psfhat))."""
     return _convolve(psfhat, lastsize, x, xout)
+
+
+def psfhat_from_psf(psf):
+    """psfhat = r2c(iFs(psf, axes=(0, 1)), axes=(0, 1), forward=True, inorm=0) per band
+    (pfb/operators/gridder.py:712-714) on the device: psf (nband, nxp, nyp) or (nxp, nyp) real
+    with its peak at (nxp//2, nyp//2) -> complex (.., nxp, nyp//2 + 1), numpy in -> numpy out,
+    CUDA tensor in -> CUDA tensor out.  Forward-only use of the Hessian's own FFT passes."""
+    pd = _dev.to_dev(psf)
+    if pd.dim() not in (2, 3):
+        raise ValueError("psf must be (nxp, nyp) or (nband, nxp, nyp)")
+    p3 = pd if pd.dim() == 3 else pd[None]
+    nband, nxp, nyp = p3.shape
+    cdt = torch.complex64 if p3.dtype == torch.float32 else torch.complex128
+    out = torch.empty((nband, nxp, nyp // 2 + 1), dtype=cdt, device=p3.device)
+    _lib.check(_lib.lib().pfb_psfhat_from_psf(_dev.ptr(p3), nband, nxp, nyp, _dev.dcode(p3), _dev.ptr(out),
+                                              _dev.stream()))
+    if pd.dim() == 2:
+        out = out[0]
+    return _dev.like(psf, out)

@@ -5,6 +5,7 @@ tiled DWT/IDWT kernels of csrc/wavelet.cu.  Coefficient layout, sizes
 "cells outside the pyramid are never written" behaviour are the reference's.
 """
 import ctypes
+import weakref
 
 import numpy as np
 import torch
@@ -12,6 +13,20 @@ import torch
 from .. import _dev, _lib
 
 _BASIS_ID = {"self": 0, "db1": 1, "db2": 2, "db3": 3, "db4": 4, "db5": 5}
+
+
+class _PsiBand(object):
+    """Per-band bookkeeping view standing in for the reference's psi_band jitclass
+    (pfb/operators/psi.py:126-185): sizes and pyramid tables, no arithmetic of its own."""
+
+    def __init__(self, psi):
+        self._psi = weakref.ref(psi)     # no cycle: the plan is destroyed with the last user reference
+        self.nx, self.ny = psi.nx, psi.ny
+        self.bases, self.nbasis, self.nlevel = tuple(psi.bases), psi.nbasis, psi.nlevel
+        self.Nxmax, self.Nymax = psi.Nxmax, psi.Nymax
+
+    def tables(self, basis):
+        return self._psi().tables(basis)
 
 
 class Psi(object):
@@ -24,11 +39,11 @@ class Psi(object):
         self.nbasis = len(self.bases)
         self.nlevel = int(nlevel)
         self.nthreads = nthreads
+        self._plans = {}
+        self._destroy = None
         for b in self.bases:
             if b not in _BASIS_ID:
                 raise ValueError(f"unknown basis {b!r}: expected 'self' or 'db1'..'db5'")
-        self._plans = {}
-        self._destroy = None
         # sizes do not depend on precision: build the default plan now so that
         # ValueError (nlevel too large) is raised at construction like the reference
         code = _lib.F32 if dtype is not None and np.dtype(dtype) == np.float32 else _lib.F64
@@ -36,6 +51,9 @@ class Psi(object):
         nxm, nym = ctypes.c_int(), ctypes.c_int()
         _lib.check(_lib.lib().pfb_psi_plan_query(self._plans[code], ctypes.byref(nxm), ctypes.byref(nym)))
         self.Nxmax, self.Nymax = nxm.value, nym.value
+        # Psi.psib (pfb/operators/psi.py:272-274): one bookkeeping object per band.  The bands
+        # share one device plan here, so the entries are views of the same tables.
+        self.psib = [_PsiBand(self) for _ in range(self.nband)]
 
     def _plan(self, code):
         p = self._plans.get(code)

@@ -7,17 +7,22 @@ primal_dual_optimised keeps the reference's signature, including its quirks:
 sum-over-band dual_update_numba, primal_dual.py:136), x and v are updated in
 place and returned.  The pdb traps of the reference become FloatingPointError.
 
-Device-resident loop, per iteration (nlevel = L):
-    L   launches  Psi.dot(xp) -> v
-    1   launch    fused dual update + `vp = 2v - vp`
-    L   launches  Psi.hdot(vp) -> xout
-    3   launches  grad: psf_convolve(xp)          (when grad is a Grad21)
-    2   launches  fused `xout += conv - data; x = P+(xp - tau*xout)` + eps terms
-and one 16-byte device->host read for the convergence test.  The reference's
-`xp[...] = x`, `vp[...] = v` copies are buffer swaps.  With
-pfb_b200.parallel enabled the bands are sharded over ranks: the dual update is
-split around an all-reduce of the band-sum slab and the eps terms are
-all-reduced.
+Device-resident loop (default, "nat" path: bases are distinct db1..db4 + self, dual kept
+in the natural orientation between iterations, include/pfb_b200.h), per iteration, L levels:
+    L   launches  Psi.dot(x_k) -> u                 (issued one iteration ahead, behind the primal step)
+    1   launch    dual update, writes v only        (pfb_dual_update; sharded: pfb_dual_update_rec)
+    L   launches  w_k = Psi.hdot(v_k)               (synthesis by linearity: 2 w_k - w_{k-1})
+    3   launches  PSF convolution, the primal step x = P+(xp - tau(2w_k - w_{k-1} + conv - data))
+                  and the eps terms being the epilogue of its last pass (pfb_hess_apply_primal;
+                  otherwise pfb_hess_apply + pfb_pd_primal_lin)
+and one 16-byte device->host read on a side stream for the convergence test.  The
+reference's `xp[...] = x`, `vp[...] = v` copies are buffer swaps.  Fallbacks: "slab" (reference
+coefficient layout, `2v - vp` fused into the synthesis loader) and "generic" (arbitrary psi /
+psiH callables).  With pfb_b200.parallel enabled the bands are sharded over ranks: the
+cross-band sum of the dual update is carried by a recursion that needs the all-reduce of one
+band-summed IMAGE per iteration (hidden behind the PSF convolution); `prox_21`-style l2 norms
+and PFB_PAR_NOREC=1 use the split partial / all-reduce(slab) / apply kernels; the eps terms
+are all-reduced.
 """
 import math
 import os
@@ -397,30 +402,39 @@ def primal_dual(x, v, lam, psi, psiH, L, prox, grad, nu=1.0, sigma=None, mask=No
                 tol=1e-5, maxit=1000, minit=10, positivity=1, report_freq=10, gamma=1.0,
                 verbosity=1):
     """pfb/opt/primal_dual.py:12-87, functional form: psiH(x) RETURNS coeffs,
-    psi(v) RETURNS an image, prox(v, thr) RETURNS an array.  Kept literal (the
-    operators it is given own the kernels); single rank only."""
+    psi(v) RETURNS an image, prox(v, thr) RETURNS an array.  The operators are the
+    caller's; everything between them runs on the fused vector kernels (pfb_axpby for
+    vtilde / the Moreau step / 2v - vp, pfb_pd_primal for the primal step with its
+    positivity projection and both norms), with x/xp and v/vp as buffer swaps.
+    Single rank only (like the reference's non-distributed form)."""
     xd = _dev.to_dev(x, copy=True)
     vd = _dev.to_dev(v, copy=True)
     xp, vp = xd.clone(), vd.clone()
+    vt, u = torch.empty_like(vd), torch.empty_like(vd)
     if sigma is None:
         sigma = L / (2.0 * gamma) / nu
     tau = 0.9 / (L / (2.0 * gamma) + sigma * nu**2)
     eps = 1.0
     k = 0
     terms = _dev.scalars(2)
+
+    def dev_like(t, ref):
+        t = _dev.to_dev(t)
+        return t if t.dtype == ref.dtype else t.to(ref.dtype)
     while (eps > tol or k < minit) and k < maxit:
-        vtilde = vd + sigma * _dev.to_dev(psiH(xp))
-        vd = vtilde - sigma * _dev.to_dev(prox(vtilde / sigma, lam / sigma))
-        xd = xp - tau * (_dev.to_dev(psi(2 * vd - vp)) + _dev.to_dev(grad(xp)))
-        if positivity == 1:
-            xd = torch.clamp_min(xd, 0.0)
-        elif positivity == 2:
-            xd[:, (xd <= 0).any(dim=0)] = 0.0
+        # vtilde = v + sigma * psiH(xp)                                  (:50)
+        _vec.axpby(vt, 1.0, vp, sigma, dev_like(psiH(xp), vd))
+        # v = vtilde - sigma * prox(vtilde / sigma, lam / sigma)         (:51)
+        _vec.axpby(u, 1.0 / sigma, vt, 0.0, vt)
+        _vec.axpby(vd, 1.0, vt, -sigma, dev_like(prox(u, lam / sigma), vd))
+        # x = xp - tau * (psi(2 v - vp) + grad(xp)); positivity; norms   (:54-64)
+        _vec.axpby(u, 2.0, vd, -1.0, vp)
+        _vec.pd_primal(xd, xp, dev_like(psi(u), xd), dev_like(grad(xp), xd), None, tau, positivity, terms)
         # eps = ||x - xp|| / ||x||
-        num, den = norm_diff_terms(xd, xp, out=terms).tolist()
+        num, den = terms.tolist()
         eps = math.sqrt(num) / math.sqrt(den) if den > 0 else float("nan")
-        xp.copy_(xd)
-        vp.copy_(vd)
+        xd, xp = xp, xd          # xp <- x, vp <- v as swaps
+        vd, vp = vp, vd
         if math.isnan(eps) or math.isinf(eps):
             raise FloatingPointError("primal_dual: eps is NaN/Inf")
         if not k % report_freq and verbosity > 1:
@@ -431,4 +445,4 @@ def primal_dual(x, v, lam, psi, psiH, L, prox, grad, nu=1.0, sigma=None, mask=No
             print(f"Max iters reached. eps = {eps:.3e}")
         else:
             print(f"Success, converged after {k} iterations")
-    return _dev.like(x, xd), _dev.like(v, vd)
+    return _dev.like(x, xp), _dev.like(v, vp)

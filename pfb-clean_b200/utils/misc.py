@@ -27,12 +27,50 @@ def norm_diff(x, xp):
     return math.sqrt(r[0] / (1e-12 + r[1]))
 
 
+def band_sum(t, out=None):
+    """Sum over the leading (band) axis on the device; with band sharding enabled
+    the sum runs over ALL ranks' bands (SUM all-reduce of the local band sums)."""
+    from .. import parallel
+    nb = t.shape[0]
+    m = t.numel() // nb
+    if out is None:
+        out = torch.empty(t.shape[1:], dtype=t.dtype, device=t.device)
+    _lib.check(_lib.lib().pfb_dual_partial(_dev.ptr(t), _dev.ptr(t), _dev.ptr(out), nb, m, m, 0.0,
+                                           _lib.BAND_SUM, _dev.dcode(t), _dev.stream()))
+    return parallel.allreduce_sum(out)
+
+
+def seg_stats(x, nseg):
+    """(nseg, 3) fp64 device tensor {mean, population std, max |x|} of each of the nseg equal
+    segments of x (pfb_seg_stats; two-pass std like numpy)."""
+    xd = _dev.to_dev(x)
+    out = _dev.scalars(3 * nseg)
+    _lib.check(_lib.lib().pfb_seg_stats(_dev.ptr(xd), nseg, xd.numel() // nseg, _dev.ptr(out),
+                                        _dev.dcode(xd), _dev.stream()))
+    return out.view(nseg, 3)
+
+
 def l1reweight_func(psiH, outvar, rmsfactor, rms_comps, model, alpha=4):
     """pfb/utils/misc.py:1070-1080: weights from the band-summed coefficient
-    magnitudes of the current model (psiH is image -> coeffs, i.e. Psi.dot)."""
+    magnitudes of the current model (psiH is image -> coeffs, i.e. Psi.dot).
+    One band-sum kernel + one weight kernel; with band sharding the sum is over
+    every rank's bands, so all ranks derive the same weights (the sharded dual
+    update relies on that)."""
     psiH(model, outvar)
     od = _dev.to_dev(outvar)
-    mcomps = torch.abs(torch.sum(od, dim=0))
-    rc = _dev.to_dev(rms_comps) if not isinstance(rms_comps, (int, float)) else rms_comps
-    w = (1 + rmsfactor) / (1 + mcomps**alpha / rc**alpha)
+    bs = band_sum(od)
+    nbasis = od.shape[1]
+    if isinstance(rms_comps, (int, float)):
+        rc = torch.full((nbasis,), float(rms_comps), dtype=od.dtype, device=od.device)
+    else:
+        rc = _dev.to_dev(rms_comps).to(od.dtype).reshape(-1)
+        if rc.numel() == 1:
+            rc = rc.expand(nbasis)
+        if rc.numel() != nbasis:
+            raise ValueError("rms_comps must be a scalar or hold one value per basis")
+        rc = rc.contiguous()
+    w = torch.empty_like(bs)
+    _lib.check(_lib.lib().pfb_l1reweight(_dev.ptr(bs), _dev.ptr(rc), nbasis, bs.numel() // nbasis,
+                                         float(rmsfactor), float(alpha), _dev.ptr(w), _dev.dcode(od),
+                                         _dev.stream()))
     return _dev.like(outvar, w)

@@ -286,7 +286,58 @@ def gen_solvers():
         save(tag, **out)
 
 
-if __name__ == "__main__" and "--psi-only" in sys.argv:
+def gen_glue():
+    """Worker glue between two minor cycles.  The spotless worker cannot be
+    imported here (it needs an MS, dask, zarr, ...), so its lines are executed on the
+    reference's own operators exactly as written there: pfb/workers/spotless.py:153-157
+    (residual_mfs), :214-223 / :356-363 (rms_comps), :229-230 / :343-345 (rms, rmax, eps),
+    :259 (data), pfb/operators/gridder.py:712-714 (psfhat = r2c(iFs(psf)))."""
+    from ducc0.fft import r2c
+    iFs = np.fft.ifftshift
+    bases = ['self', 'db1', 'db2', 'db3', 'db4']
+    nbasis = len(bases)
+    for tag, (nband, nx, ny, nxp, nyp, nlevel, dt) in {
+            "glue_f64": (3, 64, 48, 128, 128, 2, np.float64),
+            "glue_f32": (3, 64, 48, 128, 128, 2, np.float32)}.items():
+        P = synth_problem(425, nband, nx, ny, nxp, nyp, dt)
+        conv, psf, dirty, rng = P["conv"], P["psf"], P["dirty"], P["rng"]
+        out = dict(psf=psf, dirty=dirty, nlevel=nlevel, bases=np.array(bases))
+        # gridder.py:712-714, per band slice as the reference does (2-D psf, axes (0, 1))
+        psfhat = np.stack([r2c(iFs(psf[b], axes=(0, 1)), axes=(0, 1), nthreads=1, forward=True, inorm=0)
+                           for b in range(nband)])
+        out["psfhat"] = psfhat
+        model = (P["model"] * (rng.random(P["model"].shape) < 0.5)).astype(dt)
+        residual = (dirty - conv(model)).astype(dt)
+        out.update(model=model, residual=residual)
+        # spotless.py:259
+        out["data"] = residual + conv(model)
+        # spotless.py:153-157, 229-230
+        residual_mfs = np.sum(residual, axis=0)
+        out.update(residual_mfs=residual_mfs, rms=np.float64(np.std(residual_mfs)),
+                   rmax=np.float64(np.abs(residual_mfs).max()))
+        # spotless.py:214-223
+        wsums = np.array([1.5, 0.0, 2.5])
+        wsum = np.sum(wsums)
+        pix_per_beam = 11.3
+        psi = Psi(nband, nx, ny, bases, nlevel, 1)
+        psiHoutvar = np.zeros((nband, nbasis, psi.Nymax, psi.Nxmax), dtype=dirty.dtype)
+        fsel = wsums > 0
+        tmp2 = residual.copy()
+        tmp2[fsel] *= wsum / wsums[fsel, None, None]
+        psi.dot(tmp2 / pix_per_beam, psiHoutvar)
+        rms_comps = np.std(np.sum(psiHoutvar, axis=0), axis=(-1, -2))[:, None, None]
+        out.update(wsums=wsums, pix_per_beam=np.float64(pix_per_beam), rms_comps=rms_comps)
+        # spotless.py:364-371
+        out["l1weight"] = l1reweight_func(psi.dot, psiHoutvar, 1.0, rms_comps, model, alpha=4)
+        # spotless.py:345
+        modelp = (model * 0.9).astype(dt)
+        out.update(modelp=modelp, eps=np.float64(np.linalg.norm(model - modelp) / np.linalg.norm(model)))
+        save(tag, **out)
+
+
+if __name__ == "__main__" and "--glue-only" in sys.argv:
+    gen_glue()
+elif __name__ == "__main__" and "--psi-only" in sys.argv:
     gen_psi()
 elif __name__ == "__main__" and "--solvers-only" in sys.argv:
     gen_solvers()
@@ -296,3 +347,4 @@ elif __name__ == "__main__":
     gen_hess()
     gen_misc()
     gen_solvers()
+    gen_glue()
