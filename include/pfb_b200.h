@@ -253,6 +253,17 @@ int pfb_hess_apply_primal(pfb_hess_plan *plan, const void *xp, const void *w, co
  * segment per basis (spotless.py:219-223, 360-363); np.std / np.abs().max() of
  * residual_mfs with one segment (spotless.py:229-230, 343-344). */
 int pfb_seg_stats(const void *x, int nseg, long long m, double *stats3, int dtype, void *stream);
+/* pfb_seg_stats without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * pfb_seg_stats; the partial sums live in a static device array of the library (303 104
+ * bytes per GPU that loads it, held until exit) instead of a cudaMalloc'ed workspace, which
+ * limits nseg to 64: more segments return PFB_ERR_BAD_ARG with a message naming the limit.
+ * The call itself allocates nothing (no cudaMalloc / cudaFree, no events).  All calls share
+ * the array: calls that overlap on the GPU (different streams) race; calls on one stream,
+ * or otherwise ordered, are safe, and nothing has to be cleared between them. */
+int pfb_seg_stats_static(const void *x, int nseg, long long m, double *stats3, int dtype,
+                         void *stream);
 /* l1reweight_func, pfb/utils/misc.py:1070-1080, after the band sum:
  * weight[b][i] = (1 + rmsfactor) / (1 + |bsum[b][i]|^alpha / rms_comps[b]^alpha),
  * bsum, weight = (nbasis, nslab), rms_comps = (nbasis) in the array precision. */

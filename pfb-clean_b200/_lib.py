@@ -63,6 +63,7 @@ _SIGS = {
     "pfb_hess_apply": (c_int, [_P, _P, _P, c_int, c_double, c_int, c_double, _P, _P]),
     "pfb_pcg_direction": (c_int, [_P, _P, c_double, c_double, c_longlong, c_int, _P, _P]),
     "pfb_seg_stats": (c_int, [_P, c_int, c_longlong, _P, c_int, _P]),
+    "pfb_seg_stats_static": (c_int, [_P, c_int, c_longlong, _P, c_int, _P]),
     "pfb_l1reweight": (c_int, [_P, _P, c_int, c_longlong, c_double, c_double, _P, c_int, _P]),
     "pfb_psfhat_from_psf": (c_int, [_P, c_int, c_int, c_int, c_int, _P, _P]),
 }

@@ -142,6 +142,53 @@ static int l1reweight_t(const T *s, const T *rms, int nbasis, long nslab, double
     return PFB_OK;
 }
 
+// ---------------------------------------------------------------------------
+// No-allocation variant of pfb_seg_stats (for callers that cannot call cudaMalloc: CUDA graph
+// capture, tight serving loops).  The partial sums live in a file-scope device array instead
+// of the cudaMalloc'ed workspace: 2 doubles x kSegBlocks CTAs x kStaticMaxSeg segments
+// = 303 104 bytes, held by every GPU that loads the library until the process exits.
+// In host code `g_static_part` is only a stand-in for the symbol, NOT a device address: the
+// address is resolved once per device with cudaGetSymbolAddress (that device current) and
+// cached.  All calls share the array and it keeps the last call's contents; nothing in it
+// has to start at zero (every slot a pass reads was written by that same pass), but two calls
+// that overlap on the GPU (different streams) race on it.
+static const int kStaticMaxSeg = 64;
+static const int kStaticMaxDev = 64;
+static __device__ __align__(256) double g_static_part[2 * kStaticMaxSeg * kSegBlocks];
+static double *g_static_ptr[kStaticMaxDev] = {nullptr};
+
+static int static_part_ptr(double **out) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kStaticMaxDev)
+        return fail(PFB_ERR_CUDA, "pfb_seg_stats_static: cannot identify the current device");
+    if (!g_static_ptr[dev]) {
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_part);
+        if (e != cudaSuccess || !ptr)
+            return fail(PFB_ERR_CUDA, "pfb_seg_stats_static: cudaGetSymbolAddress failed: %s",
+                        cudaGetErrorString(e));
+        g_static_ptr[dev] = (double *)ptr;
+    }
+    *out = g_static_ptr[dev];
+    return PFB_OK;
+}
+
+// same launches as seg_stats_t, on a caller-supplied workspace of 2 * nseg * kSegBlocks doubles
+template <class T>
+static int seg_stats_ws_t(const T *x, int nseg, long m, double *stats, double *part, cudaStream_t st) {
+    long nb = (m + 255) / 256;
+    const int blk = (int)(nb < kSegBlocks ? (nb < 1 ? 1 : nb) : kSegBlocks);
+    launch(&k_seg_stats<T, 0>, dim3(blk, nseg), dim3(256), 0, st, x, m, (const double *)stats, part);
+    PFB_CHECK_LAUNCH();
+    launch(&k_seg_final<0>, dim3(nseg), dim3(32), 0, st, (const double *)part, blk, m, stats);
+    PFB_CHECK_LAUNCH();
+    launch(&k_seg_stats<T, 1>, dim3(blk, nseg), dim3(256), 0, st, x, m, (const double *)stats, part);
+    PFB_CHECK_LAUNCH();
+    launch(&k_seg_final<1>, dim3(nseg), dim3(32), 0, st, (const double *)part, blk, m, stats);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
 }  // namespace pfb
 
 using namespace pfb;
@@ -154,6 +201,20 @@ int pfb_seg_stats(const void *x, int nseg, long long m, double *stats3, int dtyp
     if (dtype == PFB_F32) return seg_stats_t<float>((const float *)x, nseg, (long)m, stats3, st);
     if (dtype == PFB_F64) return seg_stats_t<double>((const double *)x, nseg, (long)m, stats3, st);
     return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+}
+
+int pfb_seg_stats_static(const void *x, int nseg, long long m, double *stats3, int dtype, void *stream) {
+    if (!x || !stats3 || nseg < 1 || m < 1)
+        return fail(PFB_ERR_BAD_ARG, "pfb_seg_stats_static: bad argument");
+    if (nseg > kStaticMaxSeg)
+        return fail(PFB_ERR_BAD_ARG, "pfb_seg_stats_static: %d segments exceed the static workspace "
+                                     "(at most %d); use pfb_seg_stats", nseg, kStaticMaxSeg);
+    if (dtype != PFB_F32 && dtype != PFB_F64) return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+    double *part = nullptr;
+    if (int rc = static_part_ptr(&part)) return rc;
+    cudaStream_t st = as_stream(stream);
+    if (dtype == PFB_F32) return seg_stats_ws_t<float>((const float *)x, nseg, (long)m, stats3, part, st);
+    return seg_stats_ws_t<double>((const double *)x, nseg, (long)m, stats3, part, st);
 }
 
 int pfb_l1reweight(const void *bsum, const void *rms_comps, int nbasis, long long nslab, double rmsfactor,

@@ -29,7 +29,7 @@
 #define __constant__ static
 #define __shared__ static
 #define __launch_bounds__(...)
-#define __align__(n) alignas(n)
+#define __align__(n) __attribute__((aligned(n)))
 
 struct dim3 {
     unsigned x, y, z;
@@ -148,6 +148,8 @@ static inline cudaError_t cudaMemcpy(void *d, const void *s, size_t n, cudaMemcp
 static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 static inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
 static inline cudaError_t cudaGetLastError() { return cudaSuccess; }
+static inline cudaError_t cudaGetDevice(int *d) { *d = 0; return cudaSuccess; }
+template <class S> static inline cudaError_t cudaGetSymbolAddress(void **p, S &sym) { *p = (void *)&sym; return cudaSuccess; }
 static inline cudaError_t cudaPeekAtLastError() { return cudaSuccess; }
 static inline const char *cudaGetErrorString(cudaError_t) { return "emu"; }
 template <class F> static inline cudaError_t cudaFuncSetAttribute(F, int, int) { return cudaSuccess; }
