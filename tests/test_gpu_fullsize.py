@@ -89,13 +89,14 @@ def test_psf_convolve_random_full_size_vs_oracle(dtype, nx):
     rng = np.random.default_rng(14)
     nxp = 2 * nx
     cdt = np.complex64 if dtype == np.float32 else np.complex128
-    psfhat = (rng.standard_normal((1, nxp, nxp // 2 + 1), dtype=np.float32) +
-              1j * rng.standard_normal((1, nxp, nxp // 2 + 1), dtype=np.float32)).astype(cdt)
-    psfhat[:, 0, 0] = psfhat[:, 0, 0].real
+    nthr = os.cpu_count() or 1
+    # psfhat of a random REAL psf (what gridder.py:712-714 produces): Hermitian half spectrum
+    psf = rng.standard_normal((1, nxp, nxp), dtype=np.float32)
+    psfhat = ref.sfft.rfft2(psf.astype(np.float64), axes=(1, 2), workers=nthr).astype(cdt)
+    del psf
     x = rng.standard_normal((1, nx, nx), dtype=np.float32).astype(dtype)
     xpad, xhat = np.empty((1, nxp, nxp), dtype), np.empty(psfhat.shape, cdt)
     xo = np.empty_like(x)
-    nthr = os.cpu_count() or 1
     exp = ref.psf_convolve_cube(xpad, xhat, xo, psfhat, nxp, x, nthreads=nthr).copy()
     out = np.full(x.shape, np.nan, dtype)
     psf_convolve_cube(None, None, out, psfhat, nxp, x)
