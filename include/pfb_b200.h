@@ -135,6 +135,39 @@ int pfb_pcg_update(void *x, void *r, const void *xp, const void *rp, const void 
 int pfb_pcg_direction(void *p, const void *r, double beta, double minv,
                       long long n, int dtype, double *out1, void *stream);
 
+/* Device-resident line search of pcg (pfb/opt/pcg.py:86-122) and of the per-band solves of
+ * _pcg_psf_impl (pfb/opt/pcg.py:243-291, which the reference runs concurrently over bands
+ * with da.blockwise): the vectors are nseg independent segments of seglen elements (one
+ * segment = the whole cube for pcg, one band for pcg_psf) and the scalars live in a device
+ * state block of PFB_PCG_NSTATE doubles per segment:
+ *   [0] <r,y>  [1] <p,Ap>  [2] alpha  [3] <r,y>_next  [4] sum (x-xp)^2  [5] sum x^2
+ *   [6] beta   [7] number of non-zero p  [8] backtrack flag  [9] active (caller-set)
+ * so that an iteration is enqueued without a host round trip:
+ *   A(p); seg_dot(p, Ap -> [1]); seg_scalar(ALPHA); seg_update; seg_scalar(BETA);
+ *   seg_direction; ...host reads the state once, late...; seg_scalar(COMMIT)
+ * Inactive segments ([9] == 0) pass through unchanged.  Between a sum and the scalar step
+ * that uses it the caller may all-reduce the state (band-sharded global pcg). */
+#define PFB_PCG_NSTATE 10
+typedef enum {
+    PFB_PCG_ALPHA = 0,   /* [2] = [0] / [1]                                   pcg.py:90-91 */
+    PFB_PCG_BETA = 1,    /* [8] = active && [3] > [0];  [6] = [3] / [0]       pcg.py:96,103 */
+    PFB_PCG_SHRINK = 2,  /* [2] *= 0.75 where [8] is set                      pcg.py:97 */
+    PFB_PCG_COMMIT = 3   /* [0] = [3] where active                            pcg.py:108 */
+} pfb_pcg_step;
+/* state[seg][slot] = sum over the segment of a*b (fp64, fixed order) */
+int pfb_pcg_seg_dot(const void *a, const void *b, int nseg, long long seglen, int dtype,
+                    double *state, int slot, void *stream);
+int pfb_pcg_seg_scalar(double *state, int nseg, int step, void *stream);
+/* x = xp + alpha p; r = rp + alpha Ap (alpha = state[seg][2]); state[seg][3..5] =
+ * {<r, minv r>, sum (x-xp)^2, sum x^2}                                       pcg.py:92-95,111 */
+int pfb_pcg_seg_update(void *x, void *r, const void *xp, const void *rp, const void *p,
+                       const void *Ap, double minv, int nseg, long long seglen, int dtype,
+                       double *state, void *stream);
+/* pn = beta p - minv r (beta = state[seg][6]); state[seg][7] = count of non-zero pn; pn may
+ * not alias p (the old direction survives for a late backtrack)              pcg.py:103-107 */
+int pfb_pcg_seg_direction(void *pn, const void *p, const void *r, double minv, int nseg,
+                          long long seglen, int dtype, double *state, void *stream);
+
 /* ------------------------------------------------------------------- Psi --
  * Multi-basis wavelet dictionary, pfb/operators/psi.py:269-310 (class Psi) over
  * pfb/wavelets/wavelets.py dwt2d :174 / idwt2d :260.  basis_ids: 0 = 'self',

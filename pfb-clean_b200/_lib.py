@@ -12,6 +12,7 @@ SO_PATH = os.path.join(_HERE, "csrc", "libpfb_b200.so")
 
 F32, F64 = 0, 1
 BAND_SUM, BAND_L2 = 0, 1
+PCG_ALPHA, PCG_BETA, PCG_SHRINK, PCG_COMMIT = 0, 1, 2, 3
 
 STATUS = {1: "bad argument", 2: "odd image size", 3: "nlevel too large",
           4: "unsupported FFT size", 5: "CUDA error", 6: "allocation failed",
@@ -62,6 +63,10 @@ _SIGS = {
     "pfb_hess_plan_set_dynamic": (c_int, [_P, c_int]),
     "pfb_hess_apply": (c_int, [_P, _P, _P, c_int, c_double, c_int, c_double, _P, _P]),
     "pfb_pcg_direction": (c_int, [_P, _P, c_double, c_double, c_longlong, c_int, _P, _P]),
+    "pfb_pcg_seg_dot": (c_int, [_P, _P, c_int, c_longlong, c_int, _P, c_int, _P]),
+    "pfb_pcg_seg_scalar": (c_int, [_P, c_int, c_int, _P]),
+    "pfb_pcg_seg_update": (c_int, [_P, _P, _P, _P, _P, _P, c_double, c_int, c_longlong, c_int, _P, _P]),
+    "pfb_pcg_seg_direction": (c_int, [_P, _P, _P, c_double, c_int, c_longlong, c_int, _P, _P]),
     "pfb_seg_stats": (c_int, [_P, c_int, c_longlong, _P, c_int, _P]),
     "pfb_seg_stats_static": (c_int, [_P, c_int, c_longlong, _P, c_int, _P]),
     "pfb_l1reweight": (c_int, [_P, _P, c_int, c_longlong, c_double, c_double, _P, c_int, _P]),

@@ -481,8 +481,9 @@ static int fast_cols1(pfb_hess_plan *p, cudaStream_t st) {
     auto kern = p->dyn ? &k_hessf_cols1<T, H, true> : &k_hessf_cols1<T, H, false>;
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = persistent_grid((const void *)kern, H / 16, smem, h.nyo2 * h.nband, p->nsm);
+    static const int stagger = getenv("PFB_HESS_STAGGER") ? atoi(getenv("PFB_HESS_STAGGER")) : 0;
     launch(kern, dim3(grid), dim3(H / 16), smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
-           (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h, p->ctr + 1);
+           (const Cx<T> *)p->tabH, (const Cx<T> *)p->modg, h, p->ctr + 1, H <= 4096 ? stagger : 0);
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }

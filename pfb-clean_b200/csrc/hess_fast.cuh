@@ -481,7 +481,7 @@ k_hessf_rows_inv2(const Cx<T> *__restrict__ S, T *__restrict__ out,
 template <class T, int H, bool DYN>
 __global__ void __launch_bounds__(H / 16, (H <= 4096 ? 2 : 1))
 k_hessf_cols1(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__ tabg,
-              const Cx<T> *__restrict__ modg, HessDims h, int *counter) {
+              const Cx<T> *__restrict__ modg, HessDims h, int *counter, int stagger) {
     PFB_DYN_SMEM(raw);
     Cx<T> *buf = reinterpret_cast<Cx<T> *>(raw);
     Cx<T> *park = buf + ct_stride(H);
@@ -495,6 +495,16 @@ k_hessf_cols1(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict_
     q.init(counter);
     q.request();
     int col = q.publish();                       // also orders the table load
+#ifndef PFB_EMU
+    // Two CTAs share an SM and run identical loops: started together they stay in phase and
+    // meet in the shared-memory exchanges and in the butterflies alike (measured: run time =
+    // FMA-pipe time + shared-memory-pipe time).  Holding back the second wave of CTAs breaks
+    // the symmetry so that one CTA's exchanges fall under the other's arithmetic.
+    if (stagger > 0 && (int)blockIdx.x >= ((int)gridDim.x + 1) / 2) {
+        const long long t0 = clock64();
+        while (clock64() - t0 < (long long)stagger) {}
+    }
+#endif
     Cx<T> *const pk = park + ct_pad(t);
     while (col < total) {
         q.request();

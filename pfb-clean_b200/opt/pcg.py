@@ -1,11 +1,19 @@
-"""Drop-in for pfb/opt/pcg.py: pcg :53-136 and _pcg_psf_impl :243-291.
+"""Drop-in for pfb/opt/pcg.py: pcg :53-136, _pcg_psf_impl :243-291, pcg_psf :310-360.
 
-All vectors stay on the device; each iteration issues A(p), one fused
-two-dot-product kernel, one fused line-update kernel (x, r, <r,y>, eps terms)
-and one fused direction kernel (p, any(p)).  xp/rp copies of the reference are
-replaced by buffer ping-pong so a backtracking step is just a re-issue of the
-line update with a smaller alpha.  With pfb_b200.parallel enabled the scalars
-are all-reduced over the band-sharded ranks (global CG over the whole cube).
+All vectors stay on the device.  With M = None or the scalar preconditioner of
+_pcg_psf_impl (ScalarPrecond) the line search is device resident (csrc/pcg.cu): alpha and
+beta are computed by a one-thread kernel from sums that never leave the GPU, and an
+iteration is enqueued as
+    A(p) -> <p,Ap> -> alpha -> fused line update (x, r, <r,y>, eps terms) -> beta ->
+    fused direction (p, any(p))
+with the NEXT A(p) already queued while the host reads the one small state record it needs
+for eps / termination / the rare backtrack.  xp, rp, the old p and the old Ap are kept by
+buffer ping-pong, so a backtracking step is a re-issue of the line update with a smaller
+alpha.  The same kernels work on nseg independent segments: the whole cube (pcg) or one
+segment per band with per-band scalars and per-band termination (_pcg_psf_impl, which the
+reference runs concurrently over bands with da.blockwise).  Any other M falls back to the
+host-scalar loop (_pcg_host).  With pfb_b200.parallel enabled the sums of the global solve
+are all-reduced over the band-sharded ranks.
 """
 import math
 from functools import partial
@@ -13,7 +21,7 @@ from functools import partial
 import numpy as np
 import torch
 
-from .. import _dev, parallel
+from .. import _dev, _lib, parallel
 from ..operators.hessian import _hessian_psf_slice
 from . import _vec
 
@@ -36,10 +44,11 @@ def _host_(t, reduce=True):
     return t.tolist()
 
 
-def pcg(A, b, x0=None, M=None, tol=1e-5, maxit=500, minit=100, verbosity=1,
-        report_freq=10, backtrack=True, return_resid=False, _global=True):
-    """`_global=False` (extension) keeps the scalars rank-local when band
-    sharding is enabled (independent per-band solves)."""
+def _pcg_host(A, b, x0=None, M=None, tol=1e-5, maxit=500, minit=100, verbosity=1,
+              report_freq=10, backtrack=True, return_resid=False, _global=True):
+    """Host-scalar loop (three small device->host reads per iteration): used for
+    preconditioners that are arbitrary callables.  `_global=False` keeps the scalars
+    rank-local when band sharding is enabled."""
     _h = partial(_host_, reduce=_global)
     bd = _dev.to_dev(b)
     if x0 is None:
@@ -122,22 +131,191 @@ def pcg(A, b, x0=None, M=None, tol=1e-5, maxit=500, minit=100, verbosity=1,
     return (res, _dev.like(b, r)) if return_resid else res
 
 
+def _state_copy(st, pinned, ev):
+    """Enqueue the copy of the device state block to pinned host memory (compute stream)."""
+    if _dev._EMULATED:
+        return st.clone()
+    pinned.copy_(st, non_blocking=True)
+    ev.record()
+    return None
+
+
+def _state_wait(snap, pinned, ev):
+    """Wait for that copy only: whatever was queued behind it keeps the GPU busy."""
+    if _dev._EMULATED:
+        return snap.numpy()
+    ev.synchronize()
+    return pinned.numpy().copy()
+
+
+def _state_read(st, pinned, ev):
+    return _state_wait(_state_copy(st, pinned, ev), pinned, ev)
+
+
+def _pcg_dev(A, bd, x, minv, nseg, tol, maxit, minit, verbosity, report_freq, backtrack,
+             reduce, label="band"):
+    """Device-resident PCG on nseg independent segments of the contiguous cube bd (see the
+    module docstring).  A maps a cube to a cube.  Returns (x, r, k) with k the per-segment
+    iteration counts."""
+    L = _lib.lib()
+    code = _dev.dcode(bd)
+    n = bd.numel()
+    seglen = n // nseg
+    strm = _dev.stream
+    st = torch.zeros((nseg, 10), dtype=torch.float64, device=bd.device)
+    pinned = torch.empty((nseg, 10), dtype=torch.float64).pin_memory() if not _dev._EMULATED else None
+    ev = torch.cuda.Event() if not _dev._EMULATED else None
+    ar = (lambda lo, hi: parallel.allreduce_sum(st[0, lo:hi])) if (reduce and parallel.active()) else None
+    assert ar is None or nseg == 1
+
+    def dot(a, c, slot):
+        _lib.check(L.pfb_pcg_seg_dot(_dev.ptr(a), _dev.ptr(c), nseg, seglen, code, _dev.ptr(st), slot, strm()))
+        if ar:
+            ar(slot, slot + 1)
+
+    def scalar(step):
+        _lib.check(L.pfb_pcg_seg_scalar(_dev.ptr(st), nseg, step, strm()))
+
+    def apply_A(p, own):
+        """Ap = A(p) in a buffer that is neither p's nor the previous Ap's."""
+        t = _dev.to_dev(A(p))
+        if t.dtype != bd.dtype:
+            t = t.to(bd.dtype)
+        if own is not None and t.data_ptr() != own.data_ptr() and not t.is_contiguous():
+            t = t.contiguous()
+        return t
+
+    r = torch.empty_like(bd)
+    _vec.axpby(r, 1.0, apply_A(x, None), -1.0, bd)
+    y = r if minv == 1.0 else r * minv
+    dot(r, y, 0)
+    dot(y, y, 7)
+    h = _state_read(st, pinned, ev)
+    active = h[:, 7] != 0.0
+    k = np.zeros(nseg, dtype=np.int64)
+    eps = np.ones(nseg)
+    if not active.any():
+        if verbosity:
+            print("Initial residual is zero")
+        return x, r, k
+    st[:, 9] = torch.from_numpy(active.astype(np.float64)).to(st.device)
+    p = torch.empty_like(bd)
+    _vec.axpby(p, -1.0, y, 0.0, y)
+    del y
+    xn, rn, pn = torch.empty_like(x), torch.empty_like(r), torch.empty_like(p)
+    Ap = apply_A(p, None)
+    dot(p, Ap, 1)
+    scalar(_lib.PCG_ALPHA)
+    running = active.copy()
+    while running.any():
+        def line_search():
+            _lib.check(L.pfb_pcg_seg_update(_dev.ptr(xn), _dev.ptr(rn), _dev.ptr(x), _dev.ptr(r), _dev.ptr(p),
+                                            _dev.ptr(Ap), float(minv), nseg, seglen, code, _dev.ptr(st), strm()))
+            if ar:
+                ar(3, 6)
+            scalar(_lib.PCG_BETA)
+            _lib.check(L.pfb_pcg_seg_direction(_dev.ptr(pn), _dev.ptr(p), _dev.ptr(rn), float(minv), nseg, seglen,
+                                               code, _dev.ptr(st), strm()))
+            if ar:
+                ar(7, 8)
+        line_search()
+        snap = _state_copy(st, pinned, ev)
+        # the next A(p) is queued before the host looks at this iteration's scalars
+        Apn = apply_A(pn, Ap)
+        if Apn.data_ptr() == Ap.data_ptr():
+            # A returned the buffer that held the current Ap (a shared output array such as
+            # psf_convolve's xout): the new result gets a private copy, and the old Ap is
+            # recomputed only on the (rare) backtrack path
+            Apn = Apn.clone()
+            Ap = None
+        h = _state_wait(snap, pinned, ev)
+        while backtrack and (h[:, 8] != 0.0).any():              # pfb/opt/pcg.py:96-101
+            if Ap is None:
+                Ap = apply_A(p, None).clone()
+            scalar(_lib.PCG_SHRINK)
+            line_search()
+            snap = _state_copy(st, pinned, ev)
+            Apn = apply_A(pn, Ap)
+            if Apn.data_ptr() == Ap.data_ptr():
+                Apn = Apn.clone()
+                Ap = None
+            h = _state_wait(snap, pinned, ev)
+        changed = False
+        for s_ in np.nonzero(running)[0]:
+            if h[s_, 7] == 0.0:                                 # p is identically zero: stop (pcg.py:106-107)
+                running[s_] = False
+                changed = True
+                continue
+            k[s_] += 1
+            eps[s_] = math.sqrt(h[s_, 4] / (1e-12 + h[s_, 5]))
+            if math.isnan(eps[s_]):
+                raise FloatingPointError("pcg: eps is NaN")
+            if not k[s_] % report_freq and verbosity > 1:
+                print(f"At iteration {k[s_]} epsx = {eps[s_]:.3e}")
+            if not ((eps[s_] > tol or k[s_] < minit) and k[s_] < maxit):
+                running[s_] = False
+                changed = True
+        scalar(_lib.PCG_COMMIT)
+        x, xn = xn, x
+        r, rn = rn, r
+        p, pn = pn, p
+        Ap = Apn
+        if changed:
+            st[:, 9] = torch.from_numpy(running.astype(np.float64)).to(st.device)
+        if running.any():
+            dot(p, Ap, 1)
+            scalar(_lib.PCG_ALPHA)
+    if verbosity:
+        for s_ in range(nseg):
+            tag = f" ({label} {s_})" if nseg > 1 else ""
+            if k[s_] >= maxit:
+                print(f"Max iters reached{tag}. eps = {eps[s_]:.3e}")
+            elif active[s_]:
+                print(f"Success, converged after {k[s_]} iterations{tag}")
+            else:
+                print(f"Initial residual is zero{tag}")
+    return x, r, k
+
+
+def pcg(A, b, x0=None, M=None, tol=1e-5, maxit=500, minit=100, verbosity=1,
+        report_freq=10, backtrack=True, return_resid=False, _global=True):
+    """pfb/opt/pcg.py:53-136.  `_global=False` (extension) keeps the scalars rank-local when
+    band sharding is enabled."""
+    if not (M is None or isinstance(M, ScalarPrecond)):
+        pcg.last_path = "host-loop"
+        return _pcg_host(A, b, x0, M, tol, maxit, minit, verbosity, report_freq, backtrack,
+                         return_resid, _global)
+    pcg.last_path = "device-scalars"
+    bd = _dev.to_dev(b)
+    if x0 is None:
+        x = torch.zeros_like(bd)
+    else:
+        x = _dev.to_dev(x0, copy=True)
+        if x.dtype != bd.dtype:
+            x = x.to(bd.dtype)
+    minv = 1.0 if M is None else M.minv
+    x, r, _ = _pcg_dev(A, bd.contiguous(), x.contiguous(), minv, 1, tol, maxit, minit, verbosity,
+                       report_freq, backtrack, _global)
+    res = _dev.like(b, x)
+    return (res, _dev.like(b, r)) if return_resid else res
+
+
 def _pcg_psf_impl(psfhat, b, x0, beam, lastsize, nthreads, sigmainv, tol=1e-5,
                   maxit=500, minit=100, verbosity=1, report_freq=10, backtrack=True):
     """pfb/opt/pcg.py:243-291: independent per-band PCG with
-    A = _hessian_psf_slice(psfhat[k], beam[k], sigmainv), M = x/sigmainv."""
+    A = _hessian_psf_slice(psfhat[k], beam[k], sigmainv), M = x/sigmainv -- all bands in one
+    launch set, each with its own alpha / beta / eps and its own termination."""
+    from ..operators.hessian import hessian_psf_cube
     nband = b.shape[0]
-    bd, x0d, beamd = _dev.to_dev(b), _dev.to_dev(x0), _dev.to_dev(beam)
+    bd, x0d, beamd = _dev.to_dev(b), _dev.to_dev(x0, copy=True), _dev.to_dev(beam)
     psfd = _dev.to_dev(psfhat)
-    model = torch.zeros_like(bd)
-    M = ScalarPrecond(sigmainv) if sigmainv > 0 else None
-    for k in range(nband):
-        A = partial(_hessian_psf_slice, None, None, None, psfd[k],
-                    beamd[k] if beamd is not None else None, lastsize,
-                    nthreads=nthreads, sigmainv=sigmainv)
-        model[k] = pcg(A, bd[k], x0d[k], M=M, tol=tol, maxit=maxit, minit=minit,
-                       verbosity=verbosity, report_freq=report_freq, backtrack=backtrack,
-                       _global=False)
+    minv = 1.0 / float(sigmainv) if sigmainv > 0 else 1.0
+    A = partial(hessian_psf_cube, None, None, None, beamd, psfd, lastsize, nthreads=nthreads,
+                sigmainv=sigmainv)
+    if x0d.dtype != bd.dtype:
+        x0d = x0d.to(bd.dtype)
+    model, _, _ = _pcg_dev(A, bd.contiguous(), x0d.contiguous(), minv, nband, tol, maxit, minit,
+                           verbosity, report_freq, backtrack, False)
     return _dev.like(b, model)
 
 
