@@ -1,0 +1,148 @@
+"""The band-sharded solver on real GPUs (NCCL, one process per GPU) against the single-GPU
+path on the same cube: the recursive band-sum dual update (pfb_dual_update_rec) with its
+asynchronous image all-reduce hidden behind the PSF convolution, the slab exchange
+(PFB_PAR_NOREC), positivity 1 and 2, l1 reweighting, fp32 and fp64, and the global PCG.
+Needs >= 2 GPUs (skipped otherwise; run with `gpurun --gpus 2`, log under profiles/)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+BASES = ["self", "db1", "db2", "db3", "db4"]
+
+
+def _problem(torch, nband, nx, rdt, dev):
+    g = torch.Generator(device="cpu").manual_seed(11)
+    nxp = 2 * nx
+    ii = (torch.arange(nxp, dtype=torch.float64) - nxp // 2)
+    psf = torch.empty((nband, nxp, nxp), dtype=torch.float64)
+    for b in range(nband):
+        s = 2.0 * (1 + 0.05 * b)
+        g1 = torch.exp(-0.5 * (ii / s) ** 2)
+        g2 = torch.exp(-0.5 * (ii / (0.05 * nx)) ** 2)
+        psf[b] = g1[:, None] * g1[None, :] + 0.01 * (torch.cos(0.05 * ii) * g2)[:, None] * (torch.cos(0.03 * ii) * g2)[None, :]
+        psf[b] /= psf[b].max() * nband
+    cdt = torch.complex64 if rdt == torch.float32 else torch.complex128
+    psfhat = torch.fft.rfft2(torch.fft.ifftshift(psf, dim=(1, 2)), dim=(1, 2)).to(cdt)
+    model = torch.zeros((nband, nx, nx), dtype=torch.float64)
+    for _ in range(40):
+        i, j = torch.randint(nx // 8, 7 * nx // 8, (2,), generator=g)
+        model[:, i, j] = (1 + torch.exp(torch.randn((), generator=g))) * (1 + 0.1 * torch.arange(nband)) ** -0.7
+    noise = torch.randn(model.shape, generator=g, dtype=torch.float64)
+    return psfhat.to(dev), model.to(rdt).to(dev), noise.to(rdt).to(dev)
+
+
+def _worker(rank, world, port, q, nit):
+    try:
+        sys.path.insert(0, ROOT)
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        import torch.distributed as dist
+        from functools import partial
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        import pfb_b200  # noqa: F401
+        from pfb_b200 import parallel
+        from pfb_b200.operators import psf as P
+        from pfb_b200.operators.hessian import hessian_psf_cube
+        from pfb_b200.operators.psi import Psi
+        from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
+        from pfb_b200.opt.pcg import pcg
+        from pfb_b200.utils.misc import l1reweight_func
+        res = {}
+        nband, nx = 4, 512
+        nbl = nband // world
+        sl = slice(rank * nbl, (rank + 1) * nbl)
+        for rdt, tag, tol in ((torch.float32, "f32", 1e-5), (torch.float64, "f64", 1e-11)):
+            psfhat, model, noise = _problem(torch, nband, nx, rdt, dev)     # every rank builds the whole cube
+            nxp = 2 * nx
+            xo = torch.empty_like(model)
+            dirty = P.psf_convolve_cube(None, None, xo, psfhat, nxp, model).clone()
+            dirty += 1e-3 * dirty.max() * noise
+            lam = 0.5 * float(dirty.sum(dim=0).std())
+            hessnorm = 1.05
+
+            def solve(psf_, dirty_, nb_, positivity, rew_tol=None):
+                psi = Psi(nb_, nx, nx, BASES, 3, 1)
+                conv = partial(P.psf_convolve_cube, None, None, torch.empty_like(dirty_), psf_, nxp)
+                x = torch.zeros_like(dirty_)
+                v = torch.zeros((nb_, 5, psi.Nymax, psi.Nxmax), dtype=rdt, device=dev)
+                w = torch.ones(tuple(v.shape[1:]), dtype=rdt, device=dev)
+                rew = None
+                if rew_tol is not None:
+                    outvar = torch.zeros_like(v)
+                    rc = torch.tensor([0.3, 0.5, 0.4, 0.6, 0.2], dtype=rdt, device=dev)
+                    rew = partial(l1reweight_func, psi.dot, outvar, 1.0, rc)
+                primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, w, rew,
+                                      Grad21(conv, dirty_), nu=5, tol=rew_tol or 0.0, maxit=nit,
+                                      positivity=positivity, verbosity=0, maxreweight=3)
+                return x, v, primal_dual_optimised.last_rec
+
+            def rel(a, b):
+                return float(torch.linalg.vector_norm((a.double() - b.double()).view(-1)) /
+                             torch.linalg.vector_norm(b.double().view(-1)))
+            cases = [("rec_pos1", {}, 1, None), ("slab_pos1", {"PFB_PAR_NOREC": "1"}, 1, None),
+                     ("rec_pos2", {}, 2, None), ("rec_reweight", {}, 1, 0.5)]
+            for name, env, pos, rt in cases:
+                P.clear_plan_cache()
+                parallel.disable()
+                x1, v1, _ = solve(psfhat, dirty, nband, pos, rt)
+                assert bool(x1.any())
+                for k_, val in env.items():
+                    os.environ[k_] = val
+                parallel.enable()
+                P.clear_plan_cache()
+                xs, vs, used_rec = solve(psfhat[sl].contiguous(), dirty[sl].contiguous(), nbl, pos, rt)
+                for k_ in env:
+                    del os.environ[k_]
+                res[f"{tag}_{name}"] = (rel(xs, x1[sl]), rel(vs, v1[sl]), bool(used_rec), tol)
+            # global PCG over the sharded cube
+            P.clear_plan_cache()
+            parallel.disable()
+            A1 = partial(hessian_psf_cube, None, None, None, None, psfhat, nxp, sigmainv=1e-3)
+            xs1 = pcg(A1, dirty, torch.zeros_like(dirty), tol=0.0, maxit=8, minit=8, verbosity=0)
+            parallel.enable()
+            P.clear_plan_cache()
+            As = partial(hessian_psf_cube, None, None, None, None, psfhat[sl].contiguous(), nxp, sigmainv=1e-3)
+            xss = pcg(As, dirty[sl].contiguous(), torch.zeros_like(dirty[sl]), tol=0.0, maxit=8, minit=8, verbosity=0)
+            res[f"{tag}_pcg"] = (rel(xss, xs1[sl]), 0.0, True, 1e-10 if tag == "f64" else 2e-4)
+        q.put((rank, res))
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:   # pragma: no cover
+        import traceback
+        q.put((rank, {"error": traceback.format_exc() + str(e)}))
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_band_sharded_nccl_vs_single_gpu(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29700 + os.getpid() % 2000 + world
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, 20)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = {}
+    for _ in range(world):
+        r, res = q.get(timeout=900)
+        out[r] = res
+    for p in procs:
+        p.join(timeout=60)
+    print(out[0])
+    for r in range(world):
+        assert "error" not in out[r], out[r].get("error")
+        for name, (ex, ev, used_rec, tol) in out[r].items():
+            assert ex < tol and ev < tol, (r, name, ex, ev)
+            if "rec" in name:
+                assert used_rec, (r, name)
+            if "slab" in name:
+                assert not used_rec, (r, name)

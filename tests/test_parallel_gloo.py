@@ -69,6 +69,20 @@ def _worker(rank, world, port, q):
             res[f"rec{pos}"] = primal_dual_optimised.last_rec     # image-sized exchange (pfb_dual_update_rec)
             res[f"pd_x{pos}"] = rel(x, g[f"pdo_x_pos{pos}"][sl])
             res[f"pd_v{pos}"] = rel(v, g[f"pdo_v_pos{pos}"][sl])
+        # l1 reweighting on sharded ranks: the weights come from the band sum over ALL ranks'
+        # bands (pfb/utils/misc.py:1070-1080), so every rank must derive the same weights
+        from pfb_b200.utils.misc import l1reweight_func
+        os.environ["PFB_PAR_RESYNC"] = "64"
+        outvar = np.zeros((nbl, len(bases), psi.Nymax, psi.Nxmax))
+        rew = partial(l1reweight_func, psi.dot, outvar, 1.0, g["rms_comps"])
+        x = np.zeros_like(dirty)
+        v = np.zeros((nbl, len(bases), psi.Nymax, psi.Nxmax))
+        primal_dual_optimised(x, v, float(g["lam"]), psi.hdot, psi.dot, float(g["hessnorm"]), None,
+                              np.ones(v.shape[1:]), rew, Grad21(conv, dirty), nu=len(bases), tol=0.2,
+                              maxit=12, positivity=1, verbosity=0, maxreweight=3)
+        res["rw_x"] = rel(x, g["pdo_rw_x"][sl])
+        res["rw_v"] = rel(v, g["pdo_rw_v"][sl])
+        res["rw_w"] = rel(l1reweight_func(psi.dot, outvar, 1.0, g["rms_comps"], x), g["rw_weight"])
         # fp32: the recursively carried band sum in single precision, 10 iterations
         os.environ["PFB_PAR_RESYNC"] = "64"
         g32 = np.load(os.path.join(HERE, "golden", "solve_f32.npz"))
@@ -120,4 +134,5 @@ def test_band_sharded_two_ranks():
             assert out[r][f"pd_x{pos}"] < 1e-11, out[r]
             assert out[r][f"pd_v{pos}"] < 1e-11, out[r]
         assert out[r]["pcg_x"] < 1e-10, out[r]
+        assert out[r]["rw_x"] < 1e-11 and out[r]["rw_v"] < 1e-11 and out[r]["rw_w"] < 1e-11, out[r]
         assert out[r]["rec32"] and out[r]["pd32_x"] < 1e-5 and out[r]["pd32_v"] < 1e-5, out[r]
