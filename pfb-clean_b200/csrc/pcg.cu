@@ -13,6 +13,7 @@
 // next A(p) is already running.  Sums accumulate in fp64 in a fixed order; between a sum and
 // the scalar step that consumes it the caller may all-reduce the state (band-sharded ranks).
 #include "common.cuh"
+#include <initializer_list>
 
 namespace pfb {
 
@@ -64,20 +65,32 @@ __global__ void k_pcg_final(const double *__restrict__ part, int nblk, double *s
     }
 }
 
-// <p, Ap> per segment
-template <class T>
+template <class T, int V> struct alignas(sizeof(T) * V) PPack { T v[V]; };
+template <class T, int V> __device__ __forceinline__ PPack<T, V> pld(const T *p) {
+    return *reinterpret_cast<const PPack<T, V> *>(p);
+}
+template <class T, int V> __device__ __forceinline__ void pst(T *p, const PPack<T, V> &x) {
+    *reinterpret_cast<PPack<T, V> *>(p) = x;
+}
+
+// <a, b> per segment.  V = elements per 128-bit access (1 when sizes / pointers are unaligned).
+template <class T, int V>
 __global__ void __launch_bounds__(256)
 k_pcg_seg_dot(const T *__restrict__ a, const T *__restrict__ b, long seglen, double *part) {
     const long o = (long)blockIdx.y * seglen;
     double acc[1] = {0.0};
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < seglen; i += (long)gridDim.x * blockDim.x)
-        acc[0] += (double)a[o + i] * (double)b[o + i];
+    const long nv = seglen / V;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long)gridDim.x * blockDim.x) {
+        const PPack<T, V> x = pld<T, V>(a + o + i * V), y = pld<T, V>(b + o + i * V);
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc[0] += (double)x.v[e] * (double)y.v[e];
+    }
     p_block_store<1>(acc, part);
 }
 
 // x = xp + alpha p; r = rp + alpha Ap; y = minv r  (pfb/opt/pcg.py:92-95); sums {<r,y>, (x-xp)^2, x^2}.
 // Inactive segments are carried over unchanged (x = xp, r = rp).
-template <class T>
+template <class T, int V>
 __global__ void __launch_bounds__(256)
 k_pcg_seg_update(T *__restrict__ x, T *__restrict__ r, const T *__restrict__ xp, const T *__restrict__ rp,
                  const T *__restrict__ p, const T *__restrict__ Ap, const double *__restrict__ st, T minv,
@@ -87,26 +100,35 @@ k_pcg_seg_update(T *__restrict__ x, T *__restrict__ r, const T *__restrict__ xp,
     const bool active = st[(long)seg * NS + 9] != 0.0;
     const T alpha = (T)st[(long)seg * NS + 2];
     double acc[3] = {0.0, 0.0, 0.0};
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < seglen; i += (long)gridDim.x * blockDim.x) {
-        const T xo = xp[o + i];
-        T xi = xo, ri = rp[o + i];
+    const long nv = seglen / V;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long)gridDim.x * blockDim.x) {
+        const long k = o + i * V;
+        const PPack<T, V> xo = pld<T, V>(xp + k), ro = pld<T, V>(rp + k);
+        PPack<T, V> xi = xo, ri = ro;
         if (active) {
-            xi = xo + alpha * p[o + i];
-            ri = ri + alpha * Ap[o + i];
+            const PPack<T, V> pp = pld<T, V>(p + k), ap = pld<T, V>(Ap + k);
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                xi.v[e] = xo.v[e] + alpha * pp.v[e];
+                ri.v[e] = ro.v[e] + alpha * ap.v[e];
+            }
         }
-        x[o + i] = xi;
-        r[o + i] = ri;
-        const T yi = ri * minv;
-        const T d = xi - xo;
-        acc[0] += (double)ri * (double)yi;
-        acc[1] += (double)(d * d);
-        acc[2] += (double)(xi * xi);
+        pst<T, V>(x + k, xi);
+        pst<T, V>(r + k, ri);
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            const T yi = ri.v[e] * minv;
+            const T d = xi.v[e] - xo.v[e];
+            acc[0] += (double)ri.v[e] * (double)yi;
+            acc[1] += (double)(d * d);
+            acc[2] += (double)(xi.v[e] * xi.v[e]);
+        }
     }
     p_block_store<3>(acc, part);
 }
 
 // pn = beta p - minv r; count of non-zero pn  (pfb/opt/pcg.py:103-107).  Inactive: pn = p.
-template <class T>
+template <class T, int V>
 __global__ void __launch_bounds__(256)
 k_pcg_seg_dir(T *__restrict__ pn, const T *__restrict__ p, const T *__restrict__ r,
               const double *__restrict__ st, T minv, long seglen, double *part) {
@@ -115,11 +137,19 @@ k_pcg_seg_dir(T *__restrict__ pn, const T *__restrict__ p, const T *__restrict__
     const bool active = st[(long)seg * NS + 9] != 0.0;
     const T beta = (T)st[(long)seg * NS + 6];
     double acc[1] = {0.0};
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < seglen; i += (long)gridDim.x * blockDim.x) {
-        T pi = p[o + i];
-        if (active) pi = beta * pi - minv * r[o + i];
-        pn[o + i] = pi;
-        if (pi != (T)0) acc[0] += 1.0;
+    const long nv = seglen / V;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long)gridDim.x * blockDim.x) {
+        const long k = o + i * V;
+        PPack<T, V> pi = pld<T, V>(p + k);
+        if (active) {
+            const PPack<T, V> rr = pld<T, V>(r + k);
+#pragma unroll
+            for (int e = 0; e < V; ++e) pi.v[e] = beta * pi.v[e] - minv * rr.v[e];
+        }
+        pst<T, V>(pn + k, pi);
+#pragma unroll
+        for (int e = 0; e < V; ++e)
+            if (pi.v[e] != (T)0) acc[0] += 1.0;
     }
     p_block_store<1>(acc, part);
 }
@@ -156,9 +186,17 @@ static int ensure_ppart(long n) {
     return PFB_OK;
 }
 
+template <class T> static inline bool vec_ok(long seglen, std::initializer_list<const void *> ptrs) {
+    const int V = 16 / (int)sizeof(T);
+    if (seglen % V) return false;
+    for (const void *q : ptrs)
+        if ((uintptr_t)q & 15) return false;
+    return true;
+}
+
 static inline int seg_blocks(int nseg, long seglen) {
     long per = kPcgBlocks / nseg;
-    long need = (seglen + 255) / 256;
+    long need = (seglen / 4 + 255) / 256;
     if (per > need) per = need;
     return (int)(per < 1 ? 1 : per);
 }
@@ -176,11 +214,18 @@ int pfb_pcg_seg_dot(const void *p, const void *Ap, int nseg, long long seglen, i
     const int nblk = seg_blocks(nseg, seglen);
     if (int rc = ensure_ppart((long)nseg * nblk * 3)) return rc;
     cudaStream_t st = as_stream(stream);
-    if (dtype == PFB_F32)
-        launch(&k_pcg_seg_dot<float>, dim3(nblk, nseg), dim3(256), 0, st, (const float *)p, (const float *)Ap, (long)seglen, g_ppart);
-    else if (dtype == PFB_F64)
-        launch(&k_pcg_seg_dot<double>, dim3(nblk, nseg), dim3(256), 0, st, (const double *)p, (const double *)Ap, (long)seglen, g_ppart);
-    else
+    const dim3 g(nblk, nseg), b(256);
+    if (dtype == PFB_F32) {
+        if (vec_ok<float>(seglen, {p, Ap}))
+            launch(&k_pcg_seg_dot<float, 4>, g, b, 0, st, (const float *)p, (const float *)Ap, (long)seglen, g_ppart);
+        else
+            launch(&k_pcg_seg_dot<float, 1>, g, b, 0, st, (const float *)p, (const float *)Ap, (long)seglen, g_ppart);
+    } else if (dtype == PFB_F64) {
+        if (vec_ok<double>(seglen, {p, Ap}))
+            launch(&k_pcg_seg_dot<double, 2>, g, b, 0, st, (const double *)p, (const double *)Ap, (long)seglen, g_ppart);
+        else
+            launch(&k_pcg_seg_dot<double, 1>, g, b, 0, st, (const double *)p, (const double *)Ap, (long)seglen, g_ppart);
+    } else
         return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
     PFB_CHECK_LAUNCH();
     launch(&k_pcg_final<1>, dim3(nseg), dim3(32), 0, st, (const double *)g_ppart, nblk, state, slot);
@@ -203,13 +248,18 @@ int pfb_pcg_seg_update(void *x, void *r, const void *xp, const void *rp, const v
     const int nblk = seg_blocks(nseg, seglen);
     if (int rc = ensure_ppart((long)nseg * nblk * 3)) return rc;
     cudaStream_t st = as_stream(stream);
-    if (dtype == PFB_F32)
-        launch(&k_pcg_seg_update<float>, dim3(nblk, nseg), dim3(256), 0, st, (float *)x, (float *)r, (const float *)xp,
-               (const float *)rp, (const float *)p, (const float *)Ap, (const double *)state, (float)minv, (long)seglen, g_ppart);
-    else if (dtype == PFB_F64)
-        launch(&k_pcg_seg_update<double>, dim3(nblk, nseg), dim3(256), 0, st, (double *)x, (double *)r, (const double *)xp,
-               (const double *)rp, (const double *)p, (const double *)Ap, (const double *)state, minv, (long)seglen, g_ppart);
-    else
+    const dim3 g(nblk, nseg), b(256);
+#define PFB_UPD(T, V, MINV)                                                                                      \
+    launch(&k_pcg_seg_update<T, V>, g, b, 0, st, (T *)x, (T *)r, (const T *)xp, (const T *)rp, (const T *)p,      \
+           (const T *)Ap, (const double *)state, (T)(MINV), (long)seglen, g_ppart)
+    if (dtype == PFB_F32) {
+        if (vec_ok<float>(seglen, {x, r, xp, rp, p, Ap})) PFB_UPD(float, 4, minv);
+        else PFB_UPD(float, 1, minv);
+    } else if (dtype == PFB_F64) {
+        if (vec_ok<double>(seglen, {x, r, xp, rp, p, Ap})) PFB_UPD(double, 2, minv);
+        else PFB_UPD(double, 1, minv);
+    } else
+#undef PFB_UPD
         return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
     PFB_CHECK_LAUNCH();
     launch(&k_pcg_final<3>, dim3(nseg), dim3(32), 0, st, (const double *)g_ppart, nblk, state, 3);
@@ -224,13 +274,18 @@ int pfb_pcg_seg_direction(void *pn, const void *p, const void *r, double minv, i
     const int nblk = seg_blocks(nseg, seglen);
     if (int rc = ensure_ppart((long)nseg * nblk * 3)) return rc;
     cudaStream_t st = as_stream(stream);
-    if (dtype == PFB_F32)
-        launch(&k_pcg_seg_dir<float>, dim3(nblk, nseg), dim3(256), 0, st, (float *)pn, (const float *)p, (const float *)r,
-               (const double *)state, (float)minv, (long)seglen, g_ppart);
-    else if (dtype == PFB_F64)
-        launch(&k_pcg_seg_dir<double>, dim3(nblk, nseg), dim3(256), 0, st, (double *)pn, (const double *)p, (const double *)r,
-               (const double *)state, minv, (long)seglen, g_ppart);
-    else
+    const dim3 g(nblk, nseg), b(256);
+#define PFB_DIR(T, V, MINV)                                                                                      \
+    launch(&k_pcg_seg_dir<T, V>, g, b, 0, st, (T *)pn, (const T *)p, (const T *)r, (const double *)state,         \
+           (T)(MINV), (long)seglen, g_ppart)
+    if (dtype == PFB_F32) {
+        if (vec_ok<float>(seglen, {pn, p, r})) PFB_DIR(float, 4, minv);
+        else PFB_DIR(float, 1, minv);
+    } else if (dtype == PFB_F64) {
+        if (vec_ok<double>(seglen, {pn, p, r})) PFB_DIR(double, 2, minv);
+        else PFB_DIR(double, 1, minv);
+    } else
+#undef PFB_DIR
         return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
     PFB_CHECK_LAUNCH();
     launch(&k_pcg_final<1>, dim3(nseg), dim3(32), 0, st, (const double *)g_ppart, nblk, state, 7);

@@ -207,6 +207,7 @@ def _pcg_dev(A, bd, x, minv, nseg, tol, maxit, minit, verbosity, report_freq, ba
     dot(p, Ap, 1)
     scalar(_lib.PCG_ALPHA)
     running = active.copy()
+    last_bt = False
     while running.any():
         def line_search():
             _lib.check(L.pfb_pcg_seg_update(_dev.ptr(xn), _dev.ptr(rn), _dev.ptr(x), _dev.ptr(r), _dev.ptr(p),
@@ -220,26 +221,34 @@ def _pcg_dev(A, bd, x, minv, nseg, tol, maxit, minit, verbosity, report_freq, ba
                 ar(7, 8)
         line_search()
         snap = _state_copy(st, pinned, ev)
-        # the next A(p) is queued before the host looks at this iteration's scalars
-        Apn = apply_A(pn, Ap)
-        if Apn.data_ptr() == Ap.data_ptr():
-            # A returned the buffer that held the current Ap (a shared output array such as
-            # psf_convolve's xout): the new result gets a private copy, and the old Ap is
-            # recomputed only on the (rare) backtrack path
-            Apn = Apn.clone()
-            Ap = None
+
+        def next_A():
+            """A(pn) for the next iteration; a result that lands in the buffer of the current Ap
+            (a shared output array such as psf_convolve's xout) is moved to a private copy and
+            the old Ap marked lost (recomputed only if a backtrack needs it)."""
+            nonlocal Ap
+            t = apply_A(pn, Ap)
+            if Ap is not None and t.data_ptr() == Ap.data_ptr():
+                t = t.clone()
+                Ap = None
+            return t
+        # Speculation: the next A(p) is queued before the host looks at this iteration's scalars,
+        # so the GPU never drains -- unless the previous iteration backtracked (then this one
+        # probably will too, and a speculative Hessian would be thrown away).
+        spec = not last_bt
+        Apn = next_A() if spec else None
         h = _state_wait(snap, pinned, ev)
-        while backtrack and (h[:, 8] != 0.0).any():              # pfb/opt/pcg.py:96-101
+        last_bt = bool(backtrack and (h[:, 8] != 0.0).any())
+        if last_bt:                                              # pfb/opt/pcg.py:96-101
             if Ap is None:
                 Ap = apply_A(p, None).clone()
-            scalar(_lib.PCG_SHRINK)
-            line_search()
-            snap = _state_copy(st, pinned, ev)
-            Apn = apply_A(pn, Ap)
-            if Apn.data_ptr() == Ap.data_ptr():
-                Apn = Apn.clone()
-                Ap = None
-            h = _state_wait(snap, pinned, ev)
+            while (h[:, 8] != 0.0).any():
+                scalar(_lib.PCG_SHRINK)
+                line_search()
+                h = _state_read(st, pinned, ev)
+            Apn = next_A()
+        elif not spec:
+            Apn = next_A()
         changed = False
         for s_ in np.nonzero(running)[0]:
             if h[s_, 7] == 0.0:                                 # p is identically zero: stop (pcg.py:106-107)
