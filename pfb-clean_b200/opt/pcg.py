@@ -177,13 +177,11 @@ def _pcg_dev(A, bd, x, minv, nseg, tol, maxit, minit, verbosity, report_freq, ba
         _lib.check(L.pfb_pcg_seg_scalar(_dev.ptr(st), nseg, step, strm()))
 
     def apply_A(p, own):
-        """Ap = A(p) in a buffer that is neither p's nor the previous Ap's."""
+        """Ap = A(p) as a device tensor of the working precision."""
         t = _dev.to_dev(A(p))
         if t.dtype != bd.dtype:
             t = t.to(bd.dtype)
-        if own is not None and t.data_ptr() != own.data_ptr() and not t.is_contiguous():
-            t = t.contiguous()
-        return t
+        return t if t.is_contiguous() else t.contiguous()
 
     r = torch.empty_like(bd)
     _vec.axpby(r, 1.0, apply_A(x, None), -1.0, bd)
@@ -207,54 +205,53 @@ def _pcg_dev(A, bd, x, minv, nseg, tol, maxit, minit, verbosity, report_freq, ba
     dot(p, Ap, 1)
     scalar(_lib.PCG_ALPHA)
     running = active.copy()
-    last_bt = False
-    while running.any():
-        def line_search():
-            _lib.check(L.pfb_pcg_seg_update(_dev.ptr(xn), _dev.ptr(rn), _dev.ptr(x), _dev.ptr(r), _dev.ptr(p),
-                                            _dev.ptr(Ap), float(minv), nseg, seglen, code, _dev.ptr(st), strm()))
-            if ar:
-                ar(3, 6)
-            scalar(_lib.PCG_BETA)
-            _lib.check(L.pfb_pcg_seg_direction(_dev.ptr(pn), _dev.ptr(p), _dev.ptr(rn), float(minv), nseg, seglen,
-                                               code, _dev.ptr(st), strm()))
-            if ar:
-                ar(7, 8)
-        line_search()
-        snap = _state_copy(st, pinned, ev)
 
-        def next_A():
-            """A(pn) for the next iteration; a result that lands in the buffer of the current Ap
-            (a shared output array such as psf_convolve's xout) is moved to a private copy and
-            the old Ap marked lost (recomputed only if a backtrack needs it)."""
-            nonlocal Ap
-            t = apply_A(pn, Ap)
-            if Ap is not None and t.data_ptr() == Ap.data_ptr():
-                t = t.clone()
-                Ap = None
-            return t
-        # Speculation: the next A(p) is queued before the host looks at this iteration's scalars,
-        # so the GPU never drains -- unless the previous iteration backtracked (then this one
-        # probably will too, and a speculative Hessian would be thrown away).
-        spec = not last_bt
-        Apn = next_A() if spec else None
+    def update():
+        _lib.check(L.pfb_pcg_seg_update(_dev.ptr(xn), _dev.ptr(rn), _dev.ptr(x), _dev.ptr(r), _dev.ptr(p),
+                                        _dev.ptr(Ap), float(minv), nseg, seglen, code, _dev.ptr(st), strm()))
+        if ar:
+            ar(3, 6)
+        scalar(_lib.PCG_BETA)
+
+    def direction():
+        _lib.check(L.pfb_pcg_seg_direction(_dev.ptr(pn), _dev.ptr(p), _dev.ptr(rn), float(minv), nseg, seglen,
+                                           code, _dev.ptr(st), strm()))
+        if ar:
+            ar(7, 8)
+
+    def set_active():
+        st[:, 9] = torch.from_numpy(running.astype(np.float64)).to(st.device)
+    pending_nnz = False          # slot 7 of the state holds the count of the direction used by this iteration
+    while running.any():
+        # The host needs this iteration's sums for eps / termination / the backtrack test.  They are
+        # copied right behind the line update; the (cheap) direction kernel is queued speculatively
+        # behind the copy, so by the time the host has decided, A(pn) is queued while the GPU is
+        # still busy.  Only a backtrack throws the direction away.
+        update()
+        snap = _state_copy(st, pinned, ev)
+        direction()
         h = _state_wait(snap, pinned, ev)
-        last_bt = bool(backtrack and (h[:, 8] != 0.0).any())
-        if last_bt:                                              # pfb/opt/pcg.py:96-101
-            if Ap is None:
-                Ap = apply_A(p, None).clone()
+        if pending_nnz:
+            # `if not np.any(p): break` (pcg.py:106-107) of the PREVIOUS iteration, seen one
+            # iteration late: the segment's solution is the x this iteration started from
+            dead = running & (h[:, 7] == 0.0)
+            if dead.any():
+                running &= ~dead
+                set_active()
+                if not running.any():
+                    break
+                update()                     # pass the dead segments through unchanged
+                direction()
+                h = _state_read(st, pinned, ev)
+        if backtrack and (h[:, 8] != 0.0).any():                 # pfb/opt/pcg.py:96-101
             while (h[:, 8] != 0.0).any():
                 scalar(_lib.PCG_SHRINK)
-                line_search()
+                update()
                 h = _state_read(st, pinned, ev)
-            Apn = next_A()
-        elif not spec:
-            Apn = next_A()
+            direction()
+        pending_nnz = True
         changed = False
         for s_ in np.nonzero(running)[0]:
-            if h[s_, 7] == 0.0:                                 # p is identically zero: stop (pcg.py:106-107)
-                running[s_] = False
-                changed = True
-                continue
             k[s_] += 1
             eps[s_] = math.sqrt(h[s_, 4] / (1e-12 + h[s_, 5]))
             if math.isnan(eps[s_]):
@@ -268,10 +265,10 @@ def _pcg_dev(A, bd, x, minv, nseg, tol, maxit, minit, verbosity, report_freq, ba
         x, xn = xn, x
         r, rn = rn, r
         p, pn = pn, p
-        Ap = Apn
         if changed:
-            st[:, 9] = torch.from_numpy(running.astype(np.float64)).to(st.device)
+            set_active()
         if running.any():
+            Ap = apply_A(p, None)
             dot(p, Ap, 1)
             scalar(_lib.PCG_ALPHA)
     if verbosity:

@@ -28,6 +28,12 @@ KEYS = [
     ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "lsu%"),
     ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "fma%"),
     ("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "alu%"),
+    ("smsp__average_warp_latency_issue_stalled_mio_throttle.ratio", "st_mio"),
+    ("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smem_wavefronts"),
+    ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smem_conflicts"),
+    ("l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex%"),
+    ("lts__throughput.avg.pct_of_peak_sustained_elapsed", "lts%"),
+    ("sm__cycles_elapsed.max", "cycles"),
     ("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "l1_ld_sect"),
     ("l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum", "l1_ld_req"),
     ("l1tex__t_sector_hit_rate.pct", "l1hit%"),

@@ -12,15 +12,20 @@ nband = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 nx = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
 nit = int(sys.argv[3]) if len(sys.argv) > 3 else 10
 dev = torch.device("cuda")
-g = torch.Generator(device=dev).manual_seed(1)
 nxp = 2 * nx
-psf = torch.zeros((nband, nxp, nxp), device=dev)
-ii = torch.arange(nxp, device=dev) - nxp // 2
-g1 = torch.exp(-0.5 * (ii / 2.0) ** 2)
-psf[:] = (g1[:, None] * g1[None, :]) / nband
-psfhat = torch.fft.rfft2(torch.fft.ifftshift(psf, dim=(1, 2)), dim=(1, 2))
-del psf
-b = torch.randn((nband, nx, nx), generator=g, device=dev)
+if os.environ.get("PROBE_RANDOM"):
+    g = torch.Generator(device=dev).manual_seed(1)
+    psf = torch.zeros((nband, nxp, nxp), device=dev)
+    ii = torch.arange(nxp, device=dev) - nxp // 2
+    g1 = torch.exp(-0.5 * (ii / 2.0) ** 2)
+    psf[:] = (g1[:, None] * g1[None, :]) / nband
+    psfhat = torch.fft.rfft2(torch.fft.ifftshift(psf, dim=(1, 2)), dim=(1, 2))
+    del psf
+    b = torch.randn((nband, nx, nx), generator=g, device=dev)
+else:           # bench.py's problem
+    import bench
+    P = bench.Problem(torch, nband, nx, "f32", list(range(nband)), dev)
+    psfhat, b = P.psfhat, P.dirty
 A = partial(hessian_psf_cube, None, None, None, None, psfhat, nxp, sigmainv=1e-3)
 L = _lib.lib()
 for mode in ("global", "per-band"):

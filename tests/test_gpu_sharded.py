@@ -101,7 +101,11 @@ def _worker(rank, world, port, q, nit):
                 xs, vs, used_rec = solve(psfhat[sl].contiguous(), dirty[sl].contiguous(), nbl, pos, rt)
                 for k_ in env:
                     del os.environ[k_]
-                res[f"{tag}_{name}"] = (rel(xs, x1[sl]), rel(vs, v1[sl]), bool(used_rec), tol)
+                # positivity 2 zeroes a pixel in every band when ANY band is <= 0 there
+                # (pfb/opt/primal_dual.py:144-146): a discontinuous step, so in fp32 a few pixels
+                # flip on rounding and the dual moves by more than the model does
+                tol_c = 1e-4 if (pos == 2 and tag == "f32") else tol
+                res[f"{tag}_{name}"] = (rel(xs, x1[sl]), rel(vs, v1[sl]), bool(used_rec), tol_c)
             # global PCG over the sharded cube
             P.clear_plan_cache()
             parallel.disable()
