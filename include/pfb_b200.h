@@ -275,6 +275,38 @@ int pfb_hess_apply_primal(pfb_hess_plan *plan, const void *xp, const void *w, co
                           const void *data, double tau, int positivity, void *x, double *out2,
                           void *stream);
 
+/* ------------------------------------------------- CLEAN minor loops --
+ * pfb/deconv/clark.py (clark :84-177, subminor :29-82, subtract :12-26) and
+ * pfb/deconv/hogbom.py:8-72.  The searches are argmax decisions, so these kernels keep the
+ * reference's evaluation order and do not contract multiply-subtract into FMA.          */
+
+/* search[i] = (sum_b IR[b][i])^2 (search may be NULL); out2 = {argmax (first index on ties,
+ * like numpy), search[argmax]}                       clark.py:116-120, 145-150; hogbom.py:26-29 */
+int pfb_mfs_peak(const void *IR, int nband, long long npix, void *search, double *out2, int dtype,
+                 void *stream);
+/* Ip, Iq = np.where(IRsearch > thr) as ascending linear pixel indices (clark.py:127):
+ * idx[0..min(count, cap)), *count = number found.  scratch_counts: ceil(npix / 2048) ints. */
+int pfb_active_set(const void *search, long long npix, double thr, long long *idx, long long cap,
+                   long long *count, int *scratch_counts, int dtype, void *stream);
+/* subminor(IR[:, Ip, Iq], psf, Ip, Iq, model, wsums, gamma, th, maxit) in one launch
+ * (clark.py:29-82): model updated in place; scratchA: nband * nact reals; info2 = {iterations
+ * done, last peak}.  wsums: nband doubles on the device.  Needs nxp >= 2 nx - 1, nyp >= 2 ny - 1
+ * (every PSF shift in range -- what the reference's active-set masking silently assumes). */
+int pfb_clark_subminor(const void *IR, const void *psf, const long long *idx, long long nact,
+                       void *model, const double *wsums, int nband, int nx, int ny, int nxp, int nyp,
+                       double gamma, double th, int maxit, void *scratchA, double *info2, int dtype,
+                       void *stream);
+/* hogbom (hogbom.py:8-72) with the loop state on the device.  state: 8 + nband doubles:
+ * [0] peak pixel, [1] IRmax, [2] done, [3] iterations k, [4] tol, [5] maxit.  start: first
+ * search, tol = max(pf IRmax, threshold) and the first component; iterate: niter x
+ * {IR -= gamma xhat psf(shifted); search; decide + next component}, no-ops once done is set --
+ * the host enqueues batches and polls state[2].  wsums: nband reals (np.amax(PSF, axis=(1,2))). */
+int pfb_hogbom_start(const void *IR, void *x, const void *wsums, int nband, long long npix,
+                     double gamma, double pf, double threshold, int maxit, double *state, int dtype,
+                     void *stream);
+int pfb_hogbom_iterate(void *IR, const void *psf, void *x, const void *wsums, int nband, int nx, int ny,
+                       int nxp, int nyp, double gamma, int niter, double *state, int dtype, void *stream);
+
 /* ------------------------------------------------ worker glue (device) --
  * Pieces of the spotless major cycle between two minor cycles
  * (pfb/workers/spotless.py:217-260, 343-371), kept on the device so that model,

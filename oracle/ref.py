@@ -513,3 +513,106 @@ def rms_comps(psi, residual, wsum, wsums, pix_per_beam, psiHoutvar):
 def model_eps(model, modelp):
     """pfb/workers/spotless.py:345"""
     return np.linalg.norm(model - modelp) / np.linalg.norm(model)
+
+
+# ------------------------------------------------- CLEAN minor loops (SURVEY 8 f3)
+def subminor(A, psf, Ip, Iq, model, wsums, gamma=0.05, th=0.0, maxit=10000):
+    """pfb/deconv/clark.py:29-82 (+ subtract :12-26).  A (nband, nact) is the active set,
+    pixel i of it sitting at (Ip[i], Iq[i]).  The reference masks A by PSF overlap but not
+    Ip / Iq (:68-72), which is only consistent when the mask is all True, i.e. when the PSF
+    is at least twice the image -- asserted here."""
+    nband, nx_psf, ny_psf = psf.shape
+    nxo2, nyo2 = nx_psf // 2, ny_psf // 2
+    A = A.copy()
+    Asearch = np.sum(A, axis=0) ** 2
+    pq = Asearch.argmax()
+    p, q = Ip[pq], Iq[pq]
+    Amax = np.sqrt(Asearch[pq])
+    fsel = wsums > 0
+    if fsel.sum() == 0:
+        raise ValueError("wsums are all zero")
+    k = 0
+    while Amax > th and k < maxit:
+        xhat = A[:, pq].copy()
+        # numba evaluates gamma * xhat / wsums in fp64 (gamma, wsums are float64) before the store
+        model[fsel, p, q] += gamma * xhat[fsel].astype(np.float64) / wsums[fsel]
+        Idelp, Idelq = p - Ip, q - Iq
+        mask = (np.abs(Idelp) <= nxo2) & (np.abs(Idelq) <= nyo2)
+        assert mask.all(), "PSF smaller than twice the image: the reference's active-set masking is inconsistent"
+        A -= xhat[:, None] * psf[:, nxo2 - Idelp, nyo2 - Idelq]
+        Asearch = np.sum(A, axis=0) ** 2
+        pq = Asearch.argmax()
+        p, q = Ip[pq], Iq[pq]
+        Amax = np.sqrt(Asearch[pq])
+        k += 1
+    return model
+
+
+def clark(ID, PSF, PSFHAT, wsums, threshold=0, gamma=0.05, pf=0.05, maxit=50, subpf=0.5,
+          submaxit=1000, report_freq=1, verbosity=1, psfopts=None, sigmathreshold=2, nthreads=1):
+    """pfb/deconv/clark.py:84-177.  Returns (model, status)."""
+    nband, nx, ny = ID.shape
+    _, nx_psf, ny_psf = PSF.shape
+    assert np.allclose(wsums.sum(), 1)
+    model = np.zeros((nband, nx, ny), dtype=ID.dtype)
+    IR = ID.copy()
+    xout = np.empty(ID.shape, dtype=ID.dtype)
+    xpad = np.empty(PSF.shape, dtype=ID.dtype)
+    xhat = np.empty(PSFHAT.shape, dtype=PSFHAT.dtype)
+    IRsearch = np.sum(IR, axis=0) ** 2
+    pq = IRsearch.argmax()
+    p = pq // ny
+    q = pq - p * ny
+    IRmax = np.sqrt(IRsearch[p, q])
+    tol = np.maximum(pf * IRmax, threshold)
+    k = 0
+    stall_count = 0
+    while IRmax > tol and k < maxit and stall_count < 5:
+        subth = subpf * IRmax
+        Ip, Iq = np.where(IRsearch > subth ** 2)
+        model = subminor(IR[:, Ip, Iq], PSF, Ip, Iq, model, wsums, gamma=gamma, th=subth, maxit=submaxit)
+        psf_convolve_cube(xpad, xhat, xout, PSFHAT, ny_psf, model, nthreads=nthreads)
+        IR = ID - xout
+        IRsearch = np.sum(IR, axis=0) ** 2
+        pq = IRsearch.argmax()
+        p = pq // ny
+        q = pq - p * ny
+        IRmaxp = IRmax
+        IRmax = np.sqrt(IRsearch[p, q])
+        k += 1
+        if np.abs(IRmaxp - IRmax) / np.abs(IRmaxp) < 1e-3:
+            stall_count += stall_count          # (sic) pfb/deconv/clark.py:153: never leaves 0
+    return model, (1 if (k >= maxit or stall_count >= 5) else 0)
+
+
+def hogbom(ID, PSF, threshold=0, gamma=0.1, pf=0.1, maxit=10000, report_freq=1000, verbosity=1):
+    """pfb/deconv/hogbom.py:8-72.  Returns (x, status)."""
+    nband, nx, ny = ID.shape
+    _, nx_psf, ny_psf = PSF.shape
+    nx0, ny0 = nx_psf // 2, ny_psf // 2
+    x = np.zeros((nband, nx, ny), dtype=ID.dtype)
+    IR = ID.copy()
+    IRsearch = np.sum(IR, axis=0) ** 2
+    pq = IRsearch.argmax()
+    p = pq // ny
+    q = pq - p * ny
+    IRmax = np.sqrt(IRsearch[p, q])
+    wsums = np.amax(PSF, axis=(1, 2))
+    fsel = wsums > 0
+    tol = np.maximum(pf * IRmax, threshold)
+    k = 0
+    stall_count = 0
+    while IRmax > tol and k < maxit and stall_count < 5:
+        xhat = IR[fsel, p, q] / wsums[fsel]
+        x[:, p, q] += gamma * xhat              # (the reference indexes all bands: needs wsums > 0 everywhere)
+        IR[...] = IR - gamma * xhat[:, None, None] * PSF[:, nx0 - p:nx0 + nx - p, ny0 - q:ny0 + ny - q]
+        IRsearch = np.sum(IR, axis=0) ** 2
+        pq = IRsearch.argmax()
+        p = pq // ny
+        q = pq - p * ny
+        IRmaxp = IRmax
+        IRmax = np.sqrt(IRsearch[p, q])
+        k += 1
+        if np.abs(IRmaxp - IRmax) / np.abs(IRmaxp) < 5e-3:
+            stall_count += stall_count          # (sic) pfb/deconv/hogbom.py:55
+    return x, (1 if (k >= maxit or stall_count >= 5) else 0)

@@ -335,7 +335,38 @@ def gen_glue():
         save(tag, **out)
 
 
-if __name__ == "__main__" and "--glue-only" in sys.argv:
+
+def gen_clean():
+    """CLEAN minor loops: pfb/deconv/clark.py clark / subminor and
+    pfb/deconv/hogbom.py hogbom, imported unchanged."""
+    _misc.give_edges = None                     # imported by hogbom.py, unused by hogbom()
+    from pfb.deconv.clark import clark, subminor
+    from pfb.deconv.hogbom import hogbom
+    for tag, (nband, nx, ny, nxp, nyp, dt) in {
+            "clean_f64": (3, 48, 40, 96, 80, np.float64),
+            "clean_f32": (3, 48, 40, 96, 80, np.float32)}.items():
+        P = synth_problem(426, nband, nx, ny, nxp, nyp, dt)
+        psf, psfhat, dirty = P["psf"], P["psfhat"], P["dirty"]
+        wsums = np.amax(psf, axis=(1, 2)).astype(np.float64)
+        wsums = wsums / wsums.sum()
+        out = dict(psf=psf, psfhat=psfhat, dirty=dirty, wsums=wsums)
+        model, status = clark(dirty, psf, psfhat, wsums, threshold=0, gamma=0.1, pf=0.05, maxit=6,
+                              subpf=0.5, submaxit=40, verbosity=0)
+        out.update(clark_model=model.copy(), clark_status=status)
+        # one sub-minor call on its own
+        IRs = np.sum(dirty, axis=0) ** 2
+        Ip, Iq = np.where(IRs > (0.4 * np.sqrt(IRs.max())) ** 2)
+        m0 = np.zeros_like(dirty)
+        m1 = subminor(dirty[:, Ip, Iq], psf, Ip, Iq, m0, wsums, gamma=0.1, th=0.4 * np.sqrt(IRs.max()), maxit=25)
+        out.update(sub_Ip=Ip, sub_Iq=Iq, sub_model=m1.copy())
+        x, st = hogbom(dirty, psf, threshold=0, gamma=0.1, pf=0.1, maxit=60, verbosity=0)
+        out.update(hogbom_x=x.copy(), hogbom_status=st)
+        save(tag, **out)
+
+
+if __name__ == "__main__" and "--clean-only" in sys.argv:
+    gen_clean()
+elif __name__ == "__main__" and "--glue-only" in sys.argv:
     gen_glue()
 elif __name__ == "__main__" and "--psi-only" in sys.argv:
     gen_psi()
@@ -348,3 +379,4 @@ elif __name__ == "__main__":
     gen_misc()
     gen_solvers()
     gen_glue()
+    gen_clean()
