@@ -318,6 +318,10 @@ int pfb_hogbom_iterate(void *IR, const void *psf, void *x, const void *wsums, in
  * segment per basis (spotless.py:219-223, 360-363); np.std / np.abs().max() of
  * residual_mfs with one segment (spotless.py:229-230, 343-344). */
 int pfb_seg_stats(const void *x, int nseg, long long m, double *stats3, int dtype, void *stream);
+/* out += scale * x * y (y NULL: out += scale * x), complex arrays as 2n reals with y NULL:
+ * the per-dataset accumulation of dds2cubes, pfb/utils/misc.py:698-714 */
+int pfb_accum_mul(void *out, const void *x, const void *y, double scale, long long n, int dtype,
+                  void *stream);
 /* pfb_seg_stats without any allocation.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (CUDA graph
  * capture, tight serving loops, harnesses that forbid it).  Same arguments and results as

@@ -616,3 +616,73 @@ def hogbom(ID, PSF, threshold=0, gamma=0.1, pf=0.1, maxit=10000, report_freq=100
         if np.abs(IRmaxp - IRmax) / np.abs(IRmaxp) < 5e-3:
             stall_count += stall_count          # (sic) pfb/deconv/hogbom.py:55
     return x, (1 if (k >= maxit or stall_count >= 5) else 0)
+
+
+# ------------------------------------------------- dds2cubes / write-back
+def dds2cubes(dds, nband, apparent=False, dual=True, modelname='MODEL'):
+    """pfb/utils/misc.py:664-739 with numpy in place of the dask graph.  dds: sequence of
+    datasets exposing DIRTY, BEAM, WSUM, bandid and optionally RESIDUAL, PSF, PSFHAT, MODEL,
+    DUAL as `.NAME.data` (and `'NAME' in ds`)."""
+    real_type = dds[0].DIRTY.dtype
+    complex_type = np.result_type(real_type, np.complex64)
+    nx, ny = dds[0].DIRTY.shape
+    dirty = [np.zeros((nx, ny), real_type) for _ in range(nband)]
+    model = [np.zeros((nx, ny), real_type) for _ in range(nband)]
+    residual = [np.zeros((nx, ny), real_type) for _ in range(nband)] if 'RESIDUAL' in dds[0] else None
+    wsums = [np.zeros(1, real_type) for _ in range(nband)]
+    if 'PSF' in dds[0]:
+        psf = [np.zeros(dds[0].PSF.shape, real_type) for _ in range(nband)]
+        psfhat = [np.zeros(dds[0].PSFHAT.shape, complex_type) for _ in range(nband)]
+    else:
+        psf = psfhat = None
+    mean_beam = [np.zeros((nx, ny), real_type) for _ in range(nband)]
+    if dual and 'DUAL' in dds[0]:
+        dual = [np.zeros(dds[0].DUAL.shape, real_type) for _ in range(nband)]
+    else:
+        dual = None
+    for ds in dds:
+        b = ds.bandid
+        if apparent:
+            dirty[b] = dirty[b] + ds.DIRTY.data
+            if 'RESIDUAL' in ds:
+                residual[b] = residual[b] + ds.RESIDUAL.data
+        else:
+            dirty[b] = dirty[b] + ds.DIRTY.data * ds.BEAM.data
+            if 'RESIDUAL' in ds:
+                residual[b] = residual[b] + ds.RESIDUAL.data * ds.BEAM.data
+        if 'PSF' in ds:
+            psf[b] = psf[b] + ds.PSF.data
+            psfhat[b] = psfhat[b] + ds.PSFHAT.data
+        if modelname in ds:
+            model[b] = getattr(ds, modelname).data
+        if dual and 'DUAL' in ds:
+            dual[b] = ds.DUAL.data
+        mean_beam[b] = mean_beam[b] + ds.BEAM.data * ds.WSUM.data[0]
+        wsums[b] = wsums[b] + ds.WSUM.data[0]
+    wsums = np.stack(wsums).reshape(nband)
+    wsum = wsums.sum()
+    dirty = np.stack(dirty) / wsum
+    model = np.stack(model)
+    if residual is not None:
+        residual = np.stack(residual) / wsum
+    if psf is not None:
+        psf = np.stack(psf) / wsum
+        psfhat = np.stack(psfhat) / wsum
+    if dual:
+        dual = np.stack(dual)
+    for b in range(nband):
+        if wsums[b]:
+            mean_beam[b] = mean_beam[b] / wsums[b]
+    mean_beam = np.stack(mean_beam)
+    return dirty, model, residual, psf, psfhat, mean_beam, wsums, dual
+
+
+def cubes2dds(dds, residual, model, dual, best_model, wsum):
+    """pfb/workers/spotless.py:373-394: the per-dataset write-back of one major iteration:
+    RESIDUAL = residual[b] * wsum, MODEL = model[b], DUAL = dual[b], MODEL_BEST = best_model[b]."""
+    out = []
+    for ds in dds:
+        b = ds.bandid
+        out.append({'RESIDUAL': residual[b] * wsum, 'MODEL': model[b], 'DUAL': dual[b],
+                    'MODEL_BEST': best_model[b]})
+    return out

@@ -73,6 +73,7 @@ _SIGS = {
                                    c_double, c_double, c_int, _P, _P, c_int, _P]),
     "pfb_hogbom_start": (c_int, [_P, _P, _P, c_int, c_longlong, c_double, c_double, c_double, c_int, _P, c_int, _P]),
     "pfb_hogbom_iterate": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_double, c_int, _P, c_int, _P]),
+    "pfb_accum_mul": (c_int, [_P, _P, _P, c_double, c_longlong, c_int, _P]),
     "pfb_seg_stats": (c_int, [_P, c_int, c_longlong, _P, c_int, _P]),
     "pfb_seg_stats_static": (c_int, [_P, c_int, c_longlong, _P, c_int, _P]),
     "pfb_l1reweight": (c_int, [_P, _P, c_int, c_longlong, c_double, c_double, _P, c_int, _P]),

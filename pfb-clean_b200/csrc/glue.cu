@@ -101,6 +101,18 @@ k_l1reweight(const T *__restrict__ s, const T *__restrict__ rms, long nslab, T r
     }
 }
 
+// out[i] += scale * x[i] * y[i]  (y may be null: out += scale * x) -- the per-dataset accumulation
+// of dds2cubes, pfb/utils/misc.py:698-714 (dirty[b] += DIRTY * BEAM, mean_beam[b] += BEAM * wsum, ...)
+template <class T>
+__global__ void __launch_bounds__(256)
+k_accum_mul(T *__restrict__ out, const T *__restrict__ x, const T *__restrict__ y, T scale, long n) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        T v = x[i];
+        if (y) v = v * y[i];
+        out[i] = out[i] + scale * v;
+    }
+}
+
 static double *g_spart = nullptr;
 static long g_spart_n = 0;
 
@@ -201,6 +213,22 @@ int pfb_seg_stats(const void *x, int nseg, long long m, double *stats3, int dtyp
     if (dtype == PFB_F32) return seg_stats_t<float>((const float *)x, nseg, (long)m, stats3, st);
     if (dtype == PFB_F64) return seg_stats_t<double>((const double *)x, nseg, (long)m, stats3, st);
     return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+}
+
+int pfb_accum_mul(void *out, const void *x, const void *y, double scale, long long n, int dtype, void *stream) {
+    if (!out || !x || n < 0) return fail(PFB_ERR_BAD_ARG, "pfb_accum_mul: bad argument");
+    if (n == 0) return PFB_OK;
+    cudaStream_t st = as_stream(stream);
+    long nb = (n + 255) / 256;
+    const int blk = (int)(nb < kNumSM * 8 ? nb : kNumSM * 8);
+    if (dtype == PFB_F32)
+        launch(&k_accum_mul<float>, dim3(blk), dim3(256), 0, st, (float *)out, (const float *)x, (const float *)y, (float)scale, (long)n);
+    else if (dtype == PFB_F64)
+        launch(&k_accum_mul<double>, dim3(blk), dim3(256), 0, st, (double *)out, (const double *)x, (const double *)y, scale, (long)n);
+    else
+        return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
 }
 
 int pfb_seg_stats_static(const void *x, int nseg, long long m, double *stats3, int dtype, void *stream) {

@@ -364,7 +364,76 @@ def gen_clean():
         save(tag, **out)
 
 
-if __name__ == "__main__" and "--clean-only" in sys.argv:
+
+class _Var:
+    def __init__(self, a):
+        self.data = a
+        self.dtype = a.dtype
+        self.shape = a.shape
+
+
+class FakeDS(dict):
+    """Minimal stand-in for the xarray datasets dds2cubes walks: `'NAME' in ds`, ds.NAME.data,
+    ds.bandid."""
+
+    def __init__(self, bandid, **arrs):
+        super().__init__({k: _Var(v) for k, v in arrs.items()})
+        self.bandid = bandid
+
+    def __getattr__(self, k):
+        try:
+            return self[k]
+        except KeyError:
+            raise AttributeError(k)
+
+
+def gen_stage():
+    """dds2cubes (pfb/utils/misc.py:664-739): the function's source text is cut out of misc.py
+    (the module cannot be imported whole) and executed unchanged with a numpy-backed stand-in
+    for the three dask calls it makes (da.zeros, da.stack, dask.compute)."""
+    import types
+    path = os.path.join(shims.REFERENCE, "pfb", "utils", "misc.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    lines = src.splitlines()
+    chunk = [("\n".join(lines[n.lineno - 1:n.end_lineno])) for n in tree.body
+             if isinstance(n, ast.FunctionDef) and n.name == "dds2cubes"][0]
+    da = types.SimpleNamespace(zeros=lambda shape, chunks=None, dtype=None: np.zeros(shape, dtype=dtype),
+                               stack=np.stack)
+    dask = types.SimpleNamespace(compute=lambda *a: a)
+    ns = {"np": np, "da": da, "dask": dask}
+    exec(chunk, ns)
+    dds2cubes = ns["dds2cubes"]
+    for tag, dt in (("stage_f64", np.float64), ("stage_f32", np.float32)):
+        rng = np.random.default_rng(427)
+        nband, nx, ny, nxp, nyp, nbasis, nym, nxm = 3, 20, 16, 40, 32, 2, 24, 27
+        cdt = np.complex64 if dt == np.float32 else np.complex128
+        dds, flat = [], {}
+        for i, b in enumerate([0, 1, 1, 2, 0]):          # several time chunks per band
+            arrs = dict(DIRTY=rng.standard_normal((nx, ny)).astype(dt),
+                        BEAM=(0.5 + rng.random((nx, ny))).astype(dt),
+                        RESIDUAL=rng.standard_normal((nx, ny)).astype(dt),
+                        PSF=rng.standard_normal((nxp, nyp)).astype(dt),
+                        PSFHAT=(rng.standard_normal((nxp, nyp // 2 + 1)) +
+                                1j * rng.standard_normal((nxp, nyp // 2 + 1))).astype(cdt),
+                        MODEL=rng.standard_normal((nx, ny)).astype(dt),
+                        DUAL=rng.standard_normal((nbasis, nym, nxm)).astype(dt),
+                        WSUM=np.array([0.5 + rng.random()], dtype=dt))
+            dds.append(FakeDS(b, **arrs))
+            for k, v in arrs.items():
+                flat[f"ds{i}_{k}"] = v
+            flat[f"ds{i}_bandid"] = np.int64(b)
+        out = {}
+        for ap in (False, True):
+            r = dds2cubes(dds, nband, apparent=ap)
+            for name, a in zip(("dirty", "model", "residual", "psf", "psfhat", "mean_beam", "wsums", "dual"), r):
+                out[f"{name}_ap{int(ap)}"] = np.asarray(a)
+        save(tag, nds=np.int64(len(dds)), nband=np.int64(nband), **flat, **out)
+
+
+if __name__ == "__main__" and "--stage-only" in sys.argv:
+    gen_stage()
+elif __name__ == "__main__" and "--clean-only" in sys.argv:
     gen_clean()
 elif __name__ == "__main__" and "--glue-only" in sys.argv:
     gen_glue()
@@ -380,3 +449,4 @@ elif __name__ == "__main__":
     gen_solvers()
     gen_glue()
     gen_clean()
+    gen_stage()
