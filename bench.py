@@ -49,15 +49,23 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-bands", type=int, default=1)
+    ap.add_argument("--config", type=int, default=0, choices=[0, 1, 2, 3, 4, 5],
+                    help="BASELINE.json configuration (sets --nband/--nx): 1 = 1x512^2, 2 = 4x2048^2, "
+                         "3 = 8x4096^2 (default workload), 4 = 16x8192^2, 5 = 64x10240^2")
     ap.add_argument("--no-secondary", action="store_true",
                     help="skip the secondary lines (config 2 f32/f64, config 3 f64) of the N=1 run")
     ap.add_argument("--no-parity", action="store_true",
                     help="N>1: skip the sharded-vs-single-GPU parity check (parity_vs_n1)")
     ap.add_argument("--parity-iters", type=int, default=10)
+    ap.add_argument("--force-subset-parity", action="store_true",
+                    help="testing aid: take the one-band-per-rank parity path used by the large configurations")
     ap.add_argument("--ncu-step", action="store_true",
                     help="profiling aid: run ONE iteration between cudaProfilerStart/Stop and exit "
                          "(use with ncu --profile-from-start off); prints no bench line")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.config:
+        a.nband, a.nx = {1: (1, 512), 2: (4, 2048), 3: (8, 4096), 4: (16, 8192), 5: (64, 10240)}[a.config]
+    return a
 
 
 def workload_name(a):
@@ -312,6 +320,14 @@ def parity_vs_n1(torch, dist, a, P, rank, world, dev):
     from pfb_b200 import parallel
     from pfb_b200.opt.primal_dual import primal_dual_optimised
     nit = a.parity_iters
+    subset = None
+    if P is None:
+        # the whole cube cannot be gathered on one GPU: the same image size and code path with
+        # ONE band per rank
+        subset = world
+        a = argparse.Namespace(**vars(a))
+        a.nband = world
+        P = Problem(torch, world, a.nx, a.dtype, [rank], dev, rank, world)
     x, v = P.zeros()
     P.pd(x, v, nit)
     path = "rec" if getattr(primal_dual_optimised, "last_rec", False) else "slab"
@@ -352,8 +368,11 @@ def parity_vs_n1(torch, dist, a, P, rank, world, dev):
                 return float(torch.linalg.vector_norm((p.double() - q.double()).view(-1)) /
                              torch.linalg.vector_norm(q.double().view(-1)))
             res = {"rel_l2_x": rel(xs, x1), "rel_l2_v": rel(vs, v1), "iters": nit, "path": path,
-                   "tol": 1e-5, "x_nonzero": bool(x1.any()),
-                   "note": "sharded primal_dual_optimised vs the single-GPU path on the whole cube (rank 0)"}
+                   "tol": 1e-5, "x_nonzero": bool(x1.any()), "bands": a.nband,
+                   "note": ("sharded primal_dual_optimised vs the single-GPU path on the whole cube (rank 0)"
+                            if subset is None else
+                            f"the whole cube does not fit one GPU: same image size and code path on a "
+                            f"{subset}-band cube (one band per rank) vs the single-GPU path on rank 0")}
         finally:
             parallel.enable()
     dist.barrier()
@@ -390,6 +409,23 @@ def run_ours(a):
         raise SystemExit("nband must be divisible by the number of GPUs")
     nbl = nb // world
     bands = list(range(rank * nbl, (rank + 1) * nbl))
+    # can rank 0 hold the WHOLE cube (psfhat + the plan's copy + scratch, two duals, images) next to
+    # its own shard for the parity check?  If not, the check runs first, on a one-band-per-rank cube.
+    sz = 4 if a.dtype == "f32" else 8
+    per_band = (2 * nx) * (nx + 1) * 2 * sz * 2.5 + 5 * (nx + 24) ** 2 * sz * 5 + nx * nx * sz * 8
+    big = world > 1 and (nb * per_band > 60e9 or a.force_subset_parity)
+    if nb * per_band > 60e9:
+        # pinning the whole dual on the host (tens of GB per rank) is not safe to assume: no e2e leg
+        a.no_e2e = True
+    parity = None
+    if big and not a.no_parity:
+        parity = parity_vs_n1(torch, dist, a, None, rank, world, dev)
+        from pfb_b200.operators import psf as _psf
+        _psf.clear_plan_cache()
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        torch.cuda.reset_peak_memory_stats()
     P = Problem(torch, nb, nx, a.dtype, bands, dev, rank, world)
     rdt, s, psi, nbasis, shape_v = P.rdt, P.s, P.psi, P.nbasis, P.shape_v
     psfhat, dirty, hessnorm, lam = P.psfhat, P.dirty, P.hessnorm, P.lam
@@ -464,9 +500,17 @@ def run_ours(a):
         c = kern.setdefault(k, [0, 0.0])
         c[0] += int(n)
         c[1] += float(t)
+    # ---- memory in use after the timed region
+    free_b, total_b = torch.cuda.mem_get_info()
+    mem = torch.tensor([float(total_b - free_b), float(torch.cuda.max_memory_allocated())], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(mem, op=dist.ReduceOp.MAX)
+    memory = {"device_used_gb_max_over_ranks": round(float(mem[0]) / 1e9, 2),
+              "torch_peak_allocated_gb_max_over_ranks": round(float(mem[1]) / 1e9, 2),
+              "note": "after the timed region: device memory in use (cudaMemGetInfo: torch pool + the library's "
+                      "plan scratch) and torch's peak allocation"}
     # ---- N>1: what the sharded path computes, against the single-GPU path (outside timing)
-    parity = None
-    if world > 1 and not a.no_parity:
+    if world > 1 and not a.no_parity and not big:
         del x, v
         torch.cuda.empty_cache()
         parity = parity_vs_n1(torch, dist, a, P, rank, world, dev)
@@ -622,7 +666,7 @@ def finish_ours(a, env):
         "step_roofline": {"fused_compulsory_bytes_per_step_per_gpu": fused_iter,
                           "frac_of_hbm_peak": round(step_frac, 4)},
         "kernels": kernels, "ops": ops, "pcg": g.get("pcg_line"), "cpu_baseline": cpu,
-        "secondary": secondary, "parity_vs_n1": g.get("parity"),
+        "secondary": secondary, "parity_vs_n1": g.get("parity"), "memory": g.get("memory"),
     }
     return line
 
