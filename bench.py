@@ -343,6 +343,14 @@ def parity_vs_n1(torch, dist, a, P, rank, world, dev):
         psf_all = torch.view_as_complex(psf_all)
     dirty_all = gather(P.dirty)
     del x, v
+    lam_, hn_, s_, nbasis_, shape_v_, rdt_ = P.lam, P.hessnorm, P.s, P.nbasis, P.shape_v, P.rdt
+    if subset is not None:          # make room for the whole subset cube on rank 0
+        from pfb_b200.operators import psf as _psf0
+        del P
+        _psf0.clear_plan_cache()
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
     res = None
     if rank == 0:
         from functools import partial
@@ -353,20 +361,25 @@ def parity_vs_n1(torch, dist, a, P, rank, world, dev):
         parallel.disable()
         try:
             nb = a.nband
-            psi = Psi(nb, a.nx, a.nx, BASES, NLEVEL, 1, dtype=np.float32 if P.s == 4 else np.float64)
+            psi = Psi(nb, a.nx, a.nx, BASES, NLEVEL, 1, dtype=np.float32 if s_ == 4 else np.float64)
             xo = torch.empty_like(dirty_all)
             conv = partial(psf_convolve_cube, None, None, xo, psf_all, 2 * a.nx)
             x1 = torch.zeros_like(dirty_all)
-            v1 = torch.zeros((nb,) + tuple(P.shape_v[1:]), dtype=P.rdt, device=dev)
-            w1 = torch.ones(P.shape_v[1:], dtype=P.rdt, device=dev)
-            primal_dual_optimised(x1, v1, P.lam, psi.hdot, psi.dot, P.hessnorm, None, w1, None,
-                                  Grad21(conv, dirty_all), nu=P.nbasis, tol=0.0, maxit=nit,
+            v1 = torch.zeros((nb,) + tuple(shape_v_[1:]), dtype=rdt_, device=dev)
+            w1 = torch.ones(shape_v_[1:], dtype=rdt_, device=dev)
+            primal_dual_optimised(x1, v1, lam_, psi.hdot, psi.dot, hn_, None, w1, None,
+                                  Grad21(conv, dirty_all), nu=nbasis_, tol=0.0, maxit=nit,
                                   positivity=1, verbosity=0)
             torch.cuda.synchronize()
 
-            def rel(p, q):
-                return float(torch.linalg.vector_norm((p.double() - q.double()).view(-1)) /
-                             torch.linalg.vector_norm(q.double().view(-1)))
+            def rel(p, q):          # band by band: no cube-sized fp64 temporaries
+                num = den = 0.0
+                for b_ in range(p.shape[0]):
+                    qd = q[b_].double()
+                    num += float(torch.sum((p[b_].double() - qd) ** 2))
+                    den += float(torch.sum(qd ** 2))
+                    del qd
+                return math.sqrt(num / den)
             res = {"rel_l2_x": rel(xs, x1), "rel_l2_v": rel(vs, v1), "iters": nit, "path": path,
                    "tol": 1e-5, "x_nonzero": bool(x1.any()), "bands": a.nband,
                    "note": ("sharded primal_dual_optimised vs the single-GPU path on the whole cube (rank 0)"
