@@ -454,6 +454,52 @@ def test_minor_cycle_vs_oracle(dtype, nband, nx):
         assert rel(xs, truth) < 2 * rel(oxs, truth) + 1e-5
 
 
+@pmp("dtype", [np.float32, np.float64])
+def test_pd_tolerance_exit_lagged_check(dtype, monkeypatch):
+    """tol > 0 without a reweighter: the convergence test lags one iteration behind the GPU
+    (opt/primal_dual.py `lagged`), so the exit is noticed late and the extra iteration must be
+    discarded: same iteration count and the same model / dual as the oracle, and as the
+    non-lagged loop."""
+    from pfb_b200.operators.psf import psf_convolve_cube
+    from pfb_b200.operators.psi import Psi
+    from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
+    nband, nx = 2, 256
+    psfhat, dirty, oconv, _ = _problem(nband, nx, dtype)
+    nxp = 2 * nx
+    psi = Psi(nband, nx, nx, BASES, 3, 1)
+    opsi = ref.Psi(nband, nx, nx, BASES, 3)
+    conv = partial(psf_convolve_cube, None, None, np.empty_like(dirty), psfhat, nxp)
+    lam = 0.5 * float(np.std(dirty.sum(axis=0)))
+    shape_v = (nband, 5, psi.Nymax, psi.Nxmax)
+    w = np.ones(shape_v[1:], dtype)
+    # eps history of the oracle -> a tolerance met at iteration 6 of at most 30
+    hist = []
+    ox, ov = np.zeros_like(dirty), np.zeros(shape_v, dtype)
+    for it in range(8):
+        xp_ = ox.copy()
+        ref.primal_dual_optimised(ox, ov, lam, opsi.hdot, opsi.dot, 1.3, None, w, None,
+                                  lambda z: oconv(z) - dirty, nu=5, tol=0.0, maxit=1)
+        hist.append(ref.norm_diff(ox, xp_))
+    tol = 0.5 * (hist[5] + hist[6]) if hist[6] < hist[5] else None
+    assert tol is not None and all(h > tol for h in hist[:6]), hist
+    ox, ov = np.zeros_like(dirty), np.zeros(shape_v, dtype)
+    ref.primal_dual_optimised(ox, ov, lam, opsi.hdot, opsi.dot, 1.3, None, w, None,
+                              lambda z: oconv(z) - dirty, nu=5, tol=tol, maxit=30)
+    res = {}
+    for lag in (True, False):
+        if lag:
+            monkeypatch.delenv("PFB_PD_NOLAG", raising=False)
+        else:
+            monkeypatch.setenv("PFB_PD_NOLAG", "1")
+        x, v = np.zeros_like(dirty), np.zeros(shape_v, dtype)
+        primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, 1.3, None, w, None, Grad21(conv, dirty),
+                              nu=5, tol=tol, maxit=30, verbosity=0)
+        res[lag] = (x, v)
+        assert rel(x, ox) < (1e-11 if dtype == np.float64 else 1e-5)
+        assert rel(v, ov) < (1e-11 if dtype == np.float64 else 1e-5)
+    assert np.array_equal(res[True][0], res[False][0]) and np.array_equal(res[True][1], res[False][1])
+
+
 def test_fused_primal_pass_matches_unfused(monkeypatch):
     """pfb_hess_apply_primal (primal step as the epilogue of the TMA pass C) against the
     separate pfb_hess_apply + pfb_pd_primal_lin kernels: same arithmetic in the same order,
