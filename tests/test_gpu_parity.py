@@ -472,7 +472,7 @@ def test_pd_tolerance_exit_lagged_check(dtype, monkeypatch):
     lam = 0.5 * float(np.std(dirty.sum(axis=0)))
     shape_v = (nband, 5, psi.Nymax, psi.Nxmax)
     w = np.ones(shape_v[1:], dtype)
-    # eps history of the oracle -> a tolerance met at iteration 6 of at most 30
+    # eps history of the oracle -> a tolerance first met at iteration 4 of at most 30
     hist = []
     ox, ov = np.zeros_like(dirty), np.zeros(shape_v, dtype)
     for it in range(8):
@@ -480,8 +480,9 @@ def test_pd_tolerance_exit_lagged_check(dtype, monkeypatch):
         ref.primal_dual_optimised(ox, ov, lam, opsi.hdot, opsi.dot, 1.3, None, w, None,
                                   lambda z: oconv(z) - dirty, nu=5, tol=0.0, maxit=1)
         hist.append(ref.norm_diff(ox, xp_))
-    tol = 0.5 * (hist[5] + hist[6]) if hist[6] < hist[5] else None
-    assert tol is not None and all(h > tol for h in hist[:6]), hist
+    j = 4                                        # eps oscillates early on: stop at the first dip below tol
+    tol = 1.02 * hist[j]
+    assert all(h > tol for h in hist[:j]), hist
     ox, ov = np.zeros_like(dirty), np.zeros(shape_v, dtype)
     ref.primal_dual_optimised(ox, ov, lam, opsi.hdot, opsi.dot, 1.3, None, w, None,
                               lambda z: oconv(z) - dirty, nu=5, tol=tol, maxit=30)
