@@ -61,23 +61,34 @@ class HessPlan:
             self._h = ctypes.c_void_p()
 
 
-_PLANS = {}
+_PLANS = {}            # (shape key) -> list of plans, most recently used first
+_MAX_PLANS_PER_SHAPE = 2
 
 
 def _psf_key(psfhat):
+    """Identity + cheap content fingerprint of a psfhat.  torch: storage pointer and the
+    in-place version counter.  numpy: pointer, layout and a strided sample of the contents
+    (about 4096 values), so an array updated in place between major cycles is noticed without
+    reading it whole."""
     if isinstance(psfhat, torch.Tensor):
         return ("t", psfhat.data_ptr(), tuple(psfhat.shape), psfhat._version)
-    return ("n", psfhat.ctypes.data, psfhat.shape, psfhat.strides)
+    flat = psfhat.reshape(-1) if psfhat.flags.c_contiguous else psfhat.ravel()
+    step = max(1, flat.size // 4096)
+    sample = flat[::step]
+    fp = (complex(sample.sum()), complex(flat[0]), complex(flat[-1]))
+    return ("n", psfhat.ctypes.data, psfhat.shape, psfhat.strides, fp)
 
 
 def clear_plan_cache():
-    """Drop cached plans (call after modifying a psfhat array in place)."""
+    """Drop cached plans (releases their device memory)."""
     _PLANS.clear()
 
 
 def get_plan(psfhat, lastsize, x_shape, x_dtype_code):
-    """Plan for (shape, psfhat).  The transposed/scaled device copy of psfhat is
-    built once per psfhat object and reused by every later call."""
+    """Plan bound to THIS psfhat.  Plans are cached per (shape, psfhat): a second psfhat of the
+    same shape (a reweighter or callback convolving with another PSF mid-solve) gets its own
+    plan instead of re-binding the one a running solver holds; at most
+    _MAX_PLANS_PER_SHAPE live plans per shape, least recently used dropped first."""
     if len(x_shape) == 2:
         nband, (nx, ny) = 1, x_shape
     else:
@@ -86,18 +97,30 @@ def get_plan(psfhat, lastsize, x_shape, x_dtype_code):
     if psfhat.shape[-1] != lastsize // 2 + 1:
         raise ValueError(f"psfhat last axis {psfhat.shape[-1]} != lastsize//2+1 = {lastsize // 2 + 1}")
     key = (nband, nx, ny, nxp, lastsize, x_dtype_code)
-    plan = _PLANS.get(key)
-    if plan is None:
-        plan = HessPlan(*key)
-        _PLANS[key] = plan
+    plans = _PLANS.setdefault(key, [])
     pk = _psf_key(psfhat)
-    if plan.psf_key != pk:
-        pd = _dev.to_dev(psfhat)
-        if _dev.dcode(pd) != x_dtype_code:
-            raise TypeError("psfhat precision does not match the image precision")
-        plan.set_psfhat(pd)
-        plan.psf_key = pk
-        plan._keep = psfhat      # keep the id()/data_ptr key valid
+    for i, plan in enumerate(plans):
+        if plan.psf_key == pk:
+            if i:
+                plans.insert(0, plans.pop(i))
+            return plan
+    # same array object, new contents (updated in place): re-bind its plan rather than keep two
+    plan = None
+    for i, cand in enumerate(plans):
+        if cand.psf_key is not None and cand.psf_key[:2] == pk[:2]:
+            plan = plans.pop(i)
+            break
+    if plan is None:
+        if len(plans) >= _MAX_PLANS_PER_SHAPE:
+            plans.pop()
+        plan = HessPlan(*key)
+    plans.insert(0, plan)
+    pd = _dev.to_dev(psfhat)
+    if _dev.dcode(pd) != x_dtype_code:
+        raise TypeError("psfhat precision does not match the image precision")
+    plan.set_psfhat(pd)
+    plan.psf_key = pk
+    plan._keep = psfhat      # keep the pointer in the key valid
     return plan
 
 

@@ -99,3 +99,31 @@ def test_psi_psib_attribute(backend):
         assert (pb.Nxmax, pb.Nymax) == (opsi.Nxmax, opsi.Nymax)
         assert list(pb.bases) == ["self", "db2"]
         assert pb.tables(1)["Ntotx"] == psi.tables(1)["Ntotx"]
+
+
+def test_plan_cache_tracks_psf_identity_and_contents(backend):
+    """a numpy psfhat updated in place must not keep its stale device copy, and a
+    second psfhat of the same shape must not re-bind the plan another caller still holds."""
+    from pfb_b200.operators import psf as P
+    rng = np.random.default_rng(2)
+    nband, nx, ny, nxp, nyp = 1, 24, 20, 64, 64
+    mk = lambda: np.fft.rfft2(rng.standard_normal((nband, nxp, nyp)), axes=(1, 2))   # noqa: E731
+    pa, pb = mk(), mk()
+    x = rng.standard_normal((nband, nx, ny))
+    xpad, xhat = np.empty((nband, nxp, nyp)), np.empty(pa.shape, complex)
+
+    def conv(ph):
+        return P.psf_convolve_cube(None, None, np.empty_like(x), ph, nyp, x)
+
+    def oconv(ph):
+        return ref.psf_convolve_cube(xpad, xhat, np.empty_like(x), ph, nyp, x).copy()
+    assert rel(conv(pa), oconv(pa)) < 1e-11
+    plan_a = P.get_plan(pa, nyp, x.shape, 1)
+    assert rel(conv(pb), oconv(pb)) < 1e-11                 # another PSF, same shape ...
+    assert P.get_plan(pa, nyp, x.shape, 1) is plan_a        # ... did not take pa's plan away
+    assert rel(conv(pa), oconv(pa)) < 1e-11
+    pa *= 0.5                                               # in-place update between major cycles
+    pa[0, 3, 4] += 1.0
+    assert rel(conv(pa), oconv(pa)) < 1e-11
+    assert P.get_plan(pa, nyp, x.shape, 1) is plan_a        # same array object: re-bound, not duplicated
+    assert len(next(iter(P._PLANS.values()))) == 2
