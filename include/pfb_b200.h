@@ -91,6 +91,12 @@ int pfb_dual_update(const void *vp, void *v, const void *weight, void *u,
  * vbar, ubar, weight: n elements; vp, v: (nband, n). */
 int pfb_dual_update_rec(const void *vp, void *v, void *vbar, const void *ubar, const void *weight,
                         int nband, long long n, double lam, double sigma, int dtype, void *stream);
+/* The same update with the per-band half moved into the analysis: pfb_dual_factor does the
+ * band-independent half (S = vbar + sigma ubar; f = shrink factor; vbar <- f S; f stored) and
+ * pfb_psi_dot_nat_dual (below) stores v_b = (vp_b + sigma Psi^T x_b) f straight from the analysis
+ * kernels' registers, so the analysed coefficients u_b are never written or read back. */
+int pfb_dual_factor(void *vbar, const void *ubar, const void *weight, void *f, long long n,
+                    double lam, double sigma, int dtype, void *stream);
 int pfb_dual_partial(const void *vp, const void *v, void *bsum, int nband, long long n,
                      long long band_stride, double sigma, int mode, int dtype, void *stream);
 int pfb_dual_apply(const void *vp, void *v, const void *bsum, const void *weight,
@@ -219,6 +225,12 @@ int pfb_psi_from_nat(const pfb_psi_plan *plan, int nband, const void *nat, void 
 /* Psi.dot / Psi.hdot on the natural layout (same arithmetic, no transposition);
  * nat2 != NULL: synthesis of 2*nat - nat2.  x must be 16-byte aligned. */
 int pfb_psi_dot_nat(const pfb_psi_plan *plan, const void *x, void *nat, void *stream);
+/* Analysis fused with the per-band half of the l21 dual update (pfb/opt/primal_dual.py:135-136,
+ * pfb/prox/prox_21m.py:75-103): v_nat[b] = (vp_nat[b] + sigma * Psi^T x[b]) * f_nat, f_nat being
+ * ONE band-shaped block (nbasis, stride) from pfb_dual_factor.  vp_nat must not alias v_nat;
+ * padding cells of v_nat are not written (keep them zero). */
+int pfb_psi_dot_nat_dual(const pfb_psi_plan *plan, const void *x, const void *vp_nat,
+                         const void *f_nat, double sigma, void *v_nat, void *stream);
 int pfb_psi_hdot_nat(const pfb_psi_plan *plan, const void *nat, const void *nat2,
                      void *xo, void *stream);
 

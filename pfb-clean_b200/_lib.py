@@ -35,6 +35,8 @@ _SIGS = {
     "pfb_prox21": (c_int, [_P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
     "pfb_dual_update": (c_int, [_P, _P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, c_int, _P]),
     "pfb_dual_update_rec": (c_int, [_P, _P, _P, _P, _P, c_int, c_longlong, c_double, c_double, c_int, _P]),
+    "pfb_dual_factor": (c_int, [_P, _P, _P, _P, c_longlong, c_double, c_double, c_int, _P]),
+    "pfb_psi_dot_nat_dual": (c_int, [_P, _P, _P, _P, c_double, _P, _P]),
     "pfb_dual_partial": (c_int, [_P, _P, _P, c_int, c_longlong, c_longlong, c_double, c_int, c_int, _P]),
     "pfb_dual_apply": (c_int, [_P, _P, _P, _P, _P, c_int, c_longlong, c_longlong, c_double, c_double, c_int, c_int, _P]),
     "pfb_axpby": (c_int, [_P, c_double, _P, c_double, _P, c_longlong, c_int, _P]),

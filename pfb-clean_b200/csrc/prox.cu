@@ -369,6 +369,29 @@ k_dual_rec(const T *vp, T *v, T *vbar, const T *__restrict__ ubar, const T *__re
     }
 }
 
+// The band-independent half of k_dual_rec on its own: S = vbar + sigma ubar; f = shrink(S);
+// vbar <- f S; fout = f.  The per-band half, v_b = (vp_b + sigma u_b) f, is then the epilogue of
+// the analysis kernels (pfb_psi_dot_nat_dual), so u_b never exists in memory.
+template <class T, int V>
+__global__ void __launch_bounds__(256)
+k_dual_factor(T *vbar, const T *__restrict__ ubar, const T *__restrict__ w, T *__restrict__ fout, long n,
+              double lam, double sigma) {
+    long nv = n / V;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long)gridDim.x * blockDim.x) {
+        long k = i * V;
+        Pack<T, V> vb = ld<T, V>(vbar + k), ub = ld<T, V>(ubar + k), wk = ld<T, V>(w + k), so, fo;
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            const double S = (double)vb.v[e] + sigma * (double)ub.v[e];
+            const double f = shrink_factor(S, lam * (double)wk.v[e], 0);
+            so.v[e] = (T)(S * f);
+            fo.v[e] = (T)f;
+        }
+        st<T, V>(vbar + k, so);
+        st<T, V>(fout + k, fo);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // out = a*x + b*y  (numexpr '2.0*v - vp', 'xp - tau*xout' of
 // pfb/opt/primal_dual.py:137,140 and the axpys of pfb/opt/pcg.py:92-104);
@@ -718,6 +741,17 @@ static int dual_rec_t(const T *vp, T *v, T *vbar, const T *ubar, const T *w, int
 }
 
 template <class T>
+static int dual_factor_t(T *vbar, const T *ubar, const T *w, T *f, long n, double lam, double sigma,
+                         cudaStream_t st) {
+    const int V = 16 / sizeof(T);
+    bool vec = (n % V == 0) && aligned16<T>(vbar) && aligned16<T>(ubar) && aligned16<T>(w) && aligned16<T>(f);
+    if (vec) launch(&k_dual_factor<T, V>, dim3(stream_grid(n / V)), dim3(256), 0, st, vbar, ubar, w, f, n, lam, sigma);
+    else launch(&k_dual_factor<T, 1>, dim3(stream_grid(n)), dim3(256), 0, st, vbar, ubar, w, f, n, lam, sigma);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+template <class T>
 static int axpby_t(T *out, double a, const T *x, double b, const T *y, long n, cudaStream_t st) {
     const int V = 16 / sizeof(T);
     bool vec = (n % V == 0) && aligned16<T>(out) && aligned16<T>(x) && aligned16<T>(y);
@@ -848,6 +882,16 @@ int pfb_dual_update_rec(const void *vp, void *v, void *vbar, const void *ubar, c
     PFB_DISPATCH(dtype,
                  dual_rec_t<float>((const float *)vp, (float *)v, (float *)vbar, (const float *)ubar, (const float *)weight, nband, n, lam, sigma, st),
                  dual_rec_t<double>((const double *)vp, (double *)v, (double *)vbar, (const double *)ubar, (const double *)weight, nband, n, lam, sigma, st));
+}
+
+int pfb_dual_factor(void *vbar, const void *ubar, const void *weight, void *f, long long n, double lam,
+                    double sigma, int dtype, void *stream) {
+    if (!vbar || !ubar || !weight || !f || n < 0) return fail(PFB_ERR_BAD_ARG, "pfb_dual_factor: bad argument");
+    if (n == 0) return PFB_OK;
+    cudaStream_t st = as_stream(stream);
+    PFB_DISPATCH(dtype,
+                 dual_factor_t<float>((float *)vbar, (const float *)ubar, (const float *)weight, (float *)f, n, lam, sigma, st),
+                 dual_factor_t<double>((double *)vbar, (const double *)ubar, (const double *)weight, (double *)f, n, lam, sigma, st));
 }
 
 int pfb_axpby(void *out, double a, const void *x, double b, const void *y, long long n,

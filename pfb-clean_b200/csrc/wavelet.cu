@@ -58,6 +58,13 @@ struct LevelArgs {
     long cn_stride;                // elements per (band,basis) block of the natural layout
     int first, last;               // level is the finest / the coarsest
     int nx, ny;
+    // fused dual update of the natural-layout analysis (pfb_psi_dot_nat_dual): when fz_vp is set
+    // a coefficient u is not stored; v = (vp + sigma u) * f is, with vp laid out like the
+    // output and f like ONE band of it (fz_dvp / fz_df: element offsets from the output cube to
+    // vp and to f's band-0 position; the kernels subtract the band part)
+    const void *fz_vp;
+    long fz_dvp, fz_df;
+    double fz_sigma;
 };
 
 template <class T, int F>
@@ -491,7 +498,8 @@ static int pick_nj(int c0, long ctas_per_chunk) {
 // nat = false: alpha is the reference's slab cube; nat = true: alpha is the
 // natural-orientation layout (streaming kernels only).
 template <class T>
-static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, bool nat, cudaStream_t st) {
+static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, bool nat, cudaStream_t st,
+                     const T *fz_vp = nullptr, const T *fz_f = nullptr, double fz_sigma = 0.0) {
     if (int rc = ensure_scratch(p)) return rc;
     size_t smem = sizeof(T) * kAnaSmemElems;
     PFB_CUDA_OK(cudaFuncSetAttribute(&k_dwt_level<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -506,6 +514,12 @@ static int psi_dot_t(const pfb_psi_plan *p, const T *x, T *alpha, bool nat, cuda
         LevelArgs a;
         memset(&a, 0, sizeof a);
         fill_common(p, a, l);
+        if (fz_vp) {
+            a.fz_vp = fz_vp;
+            a.fz_dvp = fz_vp - alpha;
+            a.fz_df = fz_f - alpha;
+            a.fz_sigma = fz_sigma;
+        }
         int maxC0 = 0, maxC1 = 0, wC0 = 0, wC1 = 0;
         for (int b = 0; b < p->nbasis; ++b) {
             const BasisPlan &bp = p->bp[b];
@@ -928,6 +942,18 @@ int pfb_psi_dot_nat(const pfb_psi_plan *p, const void *x, void *nat, void *strea
     if (int rc = nat_check(p, x, nat, 1, "pfb_psi_dot_nat")) return rc;
     if (p->dtype == PFB_F32) return psi_dot_t<float>(p, (const float *)x, (float *)nat, true, as_stream(stream));
     return psi_dot_t<double>(p, (const double *)x, (double *)nat, true, as_stream(stream));
+}
+
+int pfb_psi_dot_nat_dual(const pfb_psi_plan *p, const void *x, const void *vp_nat, const void *f_nat,
+                         double sigma, void *v_nat, void *stream) {
+    if (int rc = nat_check(p, x, v_nat, 1, "pfb_psi_dot_nat_dual")) return rc;
+    if (!vp_nat || !f_nat || vp_nat == v_nat)
+        return fail(PFB_ERR_BAD_ARG, "pfb_psi_dot_nat_dual: vp and f must be given and vp must not alias the output");
+    if (p->dtype == PFB_F32)
+        return psi_dot_t<float>(p, (const float *)x, (float *)v_nat, true, as_stream(stream), (const float *)vp_nat,
+                                (const float *)f_nat, sigma);
+    return psi_dot_t<double>(p, (const double *)x, (double *)v_nat, true, as_stream(stream), (const double *)vp_nat,
+                             (const double *)f_nat, sigma);
 }
 
 int pfb_psi_hdot_nat(const pfb_psi_plan *p, const void *nat, const void *nat2, void *xo, void *stream) {

@@ -52,6 +52,18 @@ static const int kPD = 8;            // prefetch distance (coefficient rows in f
 __host__ __device__ constexpr int stream_ring_elems() { return kPD * 2 * 32 * 2; }
 
 template <class T> struct Vec2 { T v[2]; };
+
+// Fused dual update (pfb_psi_dot_nat_dual): store v = (vp + sigma u) * f instead of the
+// coefficient u.  dv, df: element offsets from the output location to vp and to f.
+template <class T> struct DualFz {
+    bool on;
+    long dv, df;
+    T sigma;
+    __device__ __forceinline__ void put(T *dst, const T u) const {
+        if (on) *dst = (dst[dv] + sigma * u) * dst[df];
+        else *dst = u;
+    }
+};
 __device__ __forceinline__ Vec2<float> ldv2(const float *p) {
     float2 q = *reinterpret_cast<const float2 *>(p);
     Vec2<float> r; r.v[0] = q.x; r.v[1] = q.y; return r;
@@ -103,7 +115,8 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
                                                 const LevelDesc &d, T *slab, const int ldslab,
                                                 T *ll_out, const bool last, const int strip,
                                                 const int chunk, const int NJ, T *s_out,
-                                                T *ring, const int dbg, const int SW) {
+                                                T *ring, const int dbg, const int SW,
+                                                const DualFz<T> fz = DualFz<T>{false, 0, 0, (T)0}) {
     const int lane = threadIdx.x & 31;
     const int T0 = SW * strip;
     const int c = 2 * T0 - 6 + 2 * lane;             // first column of this lane's pair
@@ -166,11 +179,11 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
         if (NAT) {
             if (jx >= JX0 && tval) {
                 T *dst = slab + d.off1 + (long)jx * d.ldn + ta;
-                if (last) dst[-(long)d.qs] = o[0];
+                if (last) fz.put(dst - (long)d.qs, o[0]);
                 else ll_out[(long)jx * d.ld_out + ta] = o[0];
-                dst[0] = o[1];
-                dst[d.qs] = o[2];
-                dst[2 * (long)d.qs] = o[3];
+                fz.put(dst, o[1]);
+                fz.put(dst + d.qs, o[2]);
+                fz.put(dst + 2 * (long)d.qs, o[3]);
             }
             continue;
         }
@@ -230,11 +243,16 @@ k_dwt_stream(const T *__restrict__ img, const T *__restrict__ scr_in, T *scr_out
     const T *in = a.first ? img + band * a.img_band_stride : scr_in + so;
     const int ld = a.first ? a.ny : d.ld_in;
     T *ll = scr_out + so;
+    DualFz<T> fz;
+    fz.on = NAT && a.fz_vp != nullptr;
+    fz.dv = a.fz_dvp;
+    fz.df = a.fz_df - (long)band * a.nbasis * a.cn_stride;      // f has no band axis
+    fz.sigma = (T)a.fz_sigma;
     switch (d.F) {
-    case 2: dwt_stream_task<T, 2, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW); break;
-    case 4: dwt_stream_task<T, 4, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW); break;
-    case 6: dwt_stream_task<T, 6, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW); break;
-    case 8: dwt_stream_task<T, 8, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW); break;
+    case 2: dwt_stream_task<T, 2, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW, fz); break;
+    case 4: dwt_stream_task<T, 4, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW, fz); break;
+    case 6: dwt_stream_task<T, 6, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW, fz); break;
+    case 8: dwt_stream_task<T, 8, NAT>(in, ld, d, slab, a.Nxmax, ll, a.last, strip, chunk, NJ, s_out, ring, dbg, SW, fz); break;
     default: break;   // F = 10 (db5) is routed to the tile kernel by the host
     }
 }
@@ -334,6 +352,11 @@ k_dwt_stream_all(const T *__restrict__ img, T *scr_out, T *cn, LevelArgs a, DwtA
         pll[s] = a.last ? pq[s] - d.qs : scr_out + bb * a.scr_stride + ta;
         tv[s] = d.basis >= 0 && lane >= 3 && lane < 3 + SW && ta < d.C1 && !(dbg & 1);
     }
+    DualFz<T> fz;
+    fz.on = a.fz_vp != nullptr;
+    fz.dv = a.fz_dvp;
+    fz.df = a.fz_df - (long)band * a.nbasis * a.cn_stride;      // f has no band axis
+    fz.sigma = (T)a.fz_sigma;
     T *pself = cn;
     const bool sv = g.self_basis >= 0 && lane >= 3 && lane < 3 + SW && c < n1 && !(dbg & 2);
     if (g.self_basis >= 0) pself = cn + ((long)band * a.nbasis + g.self_basis) * a.cn_stride + c;
@@ -389,16 +412,26 @@ k_dwt_stream_all(const T *__restrict__ img, T *scr_out, T *cn, LevelArgs a, DwtA
             const DwtAllSlot &d = g.s[s];
             if (tv[s] && jx < d.C0) {
                 T *dst = pq[s] + (long)jx * d.ldn;
-                if (a.last) dst[-(long)d.qs] = o[s][0];
+                if (a.last) fz.put(dst - (long)d.qs, o[s][0]);
                 else pll[s][(long)jx * d.ld_out] = o[s][0];
-                dst[0] = o[s][1];
-                dst[d.qs] = o[s][2];
-                dst[2 * (long)d.qs] = o[s][3];
+                fz.put(dst, o[s][1]);
+                fz.put(dst + d.qs, o[s][2]);
+                fz.put(dst + 2 * (long)d.qs, o[s][3]);
             }
         }
         if (sv) {
-            if (2 * jx < n0) stv2(pself + (long)(2 * jx) * g.ld_self, q0);
-            if (2 * jx + 1 < n0) stv2(pself + (long)(2 * jx + 1) * g.ld_self, q1);
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr)
+                if (2 * jx + rr < n0) {
+                    T *dst = pself + (long)(2 * jx + rr) * g.ld_self;
+                    Vec2<T> q = rr ? q1 : q0;
+                    if (fz.on) {
+                        const Vec2<T> pv = ldv2(dst + fz.dv), ff = ldv2(dst + fz.df);
+                        q.v[0] = (pv.v[0] + fz.sigma * q.v[0]) * ff.v[0];
+                        q.v[1] = (pv.v[1] + fz.sigma * q.v[1]) * ff.v[1];
+                    }
+                    stv2(dst, q);
+                }
         }
     }
     cp_async_wait<0>();

@@ -143,6 +143,12 @@ class Psi(object):
         _lib.check(_lib.lib().pfb_psi_dot_nat(self._plan(_dev.dcode(x)), _dev.ptr(x), _dev.ptr(nat),
                                               _dev.stream()))
 
+    def dot_nat_dual(self, x, vp_nat, f_nat, sigma, v_nat):
+        """v_nat = (vp_nat + sigma * Psi^T x) * f_nat (f_nat: one band-shaped block); see
+        pfb_psi_dot_nat_dual in include/pfb_b200.h."""
+        _lib.check(_lib.lib().pfb_psi_dot_nat_dual(self._plan(_dev.dcode(x)), _dev.ptr(x), _dev.ptr(vp_nat),
+                                                   _dev.ptr(f_nat), float(sigma), _dev.ptr(v_nat), _dev.stream()))
+
     def hdot_nat(self, nat, xo, nat2=None):
         _lib.check(_lib.lib().pfb_psi_hdot_nat(self._plan(_dev.dcode(nat)), _dev.ptr(nat), _dev.ptr(nat2),
                                                _dev.ptr(xo), _dev.stream()))

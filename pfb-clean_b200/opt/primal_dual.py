@@ -161,6 +161,12 @@ def _dual_rec(vp, v, vbar, ubar, w, n, lam, sigma):
                                               _dev.dcode(v), _dev.stream()))
 
 
+def _dual_factor(vbar, ubar, w, f, n, lam, sigma):
+    """pfb_dual_factor: S = vbar + sigma ubar; f = shrink factor; vbar <- f S."""
+    _lib.check(_lib.lib().pfb_dual_factor(_dev.ptr(vbar), _dev.ptr(ubar), _dev.ptr(w), _dev.ptr(f), n,
+                                          float(lam), float(sigma), _dev.dcode(vbar), _dev.stream()))
+
+
 def _gap_index(psi_obj, device):
     """Flat indices (into nbasis*Nymax*Nxmax) of the slab cells Psi.dot never
     writes.  Found by running a 1-band analysis over a NaN-filled slab once."""
@@ -276,19 +282,33 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     # analyses that image itself.  The exchange is issued right behind the primal step and hidden
     # by the next PSF convolution.  The carried sum is re-synchronised exactly every
     # PFB_PAR_RESYNC (default 64) iterations to bound rounding drift.
-    rec = nat and lin and parallel.active() and not os.environ.get("PFB_PAR_NOREC")
-    primal_dual_optimised.last_rec = bool(rec)
+    # The same recursion lets the per-band half of the dual update ride in the ANALYSIS kernels'
+    # epilogue (pfb_psi_dot_nat_dual): the band-independent half (S, the shrink factor f, the new
+    # carried sum) is one small kernel over a band-shaped block, and v_b = (vp_b + sigma Psi^T x_b) f
+    # is stored straight from the analysis registers -- the analysed coefficients never exist in
+    # memory (5.4 GB less traffic per iteration at 8 x 4096^2).  Used on one GPU as well: over the
+    # reference's 450 iterations every fp32 path stays 1.1e-6 / 2.8e-6 from the fp64 trajectory,
+    # re-synchronised or not (profiles/r02/r02m_sharded_drift_450its.jsonl).
+    norec = parallel.active() and os.environ.get("PFB_PAR_NOREC")
+    fusedual = nat and lin and not norec and not os.environ.get("PFB_PD_NOFUSEDUAL")
+    rec = nat and lin and parallel.active() and not norec and not fusedual
+    primal_dual_optimised.last_rec = bool(rec or (fusedual and parallel.active()))
+    primal_dual_optimised.last_fusedual = bool(fusedual)
     xbar_work = None
-    if rec:
+    have_xbar = False
+    if rec or fusedual:
         P1 = getattr(P, "_one_band", None)
         if P1 is None:
-            P1 = P._one_band = Psi(1, P.nx, P.ny, P.bases, P.nlevel, 1)
+            P1 = P._one_band = Psi(1, P.nx, P.ny, P.bases, P.nlevel, 1,
+                                   dtype=np.float32 if va.dtype == torch.float32 else np.float64)
         assert P1.nat_stride(_dev.dcode(va)) == vcur.shape[2]
         xbar = torch.empty_like(xa[0])
-        ubar = torch.empty((1,) + tuple(vcur.shape[1:]), dtype=va.dtype, device=va.device)
+        ubar = torch.zeros((1,) + tuple(vcur.shape[1:]), dtype=va.dtype, device=va.device)
         vbar = torch.empty(tuple(vcur.shape[1:]), dtype=va.dtype, device=va.device)
         parallel.allreduce_sum(_band_sum(vprev, vbar))
         resync = int(os.environ.get("PFB_PAR_RESYNC", "64"))
+        if fusedual:
+            fbuf = torch.empty_like(vbar)
 
     eps = 1.0
     numreweight = 0
@@ -318,12 +338,28 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
         if nat:
             # not lin: the dual kernel leaves 2v - vp in the (dead) vp buffer: one coefficient
             # set for the synthesis to read, which is instruction-issue bound
-            if rec and xbar_work is None:
+            if (rec or fusedual) and not have_xbar:
                 xbar_work = parallel.allreduce_sum_async(_band_sum(xprev, xbar))
-            if not have_dot:
+            have_xbar = False
+            if fusedual:
+                if parallel.active():
+                    if fplan is None:
+                        g = gradient()               # hides the exchange of xbar
+                    if xbar_work is not None:
+                        xbar_work.wait()
+                xbar_work = None
+                P1.dot_nat(xbar[None], ubar)
+                if resync > 0 and k > 0 and k % resync == 0:
+                    parallel.allreduce_sum(_band_sum(vprev, vbar))
+                _dual_factor(vbar, ubar, w, fbuf, n, lam, sigma)
+                P.dot_nat_dual(xprev, vprev, fbuf, sigma, vcur)
+                have_dot = False
+            elif not have_dot:
                 P.dot_nat(xprev, vcur)
             have_dot = False
-            if rec:
+            if fusedual:
+                pass
+            elif rec:
                 g = gradient()                   # hides the exchange of xbar
                 if xbar_work is not None:
                     xbar_work.wait()
@@ -364,9 +400,10 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             parallel.allreduce_max(neg)
             xcur[:, neg.bool()] = 0
             norm_diff_terms(xcur, xprev, out=terms)
-        if rec and k + 1 < maxit:
+        if (rec or fusedual) and k + 1 < maxit:
             # next iteration's exchange: sum of the new model over the local bands
             xbar_work = parallel.allreduce_sum_async(_band_sum(xcur, xbar))
+            have_xbar = True
         if lagged:
             ev.record()
             if k > 0:
@@ -376,7 +413,7 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
                 if eps < tol:                # converged one iteration ago: iteration k is discarded
                     late = True
                     break
-            if k + 1 < maxit:
+            if k + 1 < maxit and not fusedual:
                 P.dot_nat(xcur, vprev)
                 have_dot = True
             with torch.cuda.stream(side):
@@ -390,7 +427,7 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             continue
         if ahead and pos_kernel == positivity:
             ev.record()
-            if k + 1 < maxit:
+            if k + 1 < maxit and not fusedual:
                 P.dot_nat(xcur, vprev)       # next iteration: xprev = xcur, vcur = vprev (holds the dead 2v - vp)
                 have_dot = True
             with torch.cuda.stream(side):
