@@ -198,7 +198,7 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi, fused=False):
 
 
 def short_kernel_name(mangled):
-    for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_slab_to_nat", "k_nat_to_slab", "k_dual_partial", "k_dual_apply", "k_dual_rec", "k_dual",
+    for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_slab_to_nat", "k_nat_to_slab", "k_dual_partial", "k_dual_apply", "k_dual_rec", "k_dual_factor", "k_dual",
               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
               "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
               "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv", "k_pd_primal", "k_hess_red_final", "k_red_final",
@@ -592,8 +592,10 @@ def finish_ours(a, env):
     hbm, peak_src = peaks()
     fused_primal = "k_pd_primal" not in kern       # pfb_hess_apply_primal ran (primal step inside pass C)
     per_kernel, per_op, fused_iter = byte_model(nbl, nx, s, psi.Nxmax, nbasis, world > 1, fused_primal)
-    if "k_dual_rec" in kern:       # rec path: k_dual_partial is only the band-sum helper (no byte model)
-        per_kernel["k_dual_partial"] = None
+    if "k_dual_rec" in kern or "k_dual_factor" in kern:
+        per_kernel["k_dual_partial"] = None     # here only the band-sum helper (no byte model)
+    # opt-in fused dual (PFB_PD_FUSEDUAL): band-shaped factor kernel reads Vbar, ubar, w, writes f, Vbar
+    per_kernel["k_dual_factor"] = 5 * (psi.Nxmax * psi.Nxmax * nbasis * s) if "k_dual_factor" in kern else None
     # dominant kernel = largest total device time in the timed region
     tot_k = sum(t for _, t in kern.values())
     modelled = {k: v for k, v in kern.items() if per_kernel.get(k) is not None or k in
@@ -636,6 +638,7 @@ def finish_ours(a, env):
                                "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
                                "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv"],
               "dual_update": (["k_dual", "k_dual_rec"] if "k_dual_rec" in kern
+                              else ["k_dual_factor", "k_dual_partial"] if "k_dual_factor" in kern
                               else ["k_dual", "k_dual_partial", "k_dual_apply"]),
               "primal_update+eps": ["k_pd_primal"]}
     if fused_primal:

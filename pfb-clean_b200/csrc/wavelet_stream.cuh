@@ -59,9 +59,12 @@ template <class T> struct DualFz {
     bool on;
     long dv, df;
     T sigma;
-    __device__ __forceinline__ void put(T *dst, const T u) const {
-        if (on) *dst = (dst[dv] + sigma * u) * dst[df];
-        else *dst = u;
+    // vp and f are read-only here and never alias the output: loads through the read-only path
+    __device__ __forceinline__ T ldvp(const T *dst) const { return __ldg(dst + dv); }
+    __device__ __forceinline__ T ldf(const T *dst) const { return __ldg(dst + df); }
+    // a, f: vp and f at dst, fetched one coefficient row ahead (see the kernels)
+    __device__ __forceinline__ void put(T *dst, const T u, const T a, const T f) const {
+        *dst = on ? (a + sigma * u) * f : u;
     }
 };
 __device__ __forceinline__ Vec2<float> ldv2(const float *p) {
@@ -149,6 +152,19 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
     const int jx_first = JX0 - (F - 2) / 2;
 #pragma unroll 1
     for (int j = jx_first; j < jx_first + kPD; ++j) prefetch(j);
+    // fused dual update: vp / f of the NEXT coefficient row are fetched into registers while the
+    // current row is computed, so their latency is never exposed
+    T za[4] = {(T)0, (T)0, (T)0, (T)0}, zf[4] = {(T)0, (T)0, (T)0, (T)0};
+    auto zfetch = [&](const int j) {
+        if (NAT && fz.on && tval && j >= JX0 && j < jx_end) {
+            const T *dst = slab + d.off1 + (long)j * d.ldn + ta;
+            if (last) { za[0] = fz.ldvp(dst - (long)d.qs); zf[0] = fz.ldf(dst - (long)d.qs); }
+            za[1] = fz.ldvp(dst); zf[1] = fz.ldf(dst);
+            za[2] = fz.ldvp(dst + d.qs); zf[2] = fz.ldf(dst + d.qs);
+            za[3] = fz.ldvp(dst + 2 * (long)d.qs); zf[3] = fz.ldf(dst + 2 * (long)d.qs);
+        }
+    };
+    zfetch(jx_first);
 
 #pragma unroll 1
     for (int jx = jx_first; jx < jx_end; ++jx) {
@@ -179,12 +195,13 @@ __device__ __forceinline__ void dwt_stream_task(const T *__restrict__ in, const 
         if (NAT) {
             if (jx >= JX0 && tval) {
                 T *dst = slab + d.off1 + (long)jx * d.ldn + ta;
-                if (last) fz.put(dst - (long)d.qs, o[0]);
+                if (last) fz.put(dst - (long)d.qs, o[0], za[0], zf[0]);
                 else ll_out[(long)jx * d.ld_out + ta] = o[0];
-                fz.put(dst, o[1]);
-                fz.put(dst + d.qs, o[2]);
-                fz.put(dst + 2 * (long)d.qs, o[3]);
+                fz.put(dst, o[1], za[1], zf[1]);
+                fz.put(dst + d.qs, o[2], za[2], zf[2]);
+                fz.put(dst + 2 * (long)d.qs, o[3], za[3], zf[3]);
             }
+            zfetch(jx + 1);
             continue;
         }
         // staging (warm-up rows hit cells that are overwritten before the flush)
@@ -383,6 +400,39 @@ k_dwt_stream_all(const T *__restrict__ img, T *scr_out, T *cn, LevelArgs a, DwtA
     const int jx_first = JX0 - 3;                    // db4 needs three coefficient rows of history
 #pragma unroll 1
     for (int j = jx_first; j < jx_first + kPD; ++j) prefetch(j);
+    // fused dual update: vp / f of the NEXT coefficient row in registers (see dwt_stream_task)
+    T za[4][4], zf[4][4];
+    Vec2<T> zsa[2], zsf[2];
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) za[s][i] = zf[s][i] = (T)0;
+    zsa[0].v[0] = zsa[0].v[1] = zsa[1].v[0] = zsa[1].v[1] = (T)0;
+    zsf[0] = zsa[0]; zsf[1] = zsa[0];
+    auto zfetch = [&](const int j) {
+        if (!fz.on || j < JX0 || j >= jx_end) return;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            const DwtAllSlot &d = g.s[s];
+            if (tv[s] && j < d.C0) {
+                const T *dst = pq[s] + (long)j * d.ldn;
+                if (a.last) { za[s][0] = fz.ldvp(dst - (long)d.qs); zf[s][0] = fz.ldf(dst - (long)d.qs); }
+                za[s][1] = fz.ldvp(dst); zf[s][1] = fz.ldf(dst);
+                za[s][2] = fz.ldvp(dst + d.qs); zf[s][2] = fz.ldf(dst + d.qs);
+                za[s][3] = fz.ldvp(dst + 2 * (long)d.qs); zf[s][3] = fz.ldf(dst + 2 * (long)d.qs);
+            }
+        }
+        if (sv) {
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr)
+                if (2 * j + rr < n0) {
+                    const T *dst = pself + (long)(2 * j + rr) * g.ld_self;
+                    zsa[rr] = ldv2(dst + fz.dv);
+                    zsf[rr] = ldv2(dst + fz.df);
+                }
+        }
+    };
+    zfetch(jx_first);
 
 #pragma unroll 1
     for (int jx = jx_first; jx < jx_end; ++jx) {
@@ -406,17 +456,20 @@ k_dwt_stream_all(const T *__restrict__ img, T *scr_out, T *cn, LevelArgs a, DwtA
         dwt_all_bank<T, 4>(w0, w1, h1, o[1]);
         dwt_all_bank<T, 6>(w0, w1, h2, o[2]);
         dwt_all_bank<T, 8>(w0, w1, h3, o[3]);
-        if (jx < JX0) continue;                      // warm-up rows of the history
+        if (jx < JX0) {                              // warm-up rows of the history
+            zfetch(jx + 1);
+            continue;
+        }
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
             const DwtAllSlot &d = g.s[s];
             if (tv[s] && jx < d.C0) {
                 T *dst = pq[s] + (long)jx * d.ldn;
-                if (a.last) fz.put(dst - (long)d.qs, o[s][0]);
+                if (a.last) fz.put(dst - (long)d.qs, o[s][0], za[s][0], zf[s][0]);
                 else pll[s][(long)jx * d.ld_out] = o[s][0];
-                fz.put(dst, o[s][1]);
-                fz.put(dst + d.qs, o[s][2]);
-                fz.put(dst + 2 * (long)d.qs, o[s][3]);
+                fz.put(dst, o[s][1], za[s][1], zf[s][1]);
+                fz.put(dst + d.qs, o[s][2], za[s][2], zf[s][2]);
+                fz.put(dst + 2 * (long)d.qs, o[s][3], za[s][3], zf[s][3]);
             }
         }
         if (sv) {
@@ -426,13 +479,13 @@ k_dwt_stream_all(const T *__restrict__ img, T *scr_out, T *cn, LevelArgs a, DwtA
                     T *dst = pself + (long)(2 * jx + rr) * g.ld_self;
                     Vec2<T> q = rr ? q1 : q0;
                     if (fz.on) {
-                        const Vec2<T> pv = ldv2(dst + fz.dv), ff = ldv2(dst + fz.df);
-                        q.v[0] = (pv.v[0] + fz.sigma * q.v[0]) * ff.v[0];
-                        q.v[1] = (pv.v[1] + fz.sigma * q.v[1]) * ff.v[1];
+                        q.v[0] = (zsa[rr].v[0] + fz.sigma * q.v[0]) * zsf[rr].v[0];
+                        q.v[1] = (zsa[rr].v[1] + fz.sigma * q.v[1]) * zsf[rr].v[1];
                     }
                     stv2(dst, q);
                 }
         }
+        zfetch(jx + 1);
     }
     cp_async_wait<0>();
 }

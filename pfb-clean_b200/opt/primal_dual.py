@@ -286,11 +286,15 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     # epilogue (pfb_psi_dot_nat_dual): the band-independent half (S, the shrink factor f, the new
     # carried sum) is one small kernel over a band-shaped block, and v_b = (vp_b + sigma Psi^T x_b) f
     # is stored straight from the analysis registers -- the analysed coefficients never exist in
-    # memory (5.4 GB less traffic per iteration at 8 x 4096^2).  Used on one GPU as well: over the
-    # reference's 450 iterations every fp32 path stays 1.1e-6 / 2.8e-6 from the fp64 trajectory,
-    # re-synchronised or not (profiles/r02/r02m_sharded_drift_450its.jsonl).
+    # memory (5.4 GB less traffic per iteration at 8 x 4096^2).  Opt-in (PFB_PD_FUSEDUAL=1): the
+    # analysis walks are instruction-issue bound, so the extra loads cost more there than the
+    # bytes save in the 0.93-of-peak dual kernel: 2.75 ms (fused walks 2.26 incl. the one-band
+    # analysis of the band sum, factor kernel 0.36, band sum 0.13) against 1.08 + 1.41 = 2.49 ms
+    # per iteration at 8 x 4096^2 fp32, 140.1 vs 145.6 it/s (profiles/r02/r02o_*).  Numerically it
+    # is the rec path: over the reference's 450 iterations every fp32 path stays 1.1e-6 / 2.8e-6
+    # from the fp64 trajectory (profiles/r02/r02m_sharded_drift_450its.jsonl).
     norec = parallel.active() and os.environ.get("PFB_PAR_NOREC")
-    fusedual = nat and lin and not norec and not os.environ.get("PFB_PD_NOFUSEDUAL")
+    fusedual = bool(nat and lin and not norec and os.environ.get("PFB_PD_FUSEDUAL"))
     rec = nat and lin and parallel.active() and not norec and not fusedual
     primal_dual_optimised.last_rec = bool(rec or (fusedual and parallel.active()))
     primal_dual_optimised.last_fusedual = bool(fusedual)

@@ -155,6 +155,25 @@ def test_solvers_api(backend, tag):
     assert primal_dual_optimised.last_path == "slab"
     assert rel(x, g["pdo_x_pos1"]) < tolx and rel(v, g["pdo_v_pos1"]) < tolx
 
+    # opt-in: dual update in the epilogue of the analysis kernels (pfb_psi_dot_nat_dual)
+    os.environ["PFB_PD_FUSEDUAL"] = "1"
+    try:
+        for pos in (1, 2):
+            x = np.zeros(dirty.shape, dt)
+            v = np.zeros((nband, nbasis, psi.Nymax, psi.Nxmax), dt)
+            primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, np.ones(v.shape[1:], dt),
+                                  None, Grad21(psf_convolve, data), nu=nbasis, tol=0.0, maxit=10,
+                                  positivity=pos, verbosity=0)
+            assert primal_dual_optimised.last_fusedual
+            assert rel(x, g[f"pdo_x_pos{pos}"]) < tolx and rel(v, g[f"pdo_v_pos{pos}"]) < tolx
+    finally:
+        del os.environ["PFB_PD_FUSEDUAL"]
+    x = np.zeros(dirty.shape, dt)
+    v = np.zeros((nband, nbasis, psi.Nymax, psi.Nxmax), dt)
+    primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, np.ones(v.shape[1:], dt), None,
+                          Grad21(psf_convolve, data), nu=nbasis, tol=0.0, maxit=2, verbosity=0)
+    assert not primal_dual_optimised.last_fusedual           # default: separate dual kernel
+
     # l1 reweighting branch
     outvar = np.zeros((nband, nbasis, psi.Nymax, psi.Nxmax), dt)
     rew = partial(l1reweight_func, psi.dot, outvar, 1.0, g["rms_comps"])

@@ -69,6 +69,18 @@ def _worker(rank, world, port, q):
             res[f"rec{pos}"] = primal_dual_optimised.last_rec     # image-sized exchange (pfb_dual_update_rec)
             res[f"pd_x{pos}"] = rel(x, g[f"pdo_x_pos{pos}"][sl])
             res[f"pd_v{pos}"] = rel(v, g[f"pdo_v_pos{pos}"][sl])
+        # opt-in variant: dual update in the analysis epilogue, band sum carried the same way
+        os.environ["PFB_PD_FUSEDUAL"] = "1"
+        os.environ["PFB_PAR_RESYNC"] = "4"
+        x = np.zeros_like(dirty)
+        v = np.zeros((nbl, len(bases), psi.Nymax, psi.Nxmax))
+        primal_dual_optimised(x, v, float(g["lam"]), psi.hdot, psi.dot, float(g["hessnorm"]), None,
+                              np.ones(v.shape[1:]), None, Grad21(conv, dirty), nu=len(bases), tol=0.0,
+                              maxit=10, positivity=1, verbosity=0)
+        del os.environ["PFB_PD_FUSEDUAL"]
+        res["fz"] = primal_dual_optimised.last_fusedual
+        res["fz_x"] = rel(x, g["pdo_x_pos1"][sl])
+        res["fz_v"] = rel(v, g["pdo_v_pos1"][sl])
         # l1 reweighting on sharded ranks: the weights come from the band sum over ALL ranks'
         # bands (pfb/utils/misc.py:1070-1080), so every rank must derive the same weights
         from pfb_b200.utils.misc import l1reweight_func
@@ -134,5 +146,6 @@ def test_band_sharded_two_ranks():
             assert out[r][f"pd_x{pos}"] < 1e-11, out[r]
             assert out[r][f"pd_v{pos}"] < 1e-11, out[r]
         assert out[r]["pcg_x"] < 1e-10, out[r]
+        assert out[r]["fz"] and out[r]["fz_x"] < 1e-11 and out[r]["fz_v"] < 1e-11, out[r]
         assert out[r]["rw_x"] < 1e-11 and out[r]["rw_v"] < 1e-11 and out[r]["rw_w"] < 1e-11, out[r]
         assert out[r]["rec32"] and out[r]["pd32_x"] < 1e-5 and out[r]["pd32_v"] < 1e-5, out[r]
