@@ -180,6 +180,7 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi, fused=False):
     for k in ("rows_fwd", "cols", "rows_inv"):  # fast-path / mixed-radix kernels move the same bytes
         per_kernel["k_hessf_" + k] = per_kernel["k_hess_" + k]
         per_kernel["k_hessm_" + k] = per_kernel["k_hess_" + k]
+        per_kernel["k_hessp_" + k] = per_kernel["k_hess_" + k]
     per_op = {                                  # SURVEY 8(d) table, x nb_local
         "psi_dot": nb_local * (P1 + C1),
         "psi_hdot": nb_local * (C1 + P1),       # hdot(u), u = 2v - vp written by the dual update
@@ -190,7 +191,7 @@ def byte_model(nb_local, nx, s, Nmax, nbasis, multi, fused=False):
     if fused:
         # pfb_hess_apply_primal: pass C reads S, xp, w_k, w_{k-1}, data and writes x (no conv array,
         # no separate primal kernel)
-        for k in ("k_hess_rows_inv", "k_hessf_rows_inv", "k_hessm_rows_inv"):
+        for k in ("k_hess_rows_inv", "k_hessf_rows_inv", "k_hessm_rows_inv", "k_hessp_rows_inv"):
             per_kernel[k] = nb_local * (S + 5 * P1)
         per_op["psf_convolve+primal_update"] = nb_local * (6 * P1 + psfhat)
     fused_iter = nb_local * (3 * P1 + psfhat + 2 * C1) + C1     # SURVEY 8(d) headline lower bound
@@ -201,7 +202,8 @@ def short_kernel_name(mangled):
     for k in ("k_dwt_level", "k_dwt_stream", "k_self_dot", "k_idwt_level", "k_idwt_stream", "k_slab_to_nat", "k_nat_to_slab", "k_dual_partial", "k_dual_apply", "k_dual_rec", "k_dual_factor", "k_dual",
               "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
               "k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
-              "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv", "k_pd_primal", "k_hess_red_final", "k_red_final",
+              "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv",
+              "k_hessp_rows_fwd", "k_hessp_cols", "k_hessp_rows_inv", "k_pd_primal", "k_hess_red_final", "k_red_final",
               "k_norm_diff", "k_axpby", "k_dot", "k_prox21", "k_psfhat_prepare"):
         if k in mangled:
             return k
@@ -636,7 +638,8 @@ def finish_ours(a, env):
     groups = {"psi_dot": ["k_dwt_level", "k_dwt_stream", "k_self_dot"], "psi_hdot": ["k_idwt_level", "k_idwt_stream", "k_slab_to_nat"],
               "psf_convolve": ["k_hess_rows_fwd", "k_hess_cols", "k_hess_rows_inv",
                                "k_hessf_rows_fwd", "k_hessf_cols", "k_hessf_rows_inv",
-                               "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv"],
+                               "k_hessm_rows_fwd", "k_hessm_cols", "k_hessm_rows_inv",
+                               "k_hessp_rows_fwd", "k_hessp_cols", "k_hessp_rows_inv"],
               "dual_update": (["k_dual", "k_dual_rec"] if "k_dual_rec" in kern
                               else ["k_dual_factor", "k_dual_partial"] if "k_dual_factor" in kern
                               else ["k_dual", "k_dual_partial", "k_dual_apply"]),

@@ -275,6 +275,12 @@ int pfb_hess_apply(pfb_hess_plan *plan, const void *x, const void *beam, int add
 int pfb_psfhat_from_psf(const void *psf, int nband, int nxp, int nyp, int dtype, void *psfhat,
                         void *stream);
 
+/* Which kernel family the plan selected (no reference counterpart; for tests and logs):
+ * bit 0 power-of-two fast path, bit 1 mixed-radix plan (pfb/workers/grid.py:276-284 good_size
+ * paddings), bit 2 / bit 3 its row / column passes run as (3|5|7) x 2^k peeled transforms,
+ * bit 4 / bit 5 the 16384-point column / row kernels. */
+int pfb_hess_plan_kernels(const pfb_hess_plan *plan);
+
 /* PSF convolution with the primal step of primal_dual_optimised
  * (pfb/opt/primal_dual.py:138-150) fused into its last pass:
  *   x = P+( xp - tau * (2 w - wprev + psf_convolve(xp) - data) ),  out2 as pfb_norm_diff

@@ -49,6 +49,7 @@ _SIGS = {
     "pfb_psi_plan_destroy": (c_int, [_P]),
     "pfb_filter_bank": (c_int, [c_int, POINTER(ctypes.c_double)]),
     "pfb_hess_plan_can_fuse_primal": (c_int, [_P]),
+    "pfb_hess_plan_kernels": (c_int, [_P]),
     "pfb_hess_apply_primal": (c_int, [_P, _P, _P, _P, _P, c_double, c_int, _P, _P, _P]),
     "pfb_psi_plan_query": (c_int, [_P, POINTER(c_int), POINTER(c_int)]),
     "pfb_psi_plan_tables": (c_int, [_P, c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),

@@ -21,6 +21,7 @@
 // of the reference's ~5 passes over the 4x larger padded arrays.
 #include "hess_fast.cuh"
 #include "hess_mixed.cuh"
+#include "hess_peel.cuh"
 #include <cmath>
 #include <vector>
 
@@ -268,6 +269,11 @@ struct pfb_hess_plan {
     pfb::MxDesc mrow, mcol;
     void *mtwM, *mtwC, *mroots;   // length-M / length-(H or nxp) twiddle tables, odd-radix roots
     int deint;               // psfT rows stored [even | odd] per column
+    // odd factor x power of two (hess_peel.cuh): passes whose length is m * P2 leave the
+    // run-time radix list for m compile-time transforms of length P2
+    pfb::PeelDesc prow, pcol;
+    int LrowP;               // rows per CTA of the peeled row passes
+    void *ptabR, *ptabC;     // ct_fft stage tables of prow.P2 / pcol.P2
 #ifndef PFB_EMU
     CUtensorMap tmS;         // S as (band, k, row) tensor of 8-byte elements, box 2 rows x 256 k (fp32 fast path)
 #endif
@@ -579,6 +585,74 @@ template <class T> static int fast_cols_d(pfb_hess_plan *p, cudaStream_t st) {
 #undef PFB_C
 }
 
+// ---- odd factor x power of two (hess_peel.cuh)
+#define PFB_PEEL_SWITCH(n, CALL)                         \
+    switch (n) {                                         \
+    case 512: return CALL(512);                          \
+    case 1024: return CALL(1024);                        \
+    case 2048: return CALL(2048);                        \
+    case 4096: return CALL(4096);                        \
+    default: return fail(PFB_ERR_FFT_SIZE, "peeled transform: unsupported power of two %d", (int)(n)); \
+    }
+template <class T, int P2>
+static int peel_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
+    HessDims h = p->h;
+    h.R = p->LrowP;
+    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R);
+    PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_fwd<T, P2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    launch(&k_hessp_rows_fwd<T, P2>, dim3(cdiv(h.nx, h.R), h.nband), dim3(peel_threads(p->prow.m, P2, h.R)), smem, st,
+           x, beam, (Cx<T> *)p->S, (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots,
+           (const Cx<T> *)p->ptabR, p->prow.m, h);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+template <class T, int P2>
+static int peel_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
+    HessDims h = p->h;
+    h.R = p->LrowP;
+    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R);
+    PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_inv<T, P2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    launch(&k_hessp_rows_inv<T, P2>, dim3(cdiv(h.nx, h.R), h.nband), dim3(peel_threads(p->prow.m, P2, h.R)), smem, st,
+           (const Cx<T> *)p->S, out, (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots,
+           (const Cx<T> *)p->ptabR, p->prow.m, h, ep);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+template <class T, int P2>
+static int peel_cols(pfb_hess_plan *p, cudaStream_t st) {
+    const HessDims &h = p->h;
+    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(p->pcol.N, p->pcol.m, P2, 1);
+    const dim3 grid(h.nyo2, h.nband), blk(peel_threads(p->pcol.m, P2, 1));
+    if (p->split) {
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_cols<T, P2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        launch(&k_hessp_cols<T, P2, true>, grid, blk, smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
+               (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, (const Cx<T> *)p->ptabC,
+               p->pcol.m, h);
+    } else {
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_cols<T, P2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        launch(&k_hessp_cols<T, P2, false>, grid, blk, smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
+               (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, (const Cx<T> *)p->ptabC,
+               p->pcol.m, h);
+    }
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+template <class T> static int peel_rows_fwd_d(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
+#define PFB_C(N) peel_rows_fwd<T, N>(p, x, beam, st)
+    PFB_PEEL_SWITCH(p->prow.P2, PFB_C)
+#undef PFB_C
+}
+template <class T> static int peel_rows_inv_d(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
+#define PFB_C(N) peel_rows_inv<T, N>(p, out, ep, st)
+    PFB_PEEL_SWITCH(p->prow.P2, PFB_C)
+#undef PFB_C
+}
+template <class T> static int peel_cols_d(pfb_hess_plan *p, cudaStream_t st) {
+#define PFB_C(N) peel_cols<T, N>(p, st)
+    PFB_PEEL_SWITCH(p->pcol.P2, PFB_C)
+#undef PFB_C
+}
+
 template <class T>
 static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T *beam_out,
                         const T *addx, double sigmainv, int has_wsum, double wsum, T *out,
@@ -604,11 +678,17 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
         auto nthr = [](long work) { return work >= 2048 ? 512 : work >= 512 ? 256 : 128; };
         const int tr = nthr((long)h.M * h.R / 4), tc = nthr(p->mcol.N / 4);
         const dim3 grow(cdiv(h.nx, h.R), h.nband), gcol(h.nyo2, h.nband);
-        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_fwd<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
-        launch(&k_hessm_rows_fwd<T>, grow, dim3(tr), smr, st, x, beam_in, S, (const Cx<T> *)p->mtwM,
-               (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h);
+        if (p->prow.m) {
+            if (int rc = peel_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
+        } else {
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_fwd<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
+            launch(&k_hessm_rows_fwd<T>, grow, dim3(tr), smr, st, x, beam_in, S, (const Cx<T> *)p->mtwM,
+                   (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h);
+        }
         PFB_CHECK_LAUNCH();
-        if (p->split) {
+        if (p->pcol.m) {
+            if (int rc = peel_cols_d<T>(p, st)) return rc;
+        } else if (p->split) {
             PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_cols<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));
             launch(&k_hessm_cols<T, true>, gcol, dim3(tc), smc, st, S, (const Cx<T> *)p->psfT,
                    (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, p->mcol, h);
@@ -618,9 +698,13 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
                    (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, p->mcol, h);
         }
         PFB_CHECK_LAUNCH();
-        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_inv<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
-        launch(&k_hessm_rows_inv<T>, grow, dim3(tr), smr, st, (const Cx<T> *)S, out, (const Cx<T> *)p->mtwM,
-               (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h, ep);
+        if (p->prow.m) {
+            if (int rc = peel_rows_inv_d<T>(p, out, ep, st)) return rc;
+        } else {
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_inv<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
+            launch(&k_hessm_rows_inv<T>, grow, dim3(tr), smr, st, (const Cx<T> *)S, out, (const Cx<T> *)p->mtwM,
+                   (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h, ep);
+        }
         PFB_CHECK_LAUNCH();
         return PFB_OK;
     }
@@ -738,6 +822,29 @@ static int hess_plan_create_mixed(pfb_hess_plan **out, int nband, int nx, int ny
                 upload(&p->twr, M + 1, lin(nyp)) && upload(&p->modg, std::max(H, 1), lin(nxp)) &&
                 upload(&p->mroots, kMxRoots, root) &&
                 cudaMalloc(&p->S, sS) == cudaSuccess;
+    // passes whose length is (3, 5 or 7) x a power of two take the peeled kernels
+    if (good && !getenv("PFB_HESS_NOPEEL")) {
+        auto table = [&](void **dst, int P2) -> bool {
+            std::vector<char> hbuf(cs * (size_t)ct_tab_size(P2));
+            ct_fill_table(P2, [&](int i, double c, double sn) {
+                if (dtype == PFB_F32) { ((float *)hbuf.data())[2 * i] = (float)c; ((float *)hbuf.data())[2 * i + 1] = (float)sn; }
+                else { ((double *)hbuf.data())[2 * i] = c; ((double *)hbuf.data())[2 * i + 1] = sn; }
+            });
+            return cudaMalloc(dst, hbuf.size()) == cudaSuccess &&
+                   cudaMemcpy(*dst, hbuf.data(), hbuf.size(), cudaMemcpyHostToDevice) == cudaSuccess;
+        };
+        PeelDesc pr, pc;
+        if (peel_make_desc(M, pr) && cs * peel_smem_elems(M, pr.m, pr.P2, 1) <= kMaxSmemFast) {
+            p->LrowP = dtype == PFB_F32 ? 4 : 2;
+            while (p->LrowP > 1 && cs * peel_smem_elems(M, pr.m, pr.P2, p->LrowP) > kMaxSmemFast) p->LrowP >>= 1;
+            p->prow = pr;
+            good = good && table(&p->ptabR, pr.P2);
+        }
+        if (peel_make_desc(Nc, pc) && cs * peel_smem_elems(Nc, pc.m, pc.P2, 1) <= kMaxSmemFast) {
+            p->pcol = pc;
+            good = good && table(&p->ptabC, pc.P2);
+        }
+    }
     if (!good) {
         pfb_hess_plan_destroy(p);
         return fail(PFB_ERR_ALLOC, "hessian plan (mixed radix) allocation failed (%zu + %zu bytes)", sS, sP);
@@ -952,6 +1059,8 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
 
 int pfb_hess_plan_destroy(pfb_hess_plan *p) {
     if (!p) return PFB_OK;
+    if (p->ptabR) cudaFree(p->ptabR);
+    if (p->ptabC) cudaFree(p->ptabC);
     if (p->tabM) cudaFree(p->tabM);
     if (p->tabH) cudaFree(p->tabH);
     if (p->twr) cudaFree(p->twr);
@@ -1011,6 +1120,12 @@ int pfb_psfhat_from_psf(const void *psf, int nband, int nxp, int nyp, int dtype,
         rc = fail(PFB_ERR_CUDA, "pfb_psfhat_from_psf: stream synchronise failed");
     pfb_hess_plan_destroy(p);
     return rc;
+}
+
+int pfb_hess_plan_kernels(const pfb_hess_plan *p) {
+    if (!p) return 0;
+    return (p->fast ? 1 : 0) | (p->mixed ? 2 : 0) | (p->prow.m ? 4 : 0) | (p->pcol.m ? 8 : 0) |
+           (p->fastcols ? 16 : 0) | (p->fastrows ? 32 : 0);
 }
 
 int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *p) {

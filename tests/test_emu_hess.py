@@ -98,7 +98,11 @@ def test_hess_delta_kat():
 MIXED = [(8, 8, 24, 32), (8, 8, 16, 16), (5, 6, 10, 12), (12, 14, 24, 28), (9, 20, 30, 42),
          (20, 18, 44, 36), (13, 10, 26, 52), (30, 50, 60, 100), (40, 24, 48, 50),   # nx > nxp/2: full
          (7, 9, 15, 18), (6, 4, 21, 10),                                           # odd nxp: full
-         (48, 70, 96, 140), (75, 66, 150, 132), (10, 600, 20, 1200), (350, 8, 700, 16)]
+         (48, 70, 96, 140), (75, 66, 150, 132), (10, 600, 20, 1200), (350, 8, 700, 16),
+         # (3, 5, 7) x power of two: hess_peel.cuh -- rows (M = 1536, 2560), split columns
+         # (H = 1536, 3584), full columns (nxp = 3072), both at once
+         (6, 1500, 12, 3072), (4, 2500, 8, 5120), (1500, 6, 3072, 12), (3000, 4, 7168, 8),
+         (2000, 6, 3072, 12), (1400, 1300, 3072, 3072)]
 
 
 @pmp("dtype", [np.float32, np.float64])
@@ -113,6 +117,13 @@ def test_hess_mixed_radix_oracle(dtype, nx, ny, nxp, nyp):
     beam = (0.5 + rng.random(x.shape)).astype(dtype)
     H = EmuHess(nband, nx, ny, nxp, nyp, dtype)
     assert H.rc == 0
+    # which passes run as (3|5|7) x 2^k peeled transforms (hess_peel.cuh)
+    def peels(n):
+        return any(n % m == 0 and n // m in (512, 1024, 2048, 4096) for m in (3, 5, 7))
+    kern = H.L.pfb_hess_plan_kernels(H.plan)
+    assert kern & 2
+    assert bool(kern & 4) == peels(nyp // 2)
+    assert bool(kern & 8) == peels(nxp // 2 if (nxp % 2 == 0 and nx <= nxp // 2) else nxp)
     H.set_psfhat(psfhat)
     xpad, xhat = np.empty((nband, nxp, nyp), dtype), np.empty(psfhat.shape, cdt)
     xout = np.empty(x.shape, dtype)

@@ -171,7 +171,11 @@ def test_hess_vs_oracle(dtype, nx, ny, nxp, nyp):
 @pmp("nx,ny,nxp,nyp", [(8, 8, 24, 32), (9, 20, 30, 42), (20, 18, 44, 36), (13, 10, 26, 52),
                         (40, 24, 48, 50), (7, 9, 15, 18), (75, 66, 150, 132), (10, 600, 20, 1200),
                         (350, 8, 700, 16), (600, 540, 1200, 1080), (1500, 1350, 3000, 2700),
-                        (900, 1000, 1344, 2200)])
+                        (900, 1000, 1344, 2200),
+                        # (3|5|7) x 2^k: hess_peel.cuh (rows, split / full columns, all P2)
+                        (6, 1500, 12, 3072), (1500, 6, 3072, 12), (2000, 6, 3072, 12),
+                        (1400, 1300, 3072, 3072), (2500, 2400, 5120, 5120), (3000, 3500, 7168, 7168),
+                        (3000, 2900, 6144, 6144), (5000, 4800, 10240, 10240), (3584, 3000, 7168, 6144)])
 def test_hess_mixed_radix_vs_oracle(dtype, nx, ny, nxp, nyp):
     """Padded sizes that are not powers of two (ducc0 good_size lengths,
     pfb/workers/grid.py:276-284): hess_mixed.cuh, split and full column pass."""
