@@ -100,10 +100,81 @@ __device__ __forceinline__ void peel_butterflies(Cx<T> *R2, int L, int m, int P2
     }
 }
 
-// forward: R1 (natural, L lines of N) -> R2 (segment layout).  Synchronised on exit.
 template <class T, int P2>
-__device__ __forceinline__ void peel_fwd(const Cx<T> *R1, Cx<T> *R2, int L, int m,
-                                         const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt) {
+__device__ __forceinline__ void peel_load_tables(Cx<T> *rt, const Cx<T> *__restrict__ roots,
+                                                 const Cx<T> *__restrict__ tw, const Cx<T> *__restrict__ tabg,
+                                                 int N) {
+    mx_load_tables(rt, roots, tw, N);
+    Cx<T> *tab = rt + kMxHead;
+    for (int i = threadIdx.x; i < ct_tab_size(P2); i += blockDim.x) tab[i] = tabg[i];
+}
+
+// Element loops of the passes: thread t takes elements t, t + nthreads, ...; U of them are
+// fetched (ld) before the first is used (st), so U global / L2 latencies overlap instead of
+// queueing one behind the other (ncu r02q: 38-48 % of the stall samples of the first version
+// were long-scoreboard waits on single loads).
+template <int U, class LD, class ST>
+__device__ __forceinline__ void peel_batched(int n, LD ld, ST st) {
+    for (int base = threadIdx.x; base < n; base += U * (int)blockDim.x) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * (int)blockDim.x;
+            if (i < n) ld(u, i);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * (int)blockDim.x;
+            if (i < n) st(u, i);
+        }
+    }
+}
+
+// Column pass, spectrum side: forward butterflies, multiplication with the PSF spectrum and
+// inverse butterflies (+ conjugate twiddles) in one walk over the segments -- the spectrum
+// never goes back to shared memory in between.  pl: this column's (half of the) PSF spectrum.
+template <class T, int R>
+__device__ __forceinline__ void peel_mid_r(Cx<T> *R2, int P2, int cts, const Cx<T> *__restrict__ pl,
+                                           const Cx<T> *tws, const Cx<T> *rt) {
+    constexpr bool AHEAD = sizeof(T) == 4;           // fp64: no registers left for the look-ahead
+    Cx<T> pn[R];
+    int k = threadIdx.x;
+    if (AHEAD && k < P2) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) pn[r] = pl[k + r * P2];
+    }
+    for (; k < P2; k += blockDim.x) {
+        Cx<T> pc[R];
+        if (AHEAD) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) pc[r] = pn[r];
+            const int kn = k + blockDim.x;
+            if (kn < P2) {                           // next butterfly's PSF values, one trip ahead
+#pragma unroll
+                for (int r = 0; r < R; ++r) pn[r] = pl[kn + r * P2];
+            }
+        } else {
+#pragma unroll
+            for (int r = 0; r < R; ++r) pc[r] = pl[k + r * P2];
+        }
+        Cx<T> *base = R2 + k;
+        Cx<T> u[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) u[r] = base[r * cts];
+        MxDft<T, R, -1>::run(u, rt);
+#pragma unroll
+        for (int r = 0; r < R; ++r) u[r] = cmul(u[r], pc[r]);
+        MxDft<T, R, +1>::run(u, rt);
+#pragma unroll
+        for (int r = 1; r < R; ++r) u[r] = cmul(u[r], cconj(mx_twiddle(tws, r * k)));
+#pragma unroll
+        for (int r = 0; r < R; ++r) base[r * cts] = u[r];
+    }
+}
+
+// forward sub-transforms only (R1 -> twiddled segments of R2), synchronised on exit
+template <class T, int P2>
+__device__ __forceinline__ void peel_fwd_subs(const Cx<T> *R1, Cx<T> *R2, int L, int m,
+                                              const Cx<T> *tws, const Cx<T> *tab) {
     constexpr int NT = P2 / 16, cts = ct_stride(P2);
     const int N = m * P2, G = blockDim.x / NT;
     const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
@@ -132,20 +203,15 @@ __device__ __forceinline__ void peel_fwd(const Cx<T> *R1, Cx<T> *R2, int L, int 
         }
     }
     __syncthreads();
-    peel_butterflies<T, -1>(R2, L, m, P2, cts, tws, rt);
-    __syncthreads();
 }
 
-// inverse: R2 (segment layout) -> R1 (natural), unnormalised.  Synchronised on exit.
+// inverse sub-transforms only (segments of R2, already butterflied and twiddled -> R1)
 template <class T, int P2>
-__device__ __forceinline__ void peel_inv(Cx<T> *R2, Cx<T> *R1, int L, int m,
-                                         const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt) {
+__device__ __forceinline__ void peel_inv_subs(Cx<T> *R2, Cx<T> *R1, int L, int m, const Cx<T> *tab) {
     constexpr int NT = P2 / 16, cts = ct_stride(P2);
     const int N = m * P2, G = blockDim.x / NT;
     const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
     const GroupBar bar{1 + g, NT};
-    peel_butterflies<T, +1>(R2, L, m, P2, cts, tws, rt);
-    __syncthreads();
     const int nsub = m * L;
     for (int s0 = 0; s0 < nsub; s0 += G) {
         const int sub = s0 + g;
@@ -171,13 +237,35 @@ __device__ __forceinline__ void peel_inv(Cx<T> *R2, Cx<T> *R1, int L, int m,
     __syncthreads();
 }
 
+// forward: R1 (natural, L lines of N) -> R2 (segment layout).  Synchronised on exit.
 template <class T, int P2>
-__device__ __forceinline__ void peel_load_tables(Cx<T> *rt, const Cx<T> *__restrict__ roots,
-                                                 const Cx<T> *__restrict__ tw, const Cx<T> *__restrict__ tabg,
-                                                 int N) {
-    mx_load_tables(rt, roots, tw, N);
-    Cx<T> *tab = rt + kMxHead;
-    for (int i = threadIdx.x; i < ct_tab_size(P2); i += blockDim.x) tab[i] = tabg[i];
+__device__ __forceinline__ void peel_fwd(const Cx<T> *R1, Cx<T> *R2, int L, int m,
+                                         const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt) {
+    peel_fwd_subs<T, P2>(R1, R2, L, m, tws, tab);
+    peel_butterflies<T, -1>(R2, L, m, P2, ct_stride(P2), tws, rt);
+    __syncthreads();
+}
+
+// inverse: R2 (segment layout) -> R1 (natural), unnormalised.  Synchronised on exit.
+template <class T, int P2>
+__device__ __forceinline__ void peel_inv(Cx<T> *R2, Cx<T> *R1, int L, int m,
+                                         const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt) {
+    peel_butterflies<T, +1>(R2, L, m, P2, ct_stride(P2), tws, rt);
+    __syncthreads();
+    peel_inv_subs<T, P2>(R2, R1, L, m, tab);
+}
+
+// forward pair - PSF - inverse pair of one column (half): R1 -> R1
+template <class T, int P2>
+__device__ __forceinline__ void peel_conv(Cx<T> *R1, Cx<T> *R2, int m, const Cx<T> *__restrict__ pl,
+                                          const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt) {
+    constexpr int cts = ct_stride(P2);
+    peel_fwd_subs<T, P2>(R1, R2, 1, m, tws, tab);
+    if (m == 3) peel_mid_r<T, 3>(R2, P2, cts, pl, tws, rt);
+    else if (m == 5) peel_mid_r<T, 5>(R2, P2, cts, pl, tws, rt);
+    else peel_mid_r<T, 7>(R2, P2, cts, pl, tws, rt);
+    __syncthreads();
+    peel_inv_subs<T, P2>(R2, R1, 1, m, tab);
 }
 
 // ------------------------------------------------------------------ pass A
@@ -190,35 +278,44 @@ k_hessp_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
                  const Cx<T> *__restrict__ roots, const Cx<T> *__restrict__ tabg, int m, HessDims h) {
     PFB_DYN_SMEM(raw);
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
-    const int M = h.M, L = h.R;
+    const int M = h.M, L = h.R;                  // L = 1, 2 or 4
+    const int ls = L == 4 ? 2 : L == 2 ? 1 : 0;
     constexpr int cts = ct_stride(P2);
     Cx<T> *tab = rt + kMxHead;
     Cx<T> *R1 = tab + ct_tab_size(P2), *R2 = R1 + (long)L * M;
     const int band = blockIdx.y, row0 = blockIdx.x * L;
     peel_load_tables<T, P2>(rt, roots, tw, tabg, M);
-    for (int i = threadIdx.x; i < L * M; i += blockDim.x) {
-        const int l = i / M, mm = i - l * M, row = row0 + l, c0 = 2 * mm;
-        T a = (T)0, b = (T)0;
-        if (row < h.nx) {
-            const long ro = ((long)band * h.nx + row) * h.ny;
-            if (c0 < h.ny) { a = x[ro + c0]; if (beam) a *= beam[ro + c0]; }
-            if (c0 + 1 < h.ny) { b = x[ro + c0 + 1]; if (beam) b *= beam[ro + c0 + 1]; }
-        }
-        R1[i] = cx<T>(a, b);
+    for (int l = 0; l < L; ++l) {
+        const int row = row0 + l;
+        const long ro = ((long)band * h.nx + row) * h.ny;
+        T a[8], b[8];
+        peel_batched<8>(M,
+            [&](int u, int mm) {
+                const int c0 = 2 * mm;
+                a[u] = b[u] = (T)0;
+                if (row < h.nx) {
+                    if (c0 < h.ny) { a[u] = x[ro + c0]; if (beam) a[u] *= beam[ro + c0]; }
+                    if (c0 + 1 < h.ny) { b[u] = x[ro + c0 + 1]; if (beam) b[u] *= beam[ro + c0 + 1]; }
+                }
+            },
+            [&](int u, int mm) { R1[(long)l * M + mm] = cx<T>(a[u], b[u]); });
     }
     __syncthreads();
     peel_fwd<T, P2>(R1, R2, L, m, rt + 40, tab, rt);
     // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
-    for (int i = threadIdx.x; i < (M + 1) * L; i += blockDim.x) {
-        const int k = i / L, l = i - k * L;
-        const Cx<T> *z = R2 + (long)l * m * cts;
-        const Cx<T> zk = z[peel_xidx<P2>(k == M ? 0 : k)], zm = cconj(z[peel_xidx<P2>(k == 0 ? 0 : M - k)]);
-        const Cx<T> E = cx<T>((T)0.5 * (zk.x + zm.x), (T)0.5 * (zk.y + zm.y));
-        const Cx<T> D = cx<T>((T)0.5 * (zk.x - zm.x), (T)0.5 * (zk.y - zm.y));
-        const Cx<T> O = cx<T>(D.y, -D.x);
-        const Cx<T> X = E + cmul(twr[k], O);
-        if (row0 + l < h.nx) S[((long)band * h.nyo2 + k) * h.nx + row0 + l] = X;
-    }
+    Cx<T> w[4];
+    peel_batched<4>((M + 1) * L,
+        [&](int u, int i) { w[u] = twr[i >> ls]; },
+        [&](int u, int i) {
+            const int k = i >> ls, l = i & (L - 1);
+            const Cx<T> *z = R2 + (long)l * m * cts;
+            const Cx<T> zk = z[peel_xidx<P2>(k == M ? 0 : k)], zm = cconj(z[peel_xidx<P2>(k == 0 ? 0 : M - k)]);
+            const Cx<T> E = cx<T>((T)0.5 * (zk.x + zm.x), (T)0.5 * (zk.y + zm.y));
+            const Cx<T> D = cx<T>((T)0.5 * (zk.x - zm.x), (T)0.5 * (zk.y - zm.y));
+            const Cx<T> O = cx<T>(D.y, -D.x);
+            const Cx<T> X = E + cmul(w[u], O);
+            if (row0 + l < h.nx) S[((long)band * h.nyo2 + k) * h.nx + row0 + l] = X;
+        });
 }
 
 // ------------------------------------------------------------------ pass B
@@ -240,38 +337,36 @@ k_hessp_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
     const Cx<T> *pl = psfT + ((long)band * h.nyo2 + col) * h.nxp;
     peel_load_tables<T, P2>(rt, roots, tw, tabg, N);
     const Cx<T> *tws = rt + 40;
-    for (int n = threadIdx.x; n < N; n += blockDim.x) R1[n] = n < h.nx ? line[n] : cx<T>((T)0, (T)0);
+    constexpr int U1 = sizeof(T) == 4 ? 8 : 4, U2 = U1 / 2;   // batch depths by register budget
+    Cx<T> v[U1], g[U2];
+    peel_batched<U1>(N,
+        [&](int u, int n) { v[u] = n < h.nx ? line[n] : cx<T>((T)0, (T)0); },
+        [&](int u, int n) { R1[n] = v[u]; });
     __syncthreads();
-    peel_fwd<T, P2>(R1, R2, 1, m, tws, tab, rt);
-    for (int n = threadIdx.x; n < N; n += blockDim.x) {
-        Cx<T> *c = R2 + peel_xidx<P2>(n);
-        *c = cmul(*c, pl[n]);
-    }
-    __syncthreads();
-    peel_inv<T, P2>(R2, R1, 1, m, tws, tab, rt);
+    peel_conv<T, P2>(R1, R2, m, pl, tws, tab, rt);
     if (!SPLIT) {
         for (int n = threadIdx.x; n < h.nx; n += blockDim.x) line[n] = R1[n];
     } else {
-    // odd spectrum: input a[n] w^n; element n of the line and of R1 is swapped by one thread
-    for (int n = threadIdx.x; n < N; n += blockDim.x) {
-        Cx<T> in = cx<T>((T)0, (T)0);
-        if (n < h.nx) {
-            in = cmul(line[n], modg[n]);
-            line[n] = R1[n];
-        }
-        R1[n] = in;
-    }
-    __syncthreads();
-    peel_fwd<T, P2>(R1, R2, 1, m, tws, tab, rt);
-    for (int n = threadIdx.x; n < N; n += blockDim.x) {
-        Cx<T> *c = R2 + peel_xidx<P2>(n);
-        *c = cmul(*c, pl[N + n]);
-    }
-    __syncthreads();
-    peel_inv<T, P2>(R2, R1, 1, m, tws, tab, rt);
-    // the same thread wrote line[n] above (same index mapping): no fence needed
-    for (int n = threadIdx.x; n < h.nx; n += blockDim.x)
-        line[n] = line[n] + cmul(R1[n], cconj(modg[n]));
+        // odd spectrum: input a[n] w^n; element n of the line and of R1 is swapped by one thread
+        peel_batched<U2>(N,
+            [&](int u, int n) {
+                v[u] = cx<T>((T)0, (T)0);
+                if (n < h.nx) { v[u] = line[n]; g[u] = modg[n]; }
+            },
+            [&](int u, int n) {
+                Cx<T> in = cx<T>((T)0, (T)0);
+                if (n < h.nx) {
+                    in = cmul(v[u], g[u]);
+                    line[n] = R1[n];
+                }
+                R1[n] = in;
+            });
+        __syncthreads();
+        peel_conv<T, P2>(R1, R2, m, pl + N, tws, tab, rt);
+        // the same thread wrote line[n] above (same index mapping): no fence needed
+        peel_batched<U2>(h.nx,
+            [&](int u, int n) { v[u] = line[n]; g[u] = modg[n]; },
+            [&](int u, int n) { line[n] = v[u] + cmul(R1[n], cconj(g[u])); });
     }
 }
 
@@ -283,42 +378,54 @@ k_hessp_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *
                  const Cx<T> *__restrict__ tabg, int m, HessDims h, Epilogue<T> ep) {
     PFB_DYN_SMEM(raw);
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
-    const int M = h.M, L = h.R;
+    const int M = h.M, L = h.R;                  // L = 1, 2 or 4
+    const int ls = L == 4 ? 2 : L == 2 ? 1 : 0;
     constexpr int cts = ct_stride(P2);
     Cx<T> *tab = rt + kMxHead;
     Cx<T> *R1 = tab + ct_tab_size(P2), *R2 = R1 + (long)L * M;
     const int band = blockIdx.y, row0 = blockIdx.x * L;
     peel_load_tables<T, P2>(rt, roots, tw, tabg, M);
     // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m]), m < M
-    for (int i = threadIdx.x; i < M * L; i += blockDim.x) {
-        const int mm = i / L, l = i - mm * L;
-        Cx<T> xm = cx<T>((T)0, (T)0), xr = xm;
-        if (row0 + l < h.nx) {
-            const Cx<T> *col = S + (long)band * h.nyo2 * h.nx + row0 + l;
-            xm = col[(long)mm * h.nx];
-            xr = cconj(col[(long)(M - mm) * h.nx]);
-        }
-        const Cx<T> P = xm + xr, Q = xm - xr;
-        const Cx<T> wQ = cmul(cconj(twr[mm]), Q);
-        R2[(long)l * m * cts + peel_xidx<P2>(mm)] = cx<T>(P.x - wQ.y, P.y + wQ.x);
-    }
+    constexpr int U3 = sizeof(T) == 4 ? 8 : 2;
+    Cx<T> xm[U3], xr[U3], w[U3];
+    peel_batched<U3>(M * L,
+        [&](int u, int i) {
+            const int mm = i >> ls, l = i & (L - 1);
+            xm[u] = xr[u] = cx<T>((T)0, (T)0);
+            if (row0 + l < h.nx) {
+                const Cx<T> *col = S + (long)band * h.nyo2 * h.nx + row0 + l;
+                xm[u] = col[(long)mm * h.nx];
+                xr[u] = col[(long)(M - mm) * h.nx];
+            }
+            w[u] = twr[mm];
+        },
+        [&](int u, int i) {
+            const int mm = i >> ls, l = i & (L - 1);
+            const Cx<T> c = cconj(xr[u]);
+            const Cx<T> P = xm[u] + c, Q = xm[u] - c;
+            const Cx<T> wQ = cmul(cconj(w[u]), Q);
+            R2[(long)l * m * cts + peel_xidx<P2>(mm)] = cx<T>(P.x - wQ.y, P.y + wQ.x);
+        });
     __syncthreads();
     peel_inv<T, P2>(R2, R1, L, m, rt + 40, tab, rt);
-    for (int i = threadIdx.x; i < L * M; i += blockDim.x) {
-        const int l = i / M, mm = i - l * M, row = row0 + l, c0 = 2 * mm;
-        if (row >= h.nx) continue;
+    for (int l = 0; l < L; ++l) {
+        const int row = row0 + l;
+        if (row >= h.nx) break;
         const long ro = ((long)band * h.nx + row) * h.ny;
-        const Cx<T> z = R1[i];
-        const T val[2] = {z.x, z.y};
+#pragma unroll 4
+        for (int mm = threadIdx.x; mm < M; mm += blockDim.x) {
+            const Cx<T> z = R1[(long)l * M + mm];
+            const T val[2] = {z.x, z.y};
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            const int c = c0 + q;
-            if (c < h.ny) {
-                T o = val[q];
-                if (ep.beam) o *= ep.beam[ro + c];
-                if (ep.has_wsum) o /= ep.wsum;
-                if (ep.x) o += ep.x[ro + c] * ep.sigmainv;
-                out[ro + c] = o;
+            for (int q = 0; q < 2; ++q) {
+                const int c = 2 * mm + q;
+                if (c < h.ny) {
+                    T o = val[q];
+                    if (ep.beam) o *= ep.beam[ro + c];
+                    if (ep.has_wsum) o /= ep.wsum;
+                    if (ep.x) o += ep.x[ro + c] * ep.sigmainv;
+                    out[ro + c] = o;
+                }
             }
         }
     }
