@@ -272,7 +272,7 @@ struct pfb_hess_plan {
     // odd factor x power of two (hess_peel.cuh): passes whose length is m * P2 leave the
     // run-time radix list for m compile-time transforms of length P2
     pfb::PeelDesc prow, pcol;
-    int LrowP;               // rows per CTA of the peeled row passes
+    int LrowP, inplR;        // rows per CTA of the peeled row passes; lines transformed in place
     void *ptabR, *ptabC;     // ct_fft stage tables of prow.P2 / pcol.P2
 #ifndef PFB_EMU
     CUtensorMap tmS;         // S as (band, k, row) tensor of 8-byte elements, box 2 rows x 256 k (fp32 fast path)
@@ -598,11 +598,12 @@ template <class T, int P2>
 static int peel_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
     HessDims h = p->h;
     h.R = p->LrowP;
-    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R);
+    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R, p->inplR != 0);
+    const int nthr = p->inplR ? p->prow.m * (P2 / 16) : peel_threads(p->prow.m, P2, h.R);
     PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_fwd<T, P2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    launch(&k_hessp_rows_fwd<T, P2>, dim3(cdiv(h.nx, h.R), h.nband), dim3(peel_threads(p->prow.m, P2, h.R)), smem, st,
+    launch(&k_hessp_rows_fwd<T, P2>, dim3(cdiv(h.nx, h.R), h.nband), dim3(nthr), smem, st,
            x, beam, (Cx<T> *)p->S, (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots,
-           (const Cx<T> *)p->ptabR, p->prow.m, h);
+           (const Cx<T> *)p->ptabR, p->prow.m, p->inplR, h);
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
@@ -610,11 +611,12 @@ template <class T, int P2>
 static int peel_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
     HessDims h = p->h;
     h.R = p->LrowP;
-    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R);
+    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R, p->inplR != 0);
+    const int nthr = p->inplR ? p->prow.m * (P2 / 16) : peel_threads(p->prow.m, P2, h.R);
     PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_inv<T, P2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    launch(&k_hessp_rows_inv<T, P2>, dim3(cdiv(h.nx, h.R), h.nband), dim3(peel_threads(p->prow.m, P2, h.R)), smem, st,
+    launch(&k_hessp_rows_inv<T, P2>, dim3(cdiv(h.nx, h.R), h.nband), dim3(nthr), smem, st,
            (const Cx<T> *)p->S, out, (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots,
-           (const Cx<T> *)p->ptabR, p->prow.m, h, ep);
+           (const Cx<T> *)p->ptabR, p->prow.m, p->inplR, h, ep);
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
@@ -834,9 +836,11 @@ static int hess_plan_create_mixed(pfb_hess_plan **out, int nband, int nx, int ny
                    cudaMemcpy(*dst, hbuf.data(), hbuf.size(), cudaMemcpyHostToDevice) == cudaSuccess;
         };
         PeelDesc pr, pc;
-        if (peel_make_desc(M, pr) && cs * peel_smem_elems(M, pr.m, pr.P2, 1) <= kMaxSmemFast) {
+        const bool inpl = peel_make_desc(M, pr) && peel_can_inplace(pr.m, pr.P2) && !getenv("PFB_HESS_PEEL_NOINPL");
+        if (pr.m && cs * peel_smem_elems(M, pr.m, pr.P2, 1, inpl) <= kMaxSmemFast) {
+            p->inplR = inpl ? 1 : 0;
             p->LrowP = dtype == PFB_F32 ? 4 : 2;
-            while (p->LrowP > 1 && cs * peel_smem_elems(M, pr.m, pr.P2, p->LrowP) > kMaxSmemFast) p->LrowP >>= 1;
+            while (p->LrowP > 1 && cs * peel_smem_elems(M, pr.m, pr.P2, p->LrowP, inpl) > kMaxSmemFast) p->LrowP >>= 1;
             p->prow = pr;
             good = good && table(&p->ptabR, pr.P2);
         }

@@ -57,9 +57,12 @@ template <int P2> __host__ __device__ constexpr int peel_nbar() {
 }
 
 // shared memory: [roots 40][two-level twiddles of N: kMxTwMax][ct table of P2][R1: L N][R2: L m ct_stride(P2)]
-static inline size_t peel_smem_elems(int N, int m, int P2, int L) {
-    return (size_t)kMxHead + ct_tab_size(P2) + (size_t)L * N + (size_t)L * m * ct_stride(P2);
+// inpl (row passes): no R1, the natural-order line lives in its own R2 block
+static inline size_t peel_smem_elems(int N, int m, int P2, int L, bool inpl = false) {
+    return (size_t)kMxHead + ct_tab_size(P2) + 4 + (inpl ? 0 : (size_t)L * N) + (size_t)L * m * ct_stride(P2);
 }
+// in-place row passes need exactly one thread group per segment
+static inline bool peel_can_inplace(int m, int P2) { return m * (P2 / 16) <= 640; }
 // threads per CTA: G groups of P2/16 threads, G <= number of sub-transforms, <= 15 named
 // barriers, about 640 threads (register budget 102 per thread)
 static inline int peel_threads(int m, int P2, int L) {
@@ -174,9 +177,13 @@ __device__ __forceinline__ void peel_mid_r(Cx<T> *R2, int P2, int cts, const Cx<
 // forward sub-transforms only (R1 -> twiddled segments of R2), synchronised on exit
 template <class T, int P2>
 __device__ __forceinline__ void peel_fwd_subs(const Cx<T> *R1, Cx<T> *R2, int L, int m,
-                                              const Cx<T> *tws, const Cx<T> *tab) {
+                                              const Cx<T> *tws, const Cx<T> *tab,
+                                              int ld1 = 0, bool inpl = false) {
+    // inpl: R1 line l IS the R2 block of line l (ld1 = m ct_stride(P2)); requires one group per
+    // segment (blockDim = m P2/16), so that a round is exactly one line and the block-wide
+    // barrier below separates its last natural-order read from the first exchange write
     constexpr int NT = P2 / 16, cts = ct_stride(P2);
-    const int N = m * P2, G = blockDim.x / NT;
+    const int N = ld1 ? ld1 : m * P2, G = blockDim.x / NT;
     const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
     const GroupBar bar{1 + g, NT};
     const int nsub = m * L;
@@ -189,6 +196,7 @@ __device__ __forceinline__ void peel_fwd_subs(const Cx<T> *R1, Cx<T> *R2, int L,
             Cx<T> v[16];
 #pragma unroll
             for (int e = 0; e < 16; ++e) v[e] = src[(t + e * NT) * m];
+            if (inpl) __syncthreads();
             ct_fft<T, P2, -1>(v, t, X, tab, bar);
             bar();                                // the last exchange of X has been read
 #pragma unroll
@@ -207,9 +215,10 @@ __device__ __forceinline__ void peel_fwd_subs(const Cx<T> *R1, Cx<T> *R2, int L,
 
 // inverse sub-transforms only (segments of R2, already butterflied and twiddled -> R1)
 template <class T, int P2>
-__device__ __forceinline__ void peel_inv_subs(Cx<T> *R2, Cx<T> *R1, int L, int m, const Cx<T> *tab) {
+__device__ __forceinline__ void peel_inv_subs(Cx<T> *R2, Cx<T> *R1, int L, int m, const Cx<T> *tab,
+                                              int ld1 = 0, bool inpl = false) {
     constexpr int NT = P2 / 16, cts = ct_stride(P2);
-    const int N = m * P2, G = blockDim.x / NT;
+    const int N = ld1 ? ld1 : m * P2, G = blockDim.x / NT;
     const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;
     const GroupBar bar{1 + g, NT};
     const int nsub = m * L;
@@ -223,6 +232,7 @@ __device__ __forceinline__ void peel_inv_subs(Cx<T> *R2, Cx<T> *R1, int L, int m
 #pragma unroll
             for (int e = 0; e < 16; ++e) v[e] = X[t + e * NT];
             ct_fft<T, P2, +1>(v, t, X, tab, bar);
+            if (inpl) __syncthreads();            // every segment of the line is done with its exchanges
 #pragma unroll
             for (int e = 0; e < 16; ++e) dst[(t + e * NT) * m] = v[e];
 #ifdef PFB_EMU
@@ -240,8 +250,9 @@ __device__ __forceinline__ void peel_inv_subs(Cx<T> *R2, Cx<T> *R1, int L, int m
 // forward: R1 (natural, L lines of N) -> R2 (segment layout).  Synchronised on exit.
 template <class T, int P2>
 __device__ __forceinline__ void peel_fwd(const Cx<T> *R1, Cx<T> *R2, int L, int m,
-                                         const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt) {
-    peel_fwd_subs<T, P2>(R1, R2, L, m, tws, tab);
+                                         const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt,
+                                         int ld1 = 0, bool inpl = false) {
+    peel_fwd_subs<T, P2>(R1, R2, L, m, tws, tab, ld1, inpl);
     peel_butterflies<T, -1>(R2, L, m, P2, ct_stride(P2), tws, rt);
     __syncthreads();
 }
@@ -249,10 +260,11 @@ __device__ __forceinline__ void peel_fwd(const Cx<T> *R1, Cx<T> *R2, int L, int 
 // inverse: R2 (segment layout) -> R1 (natural), unnormalised.  Synchronised on exit.
 template <class T, int P2>
 __device__ __forceinline__ void peel_inv(Cx<T> *R2, Cx<T> *R1, int L, int m,
-                                         const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt) {
+                                         const Cx<T> *tws, const Cx<T> *tab, const Cx<T> *rt,
+                                         int ld1 = 0, bool inpl = false) {
     peel_butterflies<T, +1>(R2, L, m, P2, ct_stride(P2), tws, rt);
     __syncthreads();
-    peel_inv_subs<T, P2>(R2, R1, L, m, tab);
+    peel_inv_subs<T, P2>(R2, R1, L, m, tab, ld1, inpl);
 }
 
 // forward pair - PSF - inverse pair of one column (half): R1 -> R1
@@ -275,14 +287,16 @@ template <class T, int P2>
 __global__ void __launch_bounds__(640)
 k_hessp_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__restrict__ S,
                  const Cx<T> *__restrict__ tw, const Cx<T> *__restrict__ twr,
-                 const Cx<T> *__restrict__ roots, const Cx<T> *__restrict__ tabg, int m, HessDims h) {
+                 const Cx<T> *__restrict__ roots, const Cx<T> *__restrict__ tabg, int m, int inpl,
+                 HessDims h) {
     PFB_DYN_SMEM(raw);
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
     const int M = h.M, L = h.R;                  // L = 1, 2 or 4
     const int ls = L == 4 ? 2 : L == 2 ? 1 : 0;
     constexpr int cts = ct_stride(P2);
     Cx<T> *tab = rt + kMxHead;
-    Cx<T> *R1 = tab + ct_tab_size(P2), *R2 = R1 + (long)L * M;
+    Cx<T> *R1 = tab + ct_tab_size(P2) + 4, *R2 = inpl ? R1 : R1 + (long)L * M;
+    const int ld1 = inpl ? m * cts : M;
     const int band = blockIdx.y, row0 = blockIdx.x * L;
     peel_load_tables<T, P2>(rt, roots, tw, tabg, M);
     for (int l = 0; l < L; ++l) {
@@ -298,10 +312,10 @@ k_hessp_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
                     if (c0 + 1 < h.ny) { b[u] = x[ro + c0 + 1]; if (beam) b[u] *= beam[ro + c0 + 1]; }
                 }
             },
-            [&](int u, int mm) { R1[(long)l * M + mm] = cx<T>(a[u], b[u]); });
+            [&](int u, int mm) { R1[(long)l * ld1 + mm] = cx<T>(a[u], b[u]); });
     }
     __syncthreads();
-    peel_fwd<T, P2>(R1, R2, L, m, rt + 40, tab, rt);
+    peel_fwd<T, P2>(R1, R2, L, m, rt + 40, tab, rt, ld1, inpl != 0);
     // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
     Cx<T> w[4];
     peel_batched<4>((M + 1) * L,
@@ -331,7 +345,7 @@ k_hessp_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
     const int N = m * P2;
     Cx<T> *tab = rt + kMxHead;
-    Cx<T> *R1 = tab + ct_tab_size(P2), *R2 = R1 + N;
+    Cx<T> *R1 = tab + ct_tab_size(P2) + 4, *R2 = R1 + N;
     const int band = blockIdx.y, col = blockIdx.x;
     Cx<T> *line = S + ((long)band * h.nyo2 + col) * h.nx;
     const Cx<T> *pl = psfT + ((long)band * h.nyo2 + col) * h.nxp;
@@ -371,50 +385,75 @@ k_hessp_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
 }
 
 // ------------------------------------------------------------------ pass C
+// Mirror of pass A with the epilogue fused.  Every element of the S tile is fetched ONCE into
+// the line's R2 block; X[m] and X[M-m] are then combined pairwise in place.
 template <class T, int P2>
 __global__ void __launch_bounds__(640)
 k_hessp_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *__restrict__ tw,
                  const Cx<T> *__restrict__ twr, const Cx<T> *__restrict__ roots,
-                 const Cx<T> *__restrict__ tabg, int m, HessDims h, Epilogue<T> ep) {
+                 const Cx<T> *__restrict__ tabg, int m, int inpl, HessDims h, Epilogue<T> ep) {
     PFB_DYN_SMEM(raw);
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
     const int M = h.M, L = h.R;                  // L = 1, 2 or 4
     const int ls = L == 4 ? 2 : L == 2 ? 1 : 0;
     constexpr int cts = ct_stride(P2);
     Cx<T> *tab = rt + kMxHead;
-    Cx<T> *R1 = tab + ct_tab_size(P2), *R2 = R1 + (long)L * M;
+    Cx<T> *xtop = tab + ct_tab_size(P2);         // X[M] of each line
+    Cx<T> *R1 = xtop + 4, *R2 = inpl ? R1 : R1 + (long)L * M;
+    const int ld1 = inpl ? m * cts : M;
     const int band = blockIdx.y, row0 = blockIdx.x * L;
     peel_load_tables<T, P2>(rt, roots, tw, tabg, M);
-    // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m]), m < M
-    constexpr int U3 = sizeof(T) == 4 ? 8 : 2;
-    Cx<T> xm[U3], xr[U3], w[U3];
-    peel_batched<U3>(M * L,
-        [&](int u, int i) {
-            const int mm = i >> ls, l = i & (L - 1);
-            xm[u] = xr[u] = cx<T>((T)0, (T)0);
-            if (row0 + l < h.nx) {
-                const Cx<T> *col = S + (long)band * h.nyo2 * h.nx + row0 + l;
-                xm[u] = col[(long)mm * h.nx];
-                xr[u] = col[(long)(M - mm) * h.nx];
-            }
-            w[u] = twr[mm];
-        },
-        [&](int u, int i) {
-            const int mm = i >> ls, l = i & (L - 1);
-            const Cx<T> c = cconj(xr[u]);
-            const Cx<T> P = xm[u] + c, Q = xm[u] - c;
-            const Cx<T> wQ = cmul(cconj(w[u]), Q);
-            R2[(long)l * m * cts + peel_xidx<P2>(mm)] = cx<T>(P.x - wQ.y, P.y + wQ.x);
-        });
+    constexpr int U3 = sizeof(T) == 4 ? 8 : 4;
+    {
+        Cx<T> xv[U3];
+        const Cx<T> *tile = S + (long)band * h.nyo2 * h.nx + row0;
+        peel_batched<U3>((M + 1) * L,
+            [&](int u, int i) {
+                const int k = i >> ls, l = i & (L - 1);
+                xv[u] = row0 + l < h.nx ? tile[(long)k * h.nx + l] : cx<T>((T)0, (T)0);
+            },
+            [&](int u, int i) {
+                const int k = i >> ls, l = i & (L - 1);
+                if (k == M) xtop[l] = xv[u];
+                else R2[(long)l * m * cts + peel_xidx<P2>(k)] = xv[u];
+            });
+    }
     __syncthreads();
-    peel_inv<T, P2>(R2, R1, L, m, rt + 40, tab, rt);
+    // Z'[j] = (X[j] + conj X[M-j]) + i w^-j (X[j] - conj X[M-j])   (= 2 Z[j]), j < M; the pair
+    // j, M-j shares its inputs and w^(M-j) = -conj w^j
+    {
+        Cx<T> w[4];
+        const int np = M / 2 + 1;                // pairs (j, M - j), j = 0 .. M/2
+        peel_batched<4>(np * L,
+            [&](int u, int i) { w[u] = twr[i >> ls]; },
+            [&](int u, int i) {
+                const int j = i >> ls, l = i & (L - 1);
+                Cx<T> *z = R2 + (long)l * m * cts;
+                const int ia = peel_xidx<P2>(j), ib = peel_xidx<P2>(j == 0 ? 0 : M - j);
+                const Cx<T> a = z[ia], b = j == 0 ? xtop[l] : z[ib];
+                {
+                    const Cx<T> c = cconj(b);
+                    const Cx<T> P = a + c, Q = a - c;
+                    const Cx<T> wQ = cmul(cconj(w[u]), Q);
+                    z[ia] = cx<T>(P.x - wQ.y, P.y + wQ.x);
+                }
+                if (j != 0 && 2 * j != M) {
+                    const Cx<T> c = cconj(a);
+                    const Cx<T> P = b + c, Q = b - c;
+                    const Cx<T> wQ = cmul(cx<T>(-w[u].x, -w[u].y), Q);   // conj(w^(M-j)) = -w^j
+                    z[ib] = cx<T>(P.x - wQ.y, P.y + wQ.x);
+                }
+            });
+    }
+    __syncthreads();
+    peel_inv<T, P2>(R2, R1, L, m, rt + 40, tab, rt, ld1, inpl != 0);
     for (int l = 0; l < L; ++l) {
         const int row = row0 + l;
         if (row >= h.nx) break;
         const long ro = ((long)band * h.nx + row) * h.ny;
 #pragma unroll 4
         for (int mm = threadIdx.x; mm < M; mm += blockDim.x) {
-            const Cx<T> z = R1[(long)l * M + mm];
+            const Cx<T> z = R1[(long)l * ld1 + mm];
             const T val[2] = {z.x, z.y};
 #pragma unroll
             for (int q = 0; q < 2; ++q) {

@@ -102,7 +102,7 @@ MIXED = [(8, 8, 24, 32), (8, 8, 16, 16), (5, 6, 10, 12), (12, 14, 24, 28), (9, 2
          # (3, 5, 7) x power of two: hess_peel.cuh -- rows (M = 1536, 2560), split columns
          # (H = 1536, 3584), full columns (nxp = 3072), both at once
          (6, 1500, 12, 3072), (4, 2500, 8, 5120), (1500, 6, 3072, 12), (3000, 4, 7168, 8),
-         (2000, 6, 3072, 12), (1400, 1300, 3072, 3072)]
+         (2000, 6, 3072, 12), (1400, 1300, 3072, 3072), (4, 3500, 8, 7168)]
 
 
 @pmp("dtype", [np.float32, np.float64])
@@ -119,7 +119,7 @@ def test_hess_mixed_radix_oracle(dtype, nx, ny, nxp, nyp):
     assert H.rc == 0
     # which passes run as (3|5|7) x 2^k peeled transforms (hess_peel.cuh)
     def peels(n):
-        return any(n % m == 0 and n // m in (512, 1024, 2048, 4096) for m in (3, 5, 7))
+        return n <= 10240 and any(n % m == 0 and n // m in (512, 1024, 2048, 4096) for m in (3, 5, 7))
     kern = H.L.pfb_hess_plan_kernels(H.plan)
     assert kern & 2
     assert bool(kern & 4) == peels(nyp // 2)
@@ -132,6 +132,15 @@ def test_hess_mixed_radix_oracle(dtype, nx, ny, nxp, nyp):
     assert rel(H.apply(x), exp) < tol
     exp2 = ref.hessian_psf_cube(xpad, xhat, xout, beam, psfhat, nyp, x, sigmainv=0.25, wsum=3.5)
     assert rel(H.apply(x, beam, 1, 0.25, 3.5), exp2) < tol
+
+
+def test_hess_peel_two_buffer_rows(monkeypatch):
+    """Row passes of the peeled kernels with separate natural-order / segment buffers (what runs
+    when a line's thread groups do not fit one CTA) instead of the in-place lines."""
+    monkeypatch.setenv("PFB_HESS_PEEL_NOINPL", "1")
+    for dtype in (np.float32, np.float64):
+        test_hess_mixed_radix_oracle(dtype, 6, 1500, 12, 3072)
+        test_hess_mixed_radix_oracle(dtype, 5, 2500, 10, 5120)
 
 
 def test_hess_plan_errors():

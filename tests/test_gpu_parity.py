@@ -175,7 +175,8 @@ def test_hess_vs_oracle(dtype, nx, ny, nxp, nyp):
                         # (3|5|7) x 2^k: hess_peel.cuh (rows, split / full columns, all P2)
                         (6, 1500, 12, 3072), (1500, 6, 3072, 12), (2000, 6, 3072, 12),
                         (1400, 1300, 3072, 3072), (2500, 2400, 5120, 5120), (3000, 3500, 7168, 7168),
-                        (3000, 2900, 6144, 6144), (5000, 4800, 10240, 10240), (3584, 3000, 7168, 6144)])
+                        (3000, 2900, 6144, 6144), (5000, 4800, 10240, 10240), (3584, 3000, 7168, 6144),
+                        (4, 3500, 8, 7168), (3500, 5, 7168, 10)])
 def test_hess_mixed_radix_vs_oracle(dtype, nx, ny, nxp, nyp):
     """Padded sizes that are not powers of two (ducc0 good_size lengths,
     pfb/workers/grid.py:276-284): hess_mixed.cuh, split and full column pass."""
