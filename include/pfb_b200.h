@@ -33,7 +33,8 @@ typedef enum {
     PFB_ERR_FFT_SIZE = 4,    /* padded size not supported by the FFT kernels */
     PFB_ERR_CUDA = 5,        /* CUDA runtime error, see pfb_last_error() */
     PFB_ERR_ALLOC = 6,
-    PFB_ERR_NBAND = 7        /* more bands than a kernel supports */
+    PFB_ERR_NBAND = 7,       /* more bands than a kernel supports */
+    PFB_ERR_NAN = 8          /* a solver loop met NaN / Inf or an identically zero model */
 } pfb_status;
 
 typedef enum { PFB_F32 = 0, PFB_F64 = 1 } pfb_dtype;
@@ -292,6 +293,36 @@ int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *plan);
 int pfb_hess_apply_primal(pfb_hess_plan *plan, const void *xp, const void *w, const void *wprev,
                           const void *data, double tau, int positivity, void *x, double *out2,
                           void *stream);
+
+/* ---------------------------------------------------- solver loops --
+ * The iteration loops themselves as library calls, for hosts that are not Python (the Python
+ * package issues the same launch sequences from pfb_b200/opt/).  Device pointers, one
+ * stream; scratch is allocated on entry and freed on exit; every call returns after its
+ * last kernel has finished.  Band-sharded runs use the Python loops (NCCL lives there). */
+
+/* primal_dual_optimised(x, v, lam, psiH, psi, L, prox_21m, l1weight, None, grad21, nu, sigma,
+ * tol, maxit, positivity, gamma)  pfb/opt/primal_dual.py:90-171 with
+ * grad21(x) = psf_convolve(x) - data (pfb/workers/spotless.py:259-263) and no reweighter.
+ * x (nband, nx, ny) and v (nband, nbasis, Nymax, Nxmax) are updated in place; l1weight is
+ * (nbasis, Nymax, Nxmax).  sigma <= 0: L / (2 gamma) / nu.  niter = iterations run,
+ * eps = the last ||x - xp|| / ||x||.  Same kernels in the same order as the Python loop
+ * (natural-orientation dual, synthesis by linearity, primal step fused into the last
+ * Hessian pass where the plan allows). */
+int pfb_pd_run(const pfb_psi_plan *psi, pfb_hess_plan *hess, void *x, void *v, const void *data,
+               const void *l1weight, int nband, int nx, int ny, int nbasis, double lam, double L,
+               double nu, double sigma, double gamma, double tol, int maxit, int positivity,
+               int dtype, int *niter, double *eps, void *stream);
+/* power_method(psf_convolve, imsize, b0, tol, maxit)  pfb/opt/power_method.py:11-46;
+ * b holds b0 on entry and the normalised vector on exit. */
+int pfb_power_method_run(pfb_hess_plan *hess, void *b, int nband, int nx, int ny, double tol,
+                         int maxit, int dtype, double *beta, int *niter, void *stream);
+/* pcg(A, b, x0, M, tol, maxit, minit, backtrack)  pfb/opt/pcg.py:58-131 with
+ * A = hessian_psf_cube(beam, psfhat, sigmainv, wsum) (pfb/operators/hessian.py:254-281) and
+ * M(x) = minv * x; x holds x0 on entry and the solution on exit; the line-search scalars stay
+ * on the device (pfb_pcg_seg_*). */
+int pfb_pcg_run(pfb_hess_plan *hess, const void *beam, double sigmainv, int has_wsum, double wsum,
+                const void *b, void *x, double minv, int nband, int nx, int ny, double tol, int maxit,
+                int minit, int backtrack, int dtype, int *niter, double *eps, void *stream);
 
 /* ------------------------------------------------- CLEAN minor loops --
  * pfb/deconv/clark.py (clark :84-177, subminor :29-82, subtract :12-26) and

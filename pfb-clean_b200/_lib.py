@@ -70,6 +70,11 @@ _SIGS = {
     "pfb_pcg_seg_scalar": (c_int, [_P, c_int, c_int, _P]),
     "pfb_pcg_seg_update": (c_int, [_P, _P, _P, _P, _P, _P, c_double, c_int, c_longlong, c_int, _P, _P]),
     "pfb_pcg_seg_direction": (c_int, [_P, _P, _P, c_double, c_int, c_longlong, c_int, _P, _P]),
+    "pfb_pd_run": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_double, c_double,
+                           c_double, c_double, c_double, c_double, c_int, c_int, c_int, _P, _P, _P]),
+    "pfb_power_method_run": (c_int, [_P, _P, c_int, c_int, c_int, c_double, c_int, c_int, _P, _P, _P]),
+    "pfb_pcg_run": (c_int, [_P, _P, c_double, c_int, c_double, _P, _P, c_double, c_int, c_int, c_int,
+                            c_double, c_int, c_int, c_int, c_int, _P, _P, _P]),
     "pfb_mfs_peak": (c_int, [_P, c_int, c_longlong, _P, _P, c_int, _P]),
     "pfb_active_set": (c_int, [_P, c_longlong, c_double, _P, c_longlong, _P, _P, c_int, _P]),
     "pfb_clark_subminor": (c_int, [_P, _P, _P, c_longlong, _P, _P, c_int, c_int, c_int, c_int, c_int,
