@@ -293,6 +293,15 @@ int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *plan);
 int pfb_hess_apply_primal(pfb_hess_plan *plan, const void *xp, const void *w, const void *wprev,
                           const void *data, double tau, int positivity, void *x, double *out2,
                           void *stream);
+/* The same call in two halves: begin = the passes that need xp only (rows forward, columns
+ * forward x psfhat x inverse; the result stays in the plan's scratch), end = the last pass with
+ * the primal step.  A band-sharded solver issues begin right behind the previous primal step,
+ * where it hides the all-reduce of the band-sum image (pfb_dual_update_rec), and end once the
+ * synthesis w = Psi(v) of the new dual is there.  No other call on the plan in between. */
+int pfb_hess_apply_primal_begin(pfb_hess_plan *plan, const void *xp, void *stream);
+int pfb_hess_apply_primal_end(pfb_hess_plan *plan, const void *xp, const void *w, const void *wprev,
+                              const void *data, double tau, int positivity, void *x, double *out2,
+                              void *stream);
 
 /* ---------------------------------------------------- solver loops --
  * The iteration loops themselves as library calls, for hosts that are not Python (the Python

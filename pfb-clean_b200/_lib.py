@@ -51,6 +51,8 @@ _SIGS = {
     "pfb_hess_plan_can_fuse_primal": (c_int, [_P]),
     "pfb_hess_plan_kernels": (c_int, [_P]),
     "pfb_hess_apply_primal": (c_int, [_P, _P, _P, _P, _P, c_double, c_int, _P, _P, _P]),
+    "pfb_hess_apply_primal_begin": (c_int, [_P, _P, _P]),
+    "pfb_hess_apply_primal_end": (c_int, [_P, _P, _P, _P, _P, c_double, c_int, _P, _P, _P]),
     "pfb_psi_plan_query": (c_int, [_P, POINTER(c_int), POINTER(c_int)]),
     "pfb_psi_plan_tables": (c_int, [_P, c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "pfb_psi_dot": (c_int, [_P, _P, _P, _P]),

@@ -1143,32 +1143,54 @@ int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *p) {
 #endif
 }
 
-int pfb_hess_apply_primal(pfb_hess_plan *p, const void *xp, const void *w, const void *wprev,
-                          const void *data, double tau, int positivity, void *x, double *out2,
-                          void *stream) {
-#ifndef PFB_EMU
-    if (!p || !xp || !w || !wprev || !data || !x || !out2 || (positivity != 0 && positivity != 1))
-        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: bad argument");
-    if (!p->have_psf) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: psfhat not set");
+static int primal_args_ok(const pfb_hess_plan *p, const char *who) {
+    if (!p) return fail(PFB_ERR_BAD_ARG, "%s: bad argument", who);
+    if (!p->have_psf) return fail(PFB_ERR_BAD_ARG, "%s: psfhat not set", who);
     if (!pfb_hess_plan_can_fuse_primal(p))
-        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: not available for this plan "
-                                     "(see pfb_hess_plan_can_fuse_primal)");
-    if (x == xp) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: x must not alias xp");
-    if (((uintptr_t)xp | (uintptr_t)w | (uintptr_t)wprev | (uintptr_t)data | (uintptr_t)x) & 7)
-        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: arrays must be 8-byte aligned");
+        return fail(PFB_ERR_BAD_ARG, "%s: not available for this plan (see pfb_hess_plan_can_fuse_primal)", who);
+    return PFB_OK;
+}
+
+int pfb_hess_apply_primal_begin(pfb_hess_plan *p, const void *xp, void *stream) {
+#ifndef PFB_EMU
+    if (int rc = primal_args_ok(p, "pfb_hess_apply_primal_begin")) return rc;
+    if (!xp || ((uintptr_t)xp & 7)) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_begin: bad argument");
     cudaStream_t st = as_stream(stream);
     if (p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
     if (int rc = fast_rows_fwd_d<float>(p, (const float *)xp, nullptr, st)) return rc;
-    if (int rc = fast_cols_d<float>(p, st)) return rc;
+    return fast_cols_d<float>(p, st);
+#else
+    (void)p; (void)xp; (void)stream;
+    return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_begin: not available in the emulator build");
+#endif
+}
+
+int pfb_hess_apply_primal_end(pfb_hess_plan *p, const void *xp, const void *w, const void *wprev,
+                              const void *data, double tau, int positivity, void *x, double *out2,
+                              void *stream) {
+#ifndef PFB_EMU
+    if (int rc = primal_args_ok(p, "pfb_hess_apply_primal_end")) return rc;
+    if (!xp || !w || !wprev || !data || !x || !out2 || (positivity != 0 && positivity != 1))
+        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: bad argument");
+    if (x == xp) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: x must not alias xp");
+    if (((uintptr_t)xp | (uintptr_t)w | (uintptr_t)wprev | (uintptr_t)data | (uintptr_t)x) & 7)
+        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: arrays must be 8-byte aligned");
     PrimalArgs pa;
     pa.xp = (const float *)xp; pa.w = (const float *)w; pa.wprev = (const float *)wprev;
     pa.data = (const float *)data; pa.x = (float *)x; pa.tau = (float)tau; pa.positivity = positivity;
     pa.part = nullptr;
-    return run_primal_m(p, pa, out2, st);
+    return run_primal_m(p, pa, out2, as_stream(stream));
 #else
     (void)p; (void)xp; (void)w; (void)wprev; (void)data; (void)tau; (void)positivity; (void)x; (void)out2; (void)stream;
-    return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal: not available in the emulator build");
+    return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: not available in the emulator build");
 #endif
+}
+
+int pfb_hess_apply_primal(pfb_hess_plan *p, const void *xp, const void *w, const void *wprev,
+                          const void *data, double tau, int positivity, void *x, double *out2,
+                          void *stream) {
+    if (int rc = pfb_hess_apply_primal_begin(p, xp, stream)) return rc;
+    return pfb_hess_apply_primal_end(p, xp, w, wprev, data, tau, positivity, x, out2, stream);
 }
 
 }  // extern "C"

@@ -55,6 +55,17 @@ class HessPlan:
             int(positivity), _dev.ptr(x), _dev.ptr(out2), _dev.stream()))
         return out2
 
+    def apply_primal_begin(self, xp):
+        """The passes of apply_primal that need xp only (result kept in the plan's scratch)."""
+        _lib.check(_lib.lib().pfb_hess_apply_primal_begin(self._h, _dev.ptr(xp), _dev.stream()))
+
+    def apply_primal_end(self, xp, w, wprev, data, tau, positivity, x, out2):
+        """Last pass + primal step of apply_primal; apply_primal_begin(xp) must precede it."""
+        _lib.check(_lib.lib().pfb_hess_apply_primal_end(
+            self._h, _dev.ptr(xp), _dev.ptr(w), _dev.ptr(wprev), _dev.ptr(data), float(tau),
+            int(positivity), _dev.ptr(x), _dev.ptr(out2), _dev.stream()))
+        return out2
+
     def __del__(self):
         if getattr(self, "_h", None) and self._h.value:
             self._destroy(self._h)

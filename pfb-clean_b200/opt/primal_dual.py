@@ -267,8 +267,13 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     # PSF convolution with the primal step as the epilogue of its last pass
     # (pfb_hess_apply_primal): no convolution result in memory, no separate primal kernel
     fplan = None
+    # Band-sharded ranks take it in two halves (apply_primal_begin / _end): the passes that need
+    # xp only are issued where the separate convolution was (they hide the exchange of the
+    # band-sum image), the last pass + primal step once the synthesis is there.
+    shard_ok = (not parallel.active()) or (nat and not os.environ.get("PFB_PAR_NOREC")
+                                             and not os.environ.get("PFB_PAR_NOFUSE"))
     if (lin and bound is not None and data is not None and positivity in (0, 1)
-            and not parallel.active() and xa.dtype == torch.float32
+            and shard_ok and xa.dtype == torch.float32
             and not os.environ.get("PFB_PD_NOFUSE")):
         if str(bound[0].dtype).endswith("complex64"):
             from ..operators.psf import get_plan
@@ -339,6 +344,7 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
                 return _convolve(bound[0], bound[1], xprev, conv_buf)
             return _dev.to_dev(grad.psf_convolve(xprev) if fused_grad else grad(xprev))
         g = None
+        begun = False
         if nat:
             # not lin: the dual kernel leaves 2v - vp in the (dead) vp buffer: one coefficient
             # set for the synthesis to read, which is instruction-issue bound
@@ -349,6 +355,10 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
                 if parallel.active():
                     if fplan is None:
                         g = gradient()               # hides the exchange of xbar
+                    else:
+                        fplan.set_dynamic(True)
+                        fplan.apply_primal_begin(xprev)
+                        begun = True
                     if xbar_work is not None:
                         xbar_work.wait()
                 xbar_work = None
@@ -364,7 +374,12 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             if fusedual:
                 pass
             elif rec:
-                g = gradient()                   # hides the exchange of xbar
+                if fplan is None:
+                    g = gradient()               # hides the exchange of xbar
+                else:
+                    fplan.set_dynamic(True)
+                    fplan.apply_primal_begin(xprev)
+                    begun = True
                 if xbar_work is not None:
                     xbar_work.wait()
                 xbar_work = None
@@ -388,8 +403,10 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
             psi(xprev, vcur)
             _dual_step(vprev, vcur, lam, sigma, w, n, bsum)      # vprev now holds 2v - vp
             psiH(vprev, xout)
-        if fplan is not None:
-            fplan.set_dynamic(False)
+        if fplan is not None and begun:
+            fplan.apply_primal_end(xprev, xout, wprev, data, tau, positivity, xcur, terms)
+        elif fplan is not None:
+            fplan.set_dynamic(parallel.active())
             fplan.apply_primal(xprev, xout, wprev, data, tau, positivity, xcur, terms)
         else:
             if g is None:
