@@ -380,6 +380,17 @@ int pfb_seg_stats(const void *x, int nseg, long long m, double *stats3, int dtyp
  * the per-dataset accumulation of dds2cubes, pfb/utils/misc.py:698-714 */
 int pfb_accum_mul(void *out, const void *x, const void *y, double scale, long long n, int dtype,
                   void *stream);
+/* Restoring ("cheap f5"): the pieces of convolve2gaussres, pfb/utils/misc.py:186-238,
+ * that are not the PSF-convolution kernels themselves.
+ * pfb_gauss2d: Gaussian2D (misc.py:109-138) on the caller's coordinate grids (fp64, n values each):
+ *   out = exp(-c (a00 x^2 + a01 x y + a11 y^2)) where x^2 + y^2 <= extent, else 0 (the caller forms
+ *   the 2 x 2 matrix, a01 = A[0,1] + A[1,0], c = 2 sqrt(2 ln 2), extent = (nsigma Smaj)^2).
+ * pfb_spec_ratio: convkernhat = gausskernhat / thiskernhat where |thiskernhat| > 0, else 0
+ *   (misc.py:224-226); complex arrays, num (nnum values) broadcast over the blocks of den (nden). */
+int pfb_gauss2d(const double *xx, const double *yy, long long n, double a00, double a01, double a11,
+                double c, double extent, void *out, int dtype, void *stream);
+int pfb_spec_ratio(const void *num, const void *den, void *out, long long nnum, long long nden, int dtype,
+                   void *stream);
 /* pfb_seg_stats without any allocation.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (CUDA graph
  * capture, tight serving loops, harnesses that forbid it).  Same arguments and results as

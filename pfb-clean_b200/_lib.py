@@ -72,6 +72,8 @@ _SIGS = {
     "pfb_pcg_seg_scalar": (c_int, [_P, c_int, c_int, _P]),
     "pfb_pcg_seg_update": (c_int, [_P, _P, _P, _P, _P, _P, c_double, c_int, c_longlong, c_int, _P, _P]),
     "pfb_pcg_seg_direction": (c_int, [_P, _P, _P, c_double, c_int, c_longlong, c_int, _P, _P]),
+    "pfb_gauss2d": (c_int, [_P, _P, c_longlong, c_double, c_double, c_double, c_double, c_double, _P, c_int, _P]),
+    "pfb_spec_ratio": (c_int, [_P, _P, _P, c_longlong, c_longlong, c_int, _P]),
     "pfb_pd_run": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_double, c_double,
                            c_double, c_double, c_double, c_double, c_int, c_int, c_int, _P, _P, _P]),
     "pfb_power_method_run": (c_int, [_P, _P, c_int, c_int, c_int, c_double, c_int, c_int, _P, _P, _P]),

@@ -205,6 +205,39 @@ static int seg_stats_ws_t(const T *x, int nseg, long m, double *stats, double *p
 
 using namespace pfb;
 
+// Gaussian2D (pfb/utils/misc.py:109-138): out = exp(-c (a00 x^2 + a01 x y + a11 y^2)) where
+// x^2 + y^2 <= extent, 0 elsewhere; coordinates and arithmetic fp64 like the reference
+template <class T>
+__global__ void __launch_bounds__(256)
+k_gauss2d(const double *__restrict__ xx, const double *__restrict__ yy, long n, double a00, double a01,
+          double a11, double c, double extent, T *out) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const double x = xx[i], y = yy[i];
+        double g = 0.0;
+        if (x * x + y * y <= extent) g = exp(-c * (a00 * x * x + a01 * x * y + a11 * y * y));
+        out[i] = (T)g;
+    }
+}
+
+// convkernhat = gausskernhat / thiskernhat where |thiskernhat| > 0, else 0 (misc.py:224-226);
+// num has nnum elements and is broadcast over the nden / nnum blocks of den
+template <class T>
+__global__ void __launch_bounds__(256)
+k_spec_ratio(const T *__restrict__ num, const T *__restrict__ den, T *out, long nnum, long nden) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nden; i += (long)gridDim.x * blockDim.x) {
+        const long j = i % nnum;
+        const T a = num[2 * j], b = num[2 * j + 1], c = den[2 * i], d = den[2 * i + 1];
+        const T m = c * c + d * d;
+        T re = (T)0, im = (T)0;
+        if (c != (T)0 || d != (T)0) {
+            re = (a * c + b * d) / m;
+            im = (b * c - a * d) / m;
+        }
+        out[2 * i] = re;
+        out[2 * i + 1] = im;
+    }
+}
+
 extern "C" {
 
 int pfb_seg_stats(const void *x, int nseg, long long m, double *stats3, int dtype, void *stream) {
@@ -257,6 +290,42 @@ int pfb_l1reweight(const void *bsum, const void *rms_comps, int nbasis, long lon
         return l1reweight_t<double>((const double *)bsum, (const double *)rms_comps, nbasis, (long)nslab,
                                     rmsfactor, alpha, (double *)weight, st);
     return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+}
+
+
+int pfb_gauss2d(const double *xx, const double *yy, long long n, double a00, double a01, double a11,
+                double c, double extent, void *out, int dtype, void *stream) {
+    if (!xx || !yy || !out || n < 0) return fail(PFB_ERR_BAD_ARG, "pfb_gauss2d: bad argument");
+    if (n == 0) return PFB_OK;
+    cudaStream_t st = as_stream(stream);
+    long nb = (n + 255) / 256;
+    const int blk = (int)(nb < kNumSM * 8 ? nb : kNumSM * 8);
+    if (dtype == PFB_F32)
+        launch(&k_gauss2d<float>, dim3(blk), dim3(256), 0, st, xx, yy, (long)n, a00, a01, a11, c, extent, (float *)out);
+    else if (dtype == PFB_F64)
+        launch(&k_gauss2d<double>, dim3(blk), dim3(256), 0, st, xx, yy, (long)n, a00, a01, a11, c, extent, (double *)out);
+    else
+        return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+int pfb_spec_ratio(const void *num, const void *den, void *out, long long nnum, long long nden, int dtype,
+                   void *stream) {
+    if (!num || !den || !out || nnum < 1 || nden < 0 || nden % nnum)
+        return fail(PFB_ERR_BAD_ARG, "pfb_spec_ratio: bad argument");
+    if (nden == 0) return PFB_OK;
+    cudaStream_t st = as_stream(stream);
+    long nb = (nden + 255) / 256;
+    const int blk = (int)(nb < kNumSM * 8 ? nb : kNumSM * 8);
+    if (dtype == PFB_F32)
+        launch(&k_spec_ratio<float>, dim3(blk), dim3(256), 0, st, (const float *)num, (const float *)den, (float *)out, (long)nnum, (long)nden);
+    else if (dtype == PFB_F64)
+        launch(&k_spec_ratio<double>, dim3(blk), dim3(256), 0, st, (const double *)num, (const double *)den, (double *)out, (long)nnum, (long)nden);
+    else
+        return fail(PFB_ERR_BAD_ARG, "unknown dtype %d", dtype);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
 }
 
 }  // extern "C"

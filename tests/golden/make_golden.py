@@ -431,7 +431,46 @@ def gen_stage():
         save(tag, nds=np.int64(len(dds)), nband=np.int64(nband), **flat, **out)
 
 
-if __name__ == "__main__" and "--stage-only" in sys.argv:
+def gen_restore():
+    """convolve2gaussres, Gaussian2D, get_padding_info (pfb/utils/misc.py:109-138, 170-238): the
+    functions' source text is cut out of misc.py (the module cannot be imported whole) and executed
+    unchanged; r2c / c2r / good_size are the ducc0 stand-ins of oracle/shims.py (scipy.fft)."""
+    from ducc0.fft import r2c, c2r, good_size
+    path = os.path.join(shims.REFERENCE, "pfb", "utils", "misc.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    lines = src.splitlines()
+    ns = {"np": np, "r2c": r2c, "c2r": c2r, "iFs": np.fft.ifftshift, "Fs": np.fft.fftshift,
+          "good_size": lambda n, real=True: good_size(int(n), real)}
+    for name in ("Gaussian2D", "get_padding_info", "convolve2gaussres"):
+        chunk = [("\n".join(lines[n.lineno - 1:n.end_lineno])) for n in tree.body
+                 if isinstance(n, ast.FunctionDef) and n.name == name][0]
+        exec(chunk, ns)
+    conv, gauss, padinfo = ns["convolve2gaussres"], ns["Gaussian2D"], ns["get_padding_info"]
+    rng = np.random.default_rng(429)
+    nband, nx, ny = 3, 64, 48
+    cell = 1.5
+    x = (-(nx // 2) + np.arange(nx)) * cell
+    y = (-(ny // 2) + np.arange(ny)) * cell
+    xx, yy = np.meshgrid(x, y, indexing="ij")
+    image = rng.standard_normal((nband, nx, ny))
+    image[:, nx // 3, ny // 4] += 25.0
+    gaussparf = (9.0, 6.0, 30.0)
+    gausspari = tuple((4.0 + 0.5 * b, 3.0 + 0.25 * b, 10.0 * b) for b in range(nband))
+    padding, ux, uy = padinfo(nx, ny, 0.5)
+    out = dict(image=image, xx=xx, yy=yy, gaussparf=np.array(gaussparf), gausspari=np.array(gausspari),
+               padding=np.array(padding), kern=gauss(xx, yy, gaussparf, normalise=False),
+               kern_norm=gauss(xx, yy, gaussparf, normalise=True))
+    out["conv"] = conv(image.copy(), xx, yy, gaussparf, 1)
+    out["conv_norm"] = conv(image.copy(), xx, yy, gaussparf, 1, norm_kernel=True)
+    out["conv_from"] = conv(image.copy(), xx, yy, gaussparf, 1, gausspari=gausspari)
+    out["conv_p25"] = conv(image.copy(), xx, yy, gaussparf, 1, pfrac=0.25)
+    save("restore_f64", **out)
+
+
+if __name__ == "__main__" and "--restore-only" in sys.argv:
+    gen_restore()
+elif __name__ == "__main__" and "--stage-only" in sys.argv:
     gen_stage()
 elif __name__ == "__main__" and "--clean-only" in sys.argv:
     gen_clean()
@@ -450,3 +489,4 @@ elif __name__ == "__main__":
     gen_glue()
     gen_clean()
     gen_stage()
+    gen_restore()
