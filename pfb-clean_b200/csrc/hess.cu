@@ -274,6 +274,7 @@ struct pfb_hess_plan {
     pfb::PeelDesc prow, pcol;
     int LrowP, inplR;        // rows per CTA of the peeled row passes; lines transformed in place
     void *ptabR, *ptabC;     // ct_fft stage tables of prow.P2 / pcol.P2
+    double *pd_partP;        // partial eps sums of the peeled pass C's primal epilogue (2 per CTA)
 #ifndef PFB_EMU
     CUtensorMap tmS;         // S as (band, k, row) tensor of 8-byte elements, box 2 rows x 256 k (fp32 fast path)
 #endif
@@ -613,13 +614,38 @@ static int peel_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaSt
     h.R = p->LrowP;
     const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R, p->inplR != 0);
     const int nthr = p->inplR ? p->prow.m * (P2 / 16) : peel_threads(p->prow.m, P2, h.R);
-    PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_inv<T, P2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    launch(&k_hessp_rows_inv<T, P2>, dim3(cdiv(h.nx, h.R), h.nband), dim3(nthr), smem, st,
+    PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_inv<T, P2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    launch(&k_hessp_rows_inv<T, P2, false>, dim3(cdiv(h.nx, h.R), h.nband), dim3(nthr), smem, st,
            (const Cx<T> *)p->S, out, (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots,
-           (const Cx<T> *)p->ptabR, p->prow.m, p->inplR, h, ep);
+           (const Cx<T> *)p->ptabR, p->prow.m, p->inplR, h, ep, PeelPrimal());
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
+#ifndef PFB_EMU
+// pass C with the primal step as its epilogue (fp32), then the fixed-order sum of the CTAs' eps terms
+template <int P2>
+static int peel_rows_inv_primal(pfb_hess_plan *p, PrimalArgs pa, double *out2, cudaStream_t st) {
+    HessDims h = p->h;
+    h.R = p->LrowP;
+    const size_t smem = sizeof(Cx<float>) * peel_smem_elems(h.M, p->prow.m, P2, h.R, p->inplR != 0);
+    const int nthr = p->inplR ? p->prow.m * (P2 / 16) : peel_threads(p->prow.m, P2, h.R);
+    const dim3 grid(cdiv(h.nx, h.R), h.nband);
+    pa.part = p->pd_partP;
+    PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_inv<float, P2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    launch(&k_hessp_rows_inv<float, P2, true>, grid, dim3(nthr), smem, st,
+           (const Cx<float> *)p->S, (float *)nullptr, (const Cx<float> *)p->mtwM, (const Cx<float> *)p->twr,
+           (const Cx<float> *)p->mroots, (const Cx<float> *)p->ptabR, p->prow.m, p->inplR, h, Epilogue<float>(), pa);
+    PFB_CHECK_LAUNCH();
+    launch(&k_hess_red_final_wide, dim3(1), dim3(1024), 0, st, (const double *)p->pd_partP, (int)(grid.x * grid.y), out2);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+static int peel_rows_inv_primal_d(pfb_hess_plan *p, const PrimalArgs &pa, double *out2, cudaStream_t st) {
+#define PFB_C(N) peel_rows_inv_primal<N>(p, pa, out2, st)
+    PFB_PEEL_SWITCH(p->prow.P2, PFB_C)
+#undef PFB_C
+}
+#endif
 template <class T, int P2>
 static int peel_cols(pfb_hess_plan *p, cudaStream_t st) {
     const HessDims &h = p->h;
@@ -655,6 +681,42 @@ template <class T> static int peel_cols_d(pfb_hess_plan *p, cudaStream_t st) {
 #undef PFB_C
 }
 
+static inline int mixed_threads(long work) { return work >= 2048 ? 512 : work >= 512 ? 256 : 128; }
+
+// passes A and B of a mixed-radix plan: peeled kernels where a pass's length allows, the run-time
+// radix list otherwise
+template <class T>
+static int mixed_fwd_cols(pfb_hess_plan *p, const T *x, const T *beam_in, cudaStream_t st) {
+    HessDims h = p->h;
+    h.R = p->Lrow;
+    Cx<T> *S = (Cx<T> *)p->S;
+    const size_t cs = sizeof(Cx<T>);
+    const size_t smr = mx_smem_bytes(h.M, h.R, cs), smc = mx_smem_bytes(p->mcol.N, 1, cs);
+    const int tr = mixed_threads((long)h.M * h.R / 4), tc = mixed_threads(p->mcol.N / 4);
+    const dim3 grow(cdiv(h.nx, h.R), h.nband), gcol(h.nyo2, h.nband);
+    if (p->prow.m) {
+        if (int rc = peel_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
+    } else {
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_fwd<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
+        launch(&k_hessm_rows_fwd<T>, grow, dim3(tr), smr, st, x, beam_in, S, (const Cx<T> *)p->mtwM,
+               (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h);
+    }
+    PFB_CHECK_LAUNCH();
+    if (p->pcol.m) {
+        if (int rc = peel_cols_d<T>(p, st)) return rc;
+    } else if (p->split) {
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_cols<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));
+        launch(&k_hessm_cols<T, true>, gcol, dim3(tc), smc, st, S, (const Cx<T> *)p->psfT,
+               (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, p->mcol, h);
+    } else {
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_cols<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));
+        launch(&k_hessm_cols<T, false>, gcol, dim3(tc), smc, st, S, (const Cx<T> *)p->psfT,
+               (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, p->mcol, h);
+    }
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
 template <class T>
 static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T *beam_out,
                         const T *addx, double sigmainv, int has_wsum, double wsum, T *out,
@@ -673,39 +735,17 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
     ep.sigmainv = (T)sigmainv;
     ep.has_wsum = has_wsum;
     if (p->mixed) {
+        if (int rc = mixed_fwd_cols<T>(p, x, beam_in, st)) return rc;
         HessDims h = h0;
         h.R = p->Lrow;
-        const size_t cs = sizeof(Cx<T>);
-        const size_t smr = mx_smem_bytes(h.M, h.R, cs), smc = mx_smem_bytes(p->mcol.N, 1, cs);
-        auto nthr = [](long work) { return work >= 2048 ? 512 : work >= 512 ? 256 : 128; };
-        const int tr = nthr((long)h.M * h.R / 4), tc = nthr(p->mcol.N / 4);
-        const dim3 grow(cdiv(h.nx, h.R), h.nband), gcol(h.nyo2, h.nband);
-        if (p->prow.m) {
-            if (int rc = peel_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
-        } else {
-            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_fwd<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
-            launch(&k_hessm_rows_fwd<T>, grow, dim3(tr), smr, st, x, beam_in, S, (const Cx<T> *)p->mtwM,
-                   (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h);
-        }
-        PFB_CHECK_LAUNCH();
-        if (p->pcol.m) {
-            if (int rc = peel_cols_d<T>(p, st)) return rc;
-        } else if (p->split) {
-            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_cols<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));
-            launch(&k_hessm_cols<T, true>, gcol, dim3(tc), smc, st, S, (const Cx<T> *)p->psfT,
-                   (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, p->mcol, h);
-        } else {
-            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_cols<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));
-            launch(&k_hessm_cols<T, false>, gcol, dim3(tc), smc, st, S, (const Cx<T> *)p->psfT,
-                   (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, p->mcol, h);
-        }
-        PFB_CHECK_LAUNCH();
         if (p->prow.m) {
             if (int rc = peel_rows_inv_d<T>(p, out, ep, st)) return rc;
         } else {
+            const size_t smr = mx_smem_bytes(h.M, h.R, sizeof(Cx<T>));
+            const int tr = mixed_threads((long)h.M * h.R / 4);
             PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_inv<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
-            launch(&k_hessm_rows_inv<T>, grow, dim3(tr), smr, st, (const Cx<T> *)S, out, (const Cx<T> *)p->mtwM,
-                   (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h, ep);
+            launch(&k_hessm_rows_inv<T>, dim3(cdiv(h.nx, h.R), h.nband), dim3(tr), smr, st, (const Cx<T> *)S, out,
+                   (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h, ep);
         }
         PFB_CHECK_LAUNCH();
         return PFB_OK;
@@ -843,6 +883,8 @@ static int hess_plan_create_mixed(pfb_hess_plan **out, int nband, int nx, int ny
             while (p->LrowP > 1 && cs * peel_smem_elems(M, pr.m, pr.P2, p->LrowP, inpl) > kMaxSmemFast) p->LrowP >>= 1;
             p->prow = pr;
             good = good && table(&p->ptabR, pr.P2);
+            if (dtype == PFB_F32)    // eps partials of the fused primal epilogue, 2 per CTA of pass C
+                good = good && cudaMalloc((void **)&p->pd_partP, sizeof(double) * 2 * (size_t)cdiv(nx, p->LrowP) * nband) == cudaSuccess;
         }
         if (peel_make_desc(Nc, pc) && cs * peel_smem_elems(Nc, pc.m, pc.P2, 1) <= kMaxSmemFast) {
             p->pcol = pc;
@@ -1063,6 +1105,7 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
 
 int pfb_hess_plan_destroy(pfb_hess_plan *p) {
     if (!p) return PFB_OK;
+    if (p->pd_partP) cudaFree(p->pd_partP);
     if (p->ptabR) cudaFree(p->ptabR);
     if (p->ptabC) cudaFree(p->ptabC);
     if (p->tabM) cudaFree(p->tabM);
@@ -1134,8 +1177,10 @@ int pfb_hess_plan_kernels(const pfb_hess_plan *p) {
 
 int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *p) {
 #ifndef PFB_EMU
-    if (!p || !p->fast || !p->have_tma || !p->pd_part || p->dtype != PFB_F32 || p->h.nx % 2) return 0;
-    if (getenv("PFB_HESS_NOTMA") || getenv("PFB_HESS_NOPIPE") || getenv("PFB_HESS_NOFUSE")) return 0;
+    if (!p || p->dtype != PFB_F32 || getenv("PFB_HESS_NOFUSE")) return 0;
+    if (p->mixed) return (p->prow.m && p->pd_partP) ? 1 : 0;     // peeled pass C (hess_peel.cuh)
+    if (!p->fast || !p->have_tma || !p->pd_part || p->h.nx % 2) return 0;
+    if (getenv("PFB_HESS_NOTMA") || getenv("PFB_HESS_NOPIPE")) return 0;
     return tma_fits_m(p->h.M) ? 1 : 0;
 #else
     (void)p;
@@ -1156,6 +1201,7 @@ int pfb_hess_apply_primal_begin(pfb_hess_plan *p, const void *xp, void *stream) 
     if (int rc = primal_args_ok(p, "pfb_hess_apply_primal_begin")) return rc;
     if (!xp || ((uintptr_t)xp & 7)) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_begin: bad argument");
     cudaStream_t st = as_stream(stream);
+    if (p->mixed) return mixed_fwd_cols<float>(p, (const float *)xp, nullptr, st);
     if (p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
     if (int rc = fast_rows_fwd_d<float>(p, (const float *)xp, nullptr, st)) return rc;
     return fast_cols_d<float>(p, st);
@@ -1179,6 +1225,7 @@ int pfb_hess_apply_primal_end(pfb_hess_plan *p, const void *xp, const void *w, c
     pa.xp = (const float *)xp; pa.w = (const float *)w; pa.wprev = (const float *)wprev;
     pa.data = (const float *)data; pa.x = (float *)x; pa.tau = (float)tau; pa.positivity = positivity;
     pa.part = nullptr;
+    if (p->mixed) return peel_rows_inv_primal_d(p, pa, out2, as_stream(stream));
     return run_primal_m(p, pa, out2, as_stream(stream));
 #else
     (void)p; (void)xp; (void)w; (void)wprev; (void)data; (void)tau; (void)positivity; (void)x; (void)out2; (void)stream;

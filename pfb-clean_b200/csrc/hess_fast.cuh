@@ -792,6 +792,30 @@ __global__ void k_hess_red_final(const double *__restrict__ part, int n, double 
     }
     if (threadIdx.x == 0) { out2[0] = a0; out2[1] = a1; }
 }
+// the same sum over many CTAs (one per row batch of the peeled pass C): 1024 threads, fixed order
+__global__ void __launch_bounds__(1024)
+k_hess_red_final_wide(const double *__restrict__ part, int n, double *__restrict__ out2) {
+    __shared__ double s_red[2][32];
+    double a0 = 0.0, a1 = 0.0;
+    for (int c = threadIdx.x; c < n; c += 1024) { a0 += part[2 * c]; a1 += part[2 * c + 1]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a0 += __shfl_down_sync(0xffffffffu, a0, o);
+        a1 += __shfl_down_sync(0xffffffffu, a1, o);
+    }
+    const int wid = threadIdx.x >> 5, ln = threadIdx.x & 31;
+    if (ln == 0) { s_red[0][wid] = a0; s_red[1][wid] = a1; }
+    __syncthreads();
+    if (wid == 0) {
+        a0 = s_red[0][ln]; a1 = s_red[1][ln];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a0 += __shfl_down_sync(0xffffffffu, a0, o);
+            a1 += __shfl_down_sync(0xffffffffu, a1, o);
+        }
+        if (ln == 0) { out2[0] = a0; out2[1] = a1; }
+    }
+}
 #endif  // !PFB_EMU
 
 }  // namespace pfb

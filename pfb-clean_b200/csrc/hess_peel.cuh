@@ -387,11 +387,20 @@ k_hessp_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
 // ------------------------------------------------------------------ pass C
 // Mirror of pass A with the epilogue fused.  Every element of the S tile is fetched ONCE into
 // the line's R2 block; X[m] and X[M-m] are then combined pairwise in place.
-template <class T, int P2>
+#ifdef PFB_EMU
+struct PeelPrimal {};                            // the fused primal epilogue is not built for the emulator
+#else
+typedef PrimalArgs PeelPrimal;
+#endif
+// PRIMAL (fp32): the primal step of primal_dual_optimised is the epilogue, as in
+// k_hessf_rows_inv_tma<.., PRIMAL> (same arithmetic and order); pp.part holds 2 partial eps
+// sums per CTA (index blockIdx.y * gridDim.x + blockIdx.x).
+template <class T, int P2, bool PRIMAL>
 __global__ void __launch_bounds__(640)
 k_hessp_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *__restrict__ tw,
                  const Cx<T> *__restrict__ twr, const Cx<T> *__restrict__ roots,
-                 const Cx<T> *__restrict__ tabg, int m, int inpl, HessDims h, Epilogue<T> ep) {
+                 const Cx<T> *__restrict__ tabg, int m, int inpl, HessDims h, Epilogue<T> ep,
+                 PeelPrimal pp) {
     PFB_DYN_SMEM(raw);
     Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
     const int M = h.M, L = h.R;                  // L = 1, 2 or 4
@@ -447,6 +456,77 @@ k_hessp_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *
     }
     __syncthreads();
     peel_inv<T, P2>(R2, R1, L, m, rt + 40, tab, rt, ld1, inpl != 0);
+#ifndef PFB_EMU
+    constexpr bool DO_PRIMAL = PRIMAL && sizeof(T) == 4;
+#else
+    constexpr bool DO_PRIMAL = false;
+#endif
+    if constexpr (DO_PRIMAL) {
+#ifndef PFB_EMU
+        double acc0 = 0.0, acc1 = 0.0;
+        for (int l = 0; l < L; ++l) {
+            const int row = row0 + l;
+            if (row >= h.nx) break;
+            const long ro = ((long)band * h.nx + row) * h.ny;
+            const int npair = (h.ny + 1) / 2 < M ? (h.ny + 1) / 2 : M;
+            float pv[4][2], wv[4][2], qv[4][2], dv[4][2];
+            peel_batched<4>(npair,
+                [&](int u, int mm) {
+#pragma unroll
+                    for (int z = 0; z < 2; ++z) {
+                        const int c = 2 * mm + z;
+                        const bool ok = c < h.ny;
+                        pv[u][z] = ok ? pp.xp[ro + c] : 0.0f;
+                        wv[u][z] = ok ? pp.w[ro + c] : 0.0f;
+                        qv[u][z] = ok ? pp.wprev[ro + c] : 0.0f;
+                        dv[u][z] = ok ? pp.data[ro + c] : 0.0f;
+                    }
+                },
+                [&](int u, int mm) {
+                    const Cx<T> zc = R1[(long)l * ld1 + mm];
+                    const float cv[2] = {(float)zc.x, (float)zc.y};
+#pragma unroll
+                    for (int z = 0; z < 2; ++z) {
+                        const int c = 2 * mm + z;
+                        if (c < h.ny) {
+                            float ge = 2.0f * wv[u][z] - qv[u][z];
+                            const float gr = cv[z] - dv[u][z];
+                            ge = ge + gr;
+                            float xi = pv[u][z] - pp.tau * ge;
+                            if (pp.positivity == 1 && xi < 0.0f) xi = 0.0f;
+                            pp.x[ro + c] = xi;
+                            const float df = xi - pv[u][z];
+                            acc0 += (double)(df * df);
+                            acc1 += (double)(xi * xi);
+                        }
+                    }
+                });
+        }
+        __shared__ double s_red[2][32];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            acc0 += __shfl_down_sync(0xffffffffu, acc0, o);
+            acc1 += __shfl_down_sync(0xffffffffu, acc1, o);
+        }
+        const int wid = threadIdx.x >> 5, ln = threadIdx.x & 31;
+        if (ln == 0) { s_red[0][wid] = acc0; s_red[1][wid] = acc1; }
+        __syncthreads();
+        if (wid == 0) {
+            const int nw = blockDim.x >> 5;
+            double a0 = ln < nw ? s_red[0][ln] : 0.0, a1 = ln < nw ? s_red[1][ln] : 0.0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a0 += __shfl_down_sync(0xffffffffu, a0, o);
+                a1 += __shfl_down_sync(0xffffffffu, a1, o);
+            }
+            if (ln == 0) {
+                const long cta = (long)blockIdx.y * gridDim.x + blockIdx.x;
+                pp.part[2 * cta] = a0;
+                pp.part[2 * cta + 1] = a1;
+            }
+        }
+#endif
+    } else {
     for (int l = 0; l < L; ++l) {
         const int row = row0 + l;
         if (row >= h.nx) break;
@@ -467,6 +547,7 @@ k_hessp_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *
                 }
             }
         }
+    }
     }
 }
 

@@ -506,14 +506,16 @@ def test_pd_tolerance_exit_lagged_check(dtype, monkeypatch):
     assert np.array_equal(res[True][0], res[False][0]) and np.array_equal(res[True][1], res[False][1])
 
 
-def test_fused_primal_pass_matches_unfused(monkeypatch):
-    """pfb_hess_apply_primal (primal step as the epilogue of the TMA pass C) against the
-    separate pfb_hess_apply + pfb_pd_primal_lin kernels: same arithmetic in the same order,
-    so the model is bit-identical; both positivity modes the fused pass takes."""
+@pmp("nx", [1024, 1536])
+def test_fused_primal_pass_matches_unfused(monkeypatch, nx):
+    """pfb_hess_apply_primal (primal step as the epilogue of pass C: the TMA kernel at 1024^2 /
+    2048^2, the peeled kernel of hess_peel.cuh at 1536^2 / 3072^2, lines of 3 x 512 points)
+    against the separate pfb_hess_apply + pfb_pd_primal_lin kernels: same arithmetic in
+    the same order, so the model is bit-identical; both positivity modes the fused pass takes."""
     from pfb_b200.operators.psf import psf_convolve_cube
     from pfb_b200.operators.psi import Psi
     from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
-    nband, nx = 2, 1024
+    nband = 2
     psfhat, dirty, _, _ = _problem(nband, nx, np.float32)
     dev = torch.device("cuda")
     psfd, dd = torch.from_numpy(psfhat).to(dev), torch.from_numpy(dirty).to(dev)
