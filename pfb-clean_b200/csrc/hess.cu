@@ -222,7 +222,7 @@ k_psfm_cols_fwd(Cx<T> *S, const Cx<T> *__restrict__ tw, const Cx<T> *__restrict_
 // psfhat (nband, nxp, nyo2) -> psfT (nband, nyo2, nxp) * scale
 template <class T>
 __global__ void k_psfhat_prepare(const Cx<T> *__restrict__ in, Cx<T> *__restrict__ out,
-                                 int nxp, int nyo2, T scale, int deint) {
+                                 int nxp, int nyo2, T scale, int deint, int pm, int pP2) {
     __shared__ Cx<T> tile[32][33];
     int band = blockIdx.z;
     const Cx<T> *src = in + (long)band * nxp * nyo2;
@@ -239,6 +239,10 @@ __global__ void k_psfhat_prepare(const Cx<T> *__restrict__ in, Cx<T> *__restrict
             Cx<T> v = tile[threadIdx.x][i];
             // fast path: rows de-interleaved per column, [even rows | odd rows]
             int rr = deint ? ((r & 1) * (nxp >> 1) + (r >> 1)) : r;
+            if (pm) {    // k_hessp_cols2: element K of a (half) spectrum at [K mod m][K / m]
+                const int N = pm * pP2, hf = rr / N, K = rr - hf * N;
+                rr = hf * N + (K % pm) * pP2 + K / pm;
+            }
             dst[(long)c * nxp + rr] = cx<T>(v.x * scale, v.y * scale);
         }
     }
@@ -275,6 +279,7 @@ struct pfb_hess_plan {
     int LrowP, inplR;        // rows per CTA of the peeled row passes; lines transformed in place
     void *ptabR, *ptabC;     // ct_fft stage tables of prow.P2 / pcol.P2
     double *pd_partP;        // partial eps sums of the peeled pass C's primal epilogue (2 per CTA)
+    int pcol2;               // column pass on k_hessp_cols2 (psfT stored permuted [q][k] per half)
 #ifndef PFB_EMU
     CUtensorMap tmS;         // S as (band, k, row) tensor of 8-byte elements, box 2 rows x 256 k (fp32 fast path)
 #endif
@@ -316,7 +321,7 @@ static int hess_set_psf_t(pfb_hess_plan *p, const void *psfhat, cudaStream_t st)
         }
     }
     launch(&k_psfhat_prepare<T>, grid, block, 0, st, (const Cx<T> *)psfhat, (Cx<T> *)p->psfT,
-           h.nxp, h.nyo2, scale, p->deint);
+           h.nxp, h.nyo2, scale, p->deint, p->pcol2 ? p->pcol.m : 0, p->pcol.P2);
     PFB_CHECK_LAUNCH();
     p->have_psf = 1;
     return PFB_OK;
@@ -649,6 +654,23 @@ static int peel_rows_inv_primal_d(pfb_hess_plan *p, const PrimalArgs &pa, double
 template <class T, int P2>
 static int peel_cols(pfb_hess_plan *p, cudaStream_t st) {
     const HessDims &h = p->h;
+    if (p->pcol2) {
+        const size_t smem2 = sizeof(Cx<T>) * peel_smem_elems_cols2(p->pcol.N, p->pcol.m, P2, p->split != 0);
+        const dim3 grid2(h.nyo2, h.nband), blk2(p->pcol.m * (P2 / 16));
+        if (p->split) {
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_cols2<T, P2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+            launch(&k_hessp_cols2<T, P2, true>, grid2, blk2, smem2, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
+                   (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, (const Cx<T> *)p->ptabC,
+                   p->pcol.m, h);
+        } else {
+            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_cols2<T, P2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+            launch(&k_hessp_cols2<T, P2, false>, grid2, blk2, smem2, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
+                   (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, (const Cx<T> *)p->ptabC,
+                   p->pcol.m, h);
+        }
+        PFB_CHECK_LAUNCH();
+        return PFB_OK;
+    }
     const size_t smem = sizeof(Cx<T>) * peel_smem_elems(p->pcol.N, p->pcol.m, P2, 1);
     const dim3 grid(h.nyo2, h.nband), blk(peel_threads(p->pcol.m, P2, 1));
     if (p->split) {
@@ -886,8 +908,11 @@ static int hess_plan_create_mixed(pfb_hess_plan **out, int nband, int nx, int ny
             if (dtype == PFB_F32)    // eps partials of the fused primal epilogue, 2 per CTA of pass C
                 good = good && cudaMalloc((void **)&p->pd_partP, sizeof(double) * 2 * (size_t)cdiv(nx, p->LrowP) * nband) == cudaSuccess;
         }
-        if (peel_make_desc(Nc, pc) && cs * peel_smem_elems(Nc, pc.m, pc.P2, 1) <= kMaxSmemFast) {
+        const bool c2 = peel_make_desc(Nc, pc) && peel_can_inplace(pc.m, pc.P2) && !getenv("PFB_HESS_PEEL_COLS1") &&
+                        cs * peel_smem_elems_cols2(Nc, pc.m, pc.P2, split) <= kMaxSmemFast;
+        if (pc.m && (c2 || cs * peel_smem_elems(Nc, pc.m, pc.P2, 1) <= kMaxSmemFast)) {
             p->pcol = pc;
+            p->pcol2 = c2 ? 1 : 0;
             good = good && table(&p->ptabC, pc.P2);
         }
     }
@@ -939,7 +964,7 @@ static int psfhat_from_psf_t(pfb_hess_plan *p, const T *psf, Cx<T> *out, cudaStr
     }
     // S (nband, nyo2, nxp) -> psfhat (nband, nxp, nyo2): the transposing kernel with the roles swapped
     dim3 grid(cdiv(h0.nxp, 32), cdiv(h0.nyo2, 32), h0.nband), block(32, 8);
-    launch(&k_psfhat_prepare<T>, grid, block, 0, st, (const Cx<T> *)S, out, h0.nyo2, h0.nxp, (T)1, 0);
+    launch(&k_psfhat_prepare<T>, grid, block, 0, st, (const Cx<T> *)S, out, h0.nyo2, h0.nxp, (T)1, 0, 0, 0);
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }

@@ -23,6 +23,7 @@
 // even / odd split of the column pass as hess_mixed.cuh.
 #pragma once
 #include "hess_mixed.cuh"
+#include <type_traits>
 
 namespace pfb {
 
@@ -60,6 +61,10 @@ template <int P2> __host__ __device__ constexpr int peel_nbar() {
 // inpl (row passes): no R1, the natural-order line lives in its own R2 block
 static inline size_t peel_smem_elems(int N, int m, int P2, int L, bool inpl = false) {
     return (size_t)kMxHead + ct_tab_size(P2) + 4 + (inpl ? 0 : (size_t)L * N) + (size_t)L * m * ct_stride(P2);
+}
+// second form of the column pass: segments (+ the parked even half when split)
+static inline size_t peel_smem_elems_cols2(int N, int m, int P2, bool split) {
+    return (size_t)kMxHead + ct_tab_size(P2) + 4 + (size_t)m * ct_stride(P2) + (split ? (size_t)N : 0);
 }
 // in-place row passes need exactly one thread group per segment
 static inline bool peel_can_inplace(int m, int P2) { return m * (P2 / 16) <= 640; }
@@ -381,6 +386,124 @@ k_hessp_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
         peel_batched<U2>(h.nx,
             [&](int u, int n) { v[u] = line[n]; g[u] = modg[n]; },
             [&](int u, int n) { line[n] = v[u] + cmul(R1[n], cconj(g[u])); });
+    }
+}
+
+// ------------------------------------------------------------------ pass B, second form
+// Decimation in frequency on the way in, in time on the way out (n = j + P2 s, K = m k + q):
+//     X[m k + q] = FFT_P2( b_q )[k],   b_q[j] = w_N^(j q) sum_s w_m^(s q) a[j + P2 s]
+//     y[j + P2 s] = sum_q w_m^(-s q) w_N^(-j q) IFFT_P2( Y[m . + q] )[j]
+// The m-point butterflies now sit at the GLOBAL-memory ends of the pipeline: a butterfly thread
+// loads a[j + P2 s] straight from the S line (coalesced over j) and stores y[j + P2 s] straight
+// back, so no natural-order staging line exists; a sub-transform's forward output is, element
+// for element, the inverse sub-transform's input, so the PSF product (psfT stored permuted,
+// [q][k], by k_psfhat_prepare) and the turn-around happen in registers like in the
+// power-of-two kernel.  12 shared-memory accesses per point and half instead of 16, three
+// block-wide barriers per half instead of seven.  Needs one thread group per segment
+// (peel_can_inplace).  SPLIT: the even half's result waits in a shared-memory line (PARK).
+template <class T, int P2, bool SPLIT>
+__global__ void __launch_bounds__(640)
+k_hessp_cols2(Cx<T> *S, const Cx<T> *__restrict__ psfP, const Cx<T> *__restrict__ tw,
+              const Cx<T> *__restrict__ modg, const Cx<T> *__restrict__ roots,
+              const Cx<T> *__restrict__ tabg, int m, HessDims h) {
+    PFB_DYN_SMEM(raw);
+    Cx<T> *rt = reinterpret_cast<Cx<T> *>(raw);
+    constexpr int NT = P2 / 16, cts = ct_stride(P2);
+    const int N = m * P2;
+    Cx<T> *tab = rt + kMxHead;
+    Cx<T> *SEG = tab + ct_tab_size(P2) + 4, *PARK = SEG + (long)m * cts;
+    const int band = blockIdx.y, col = blockIdx.x;
+    Cx<T> *line = S + ((long)band * h.nyo2 + col) * h.nx;
+    const Cx<T> *pl = psfP + ((long)band * h.nyo2 + col) * h.nxp;
+    peel_load_tables<T, P2>(rt, roots, tw, tabg, N);
+    const Cx<T> *tws = rt + 40;
+    const int g = threadIdx.x / NT, t = threadIdx.x - g * NT;      // group g = segment q
+    const GroupBar bar{1 + g, NT};
+    __syncthreads();
+#pragma unroll 1
+    for (int half = 0; half < (SPLIT ? 2 : 1); ++half) {
+        const Cx<T> *ph = pl + (long)half * N;
+        {   // this half's PSF values: DRAM -> L2 now, read after the forward sub-transform
+            constexpr int PL = 128 / (int)sizeof(Cx<T>);
+            for (int i = threadIdx.x * PL; i < N; i += (int)blockDim.x * PL) prefetch_l2(ph + i);
+        }
+        // ---- in: m-point butterflies on a[j + P2 s] (x w_2N^n for the odd half), twiddle, -> SEG
+        auto fwd_bfly = [&](auto tag) {
+            constexpr int R = decltype(tag)::value;
+            for (int j = threadIdx.x; j < P2; j += blockDim.x) {
+                Cx<T> u[R];
+#pragma unroll
+                for (int s = 0; s < R; ++s) {
+                    const int n = j + s * P2;
+                    u[s] = n < h.nx ? line[n] : cx<T>((T)0, (T)0);
+                }
+                if (SPLIT && half == 1) {
+#pragma unroll
+                    for (int s = 0; s < R; ++s) {
+                        const int n = j + s * P2;
+                        if (n < h.nx) u[s] = cmul(u[s], modg[n]);
+                    }
+                }
+                MxDft<T, R, -1>::run(u, rt);
+#pragma unroll
+                for (int q = 1; q < R; ++q) u[q] = cmul(u[q], mx_twiddle(tws, q * j));
+#pragma unroll
+                for (int q = 0; q < R; ++q) SEG[q * cts + j] = u[q];
+            }
+        };
+        if (m == 3) fwd_bfly(std::integral_constant<int, 3>());
+        else if (m == 5) fwd_bfly(std::integral_constant<int, 5>());
+        else fwd_bfly(std::integral_constant<int, 7>());
+        __syncthreads();
+        // ---- sub-transform q forward, x PSF, inverse: all in registers
+        {
+            Cx<T> *X = SEG + (long)g * cts;
+            Cx<T> v[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = X[t + e * NT];
+            ct_fft<T, P2, -1>(v, t, X, tab, bar);
+            const Cx<T> *pq = ph + (long)g * P2;
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = cmul(v[e], pq[t + e * NT]);
+            ct_fft<T, P2, +1>(v, t, X, tab, bar);
+            bar();                                // the last exchange of X has been read
+#pragma unroll
+            for (int e = 0; e < 16; ++e) X[t + e * NT] = v[e];
+        }
+        __syncthreads();
+        // ---- out: conjugate twiddle, inverse m-point butterflies, y[j + P2 s] -> PARK / line
+        auto inv_bfly = [&](auto tag) {
+            constexpr int R = decltype(tag)::value;
+            for (int j = threadIdx.x; j < P2; j += blockDim.x) {
+                Cx<T> u[R];
+#pragma unroll
+                for (int q = 0; q < R; ++q) u[q] = SEG[q * cts + j];
+#pragma unroll
+                for (int q = 1; q < R; ++q) u[q] = cmul(u[q], cconj(mx_twiddle(tws, q * j)));
+                MxDft<T, R, +1>::run(u, rt);
+                if (SPLIT && half == 0) {
+#pragma unroll
+                    for (int s = 0; s < R; ++s) PARK[j + s * P2] = u[s];
+                } else if (SPLIT) {
+#pragma unroll
+                    for (int s = 0; s < R; ++s) {
+                        const int n = j + s * P2;
+                        if (n < h.nx) line[n] = PARK[n] + cmul(u[s], cconj(modg[n]));
+                    }
+                } else {
+#pragma unroll
+                    for (int s = 0; s < R; ++s) {
+                        const int n = j + s * P2;
+                        if (n < h.nx) line[n] = u[s];
+                    }
+                }
+            }
+        };
+        if (m == 3) inv_bfly(std::integral_constant<int, 3>());
+        else if (m == 5) inv_bfly(std::integral_constant<int, 5>());
+        else inv_bfly(std::integral_constant<int, 7>());
+        // no barrier: the next half's butterflies touch SEG[.][j], PARK[j + P2 s] and line[j + P2 s]
+        // of the SAME j in the same thread
     }
 }
 

@@ -141,6 +141,11 @@ def test_hess_peel_two_buffer_rows(monkeypatch):
     for dtype in (np.float32, np.float64):
         test_hess_mixed_radix_oracle(dtype, 6, 1500, 12, 3072)
         test_hess_mixed_radix_oracle(dtype, 5, 2500, 10, 5120)
+    # first form of the peeled column pass (natural-order staging line), split and full
+    monkeypatch.setenv("PFB_HESS_PEEL_COLS1", "1")
+    for dtype in (np.float32, np.float64):
+        test_hess_mixed_radix_oracle(dtype, 1500, 6, 3072, 12)
+        test_hess_mixed_radix_oracle(dtype, 2000, 6, 3072, 12)
 
 
 def test_hess_plan_errors():
