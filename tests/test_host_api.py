@@ -158,7 +158,7 @@ def test_solvers_api(backend, tag):
     # opt-in: dual update in the epilogue of the analysis kernels (pfb_psi_dot_nat_dual)
     os.environ["PFB_PD_FUSEDUAL"] = "1"
     try:
-        for pos in (1, 2):
+        for pos in (1,):                  # the dual half does not depend on the positivity mode
             x = np.zeros(dirty.shape, dt)
             v = np.zeros((nband, nbasis, psi.Nymax, psi.Nxmax), dt)
             primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, hessnorm, None, np.ones(v.shape[1:], dt),
