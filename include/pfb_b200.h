@@ -287,8 +287,10 @@ int pfb_hess_plan_kernels(const pfb_hess_plan *plan);
  *   x = P+( xp - tau * (2 w - wprev + psf_convolve(xp) - data) ),  out2 as pfb_norm_diff
  * (positivity 0 or 1; w, wprev = Psi(v) of this and the previous iteration, see
  * pfb_pd_primal_lin).  The convolution result is never written.  Available when
- * pfb_hess_plan_can_fuse_primal() is 1: fp32 power-of-two fast path whose pass C
- * gathers through the TMA unit; otherwise use pfb_hess_apply + pfb_pd_primal_lin. */
+ * pfb_hess_plan_can_fuse_primal() is 1: the power-of-two fast paths (fp32 and fp64; every pass C
+ * kernel of hess_fast.cuh takes the epilogue) and fp32 plans whose rows are (3|5|7) x 2^k points
+ * (hess_peel.cuh); otherwise use pfb_hess_apply + pfb_pd_primal_lin.  ny even, arrays aligned to
+ * two elements. */
 int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *plan);
 int pfb_hess_apply_primal(pfb_hess_plan *plan, const void *xp, const void *w, const void *wprev,
                           const void *data, double tau, int positivity, void *x, double *out2,

@@ -364,17 +364,30 @@ static int fast_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream
     return fast_rows_fwd_k<T, M, RB, false>(p, x, beam, st, smem);
 }
 
+// eps terms of a fused primal pass: fixed-order sum of the CTAs' partials
+static int primal_finish(pfb_hess_plan *p, int grid, double *out2, cudaStream_t st) {
+    launch(&k_hess_red_final, dim3(1), dim3(32), 0, st, (const double *)p->pd_part, grid, out2);
+    PFB_CHECK_LAUNCH();
+    return PFB_OK;
+}
+
+// pa != nullptr: the primal step is the epilogue (PrimalArgsT), eps terms -> out2
 template <class T, int M, bool TWS>
-static int fast_rows_inv2(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st, size_t smem) {
+static int fast_rows_inv2(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st, size_t smem,
+                          const PrimalArgsT<T> *pa = nullptr, double *out2 = nullptr) {
     const HessDims &h = p->h;
-    auto kern = p->dyn ? &k_hessf_rows_inv2<T, M, TWS, true> : &k_hessf_rows_inv2<T, M, TWS, false>;
+    auto kern = pa ? (p->dyn ? &k_hessf_rows_inv2<T, M, TWS, true, true> : &k_hessf_rows_inv2<T, M, TWS, false, true>)
+                   : (p->dyn ? &k_hessf_rows_inv2<T, M, TWS, true, false> : &k_hessf_rows_inv2<T, M, TWS, false, false>);
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int nbb = cdiv(h.nx, 4);
     int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
+    if (grid > 4 * p->nsm) grid = 4 * p->nsm;      // size of pd_part
+    PrimalArgsT<T> a = pa ? *pa : PrimalArgsT<T>();
+    a.part = p->pd_part;
     launch(kern, dim3(grid), dim3(M / 8), smem, st, (const Cx<T> *)p->S, out, (const Cx<T> *)p->tabM,
-           (const Cx<T> *)p->twr, h, nbb, ep, p->ctr + 2);
+           (const Cx<T> *)p->twr, h, nbb, ep, p->ctr + 2, a);
     PFB_CHECK_LAUNCH();
-    return PFB_OK;
+    return pa ? primal_finish(p, grid, out2, st) : PFB_OK;
 }
 
 #ifndef PFB_EMU
@@ -439,51 +452,41 @@ template <int M> struct RowsInvTma<float, M> {
     }
 };
 
-// M-dispatch of the fused pass C (fp32 only)
-static bool tma_fits_m(int M) {
-    switch (M) {
-    case 512: return RowsInvTma<float, 512>::fits();
-    case 1024: return RowsInvTma<float, 1024>::fits();
-    case 2048: return RowsInvTma<float, 2048>::fits();
-    case 4096: return RowsInvTma<float, 4096>::fits();
-    default: return false;
-    }
-}
-static int run_primal_m(pfb_hess_plan *p, const PrimalArgs &pa, double *out2, cudaStream_t st) {
-    switch (p->h.M) {
-    case 512: return RowsInvTma<float, 512>::run_primal(p, pa, out2, st);
-    case 1024: return RowsInvTma<float, 1024>::run_primal(p, pa, out2, st);
-    case 2048: return RowsInvTma<float, 2048>::run_primal(p, pa, out2, st);
-    case 4096: return RowsInvTma<float, 4096>::run_primal(p, pa, out2, st);
-    default: return fail(PFB_ERR_FFT_SIZE, "fused primal pass: unsupported length %d", p->h.M);
-    }
-}
 #endif
 
 template <class T, int M, int RB>
-static int fast_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
+static int fast_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st,
+                         const PrimalArgsT<T> *pa = nullptr, double *out2 = nullptr) {
     const HessDims &h = p->h;
 #ifndef PFB_EMU
     if (p->have_tma && h.nx % 2 == 0 && RowsInvTma<T, M>::fits() && !getenv("PFB_HESS_NOTMA") &&
-        !getenv("PFB_HESS_NOPIPE"))
+        !getenv("PFB_HESS_NOPIPE")) {
+        if constexpr (sizeof(T) == 4) {
+            if (pa) return RowsInvTma<T, M>::run_primal(p, *pa, out2, st);
+        }
         return RowsInvTma<T, M>::run(p, out, ep, st);
+    }
 #endif
     // pipelined kernel (four lines: gather of the next row pair under the transforms) when it fits
     const size_t smem4 = sizeof(Cx<T>) * ((size_t)4 * ct_stride(M) + ct_tab_size(M));
     if (!getenv("PFB_HESS_NOPIPE") && h.nx % 2 == 0) {
         if (smem4 + sizeof(Cx<T>) * M <= kMaxSmemFast)
-            return fast_rows_inv2<T, M, true>(p, out, ep, st, smem4 + sizeof(Cx<T>) * M);
-        if (smem4 <= kMaxSmemFast) return fast_rows_inv2<T, M, false>(p, out, ep, st, smem4);
+            return fast_rows_inv2<T, M, true>(p, out, ep, st, smem4 + sizeof(Cx<T>) * M, pa, out2);
+        if (smem4 <= kMaxSmemFast) return fast_rows_inv2<T, M, false>(p, out, ep, st, smem4, pa, out2);
     }
     size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
-    auto kern = p->dyn ? &k_hessf_rows_inv<T, M, RB, true> : &k_hessf_rows_inv<T, M, RB, false>;
+    auto kern = pa ? (p->dyn ? &k_hessf_rows_inv<T, M, RB, true, 2, true> : &k_hessf_rows_inv<T, M, RB, false, 2, true>)
+                   : (p->dyn ? &k_hessf_rows_inv<T, M, RB, true, 2, false> : &k_hessf_rows_inv<T, M, RB, false, 2, false>);
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int nbb = cdiv(h.nx, RB);
     int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
+    if (grid > 4 * p->nsm) grid = 4 * p->nsm;      // size of pd_part
+    PrimalArgsT<T> a = pa ? *pa : PrimalArgsT<T>();
+    a.part = p->pd_part;
     launch(kern, dim3(grid), dim3(M / 8), smem, st, (const Cx<T> *)p->S, out, (const Cx<T> *)p->tabM,
-           (const Cx<T> *)p->twr, h, nbb, ep, p->ctr + 2);
+           (const Cx<T> *)p->twr, h, nbb, ep, p->ctr + 2, a);
     PFB_CHECK_LAUNCH();
-    return PFB_OK;
+    return pa ? primal_finish(p, grid, out2, st) : PFB_OK;
 }
 
 template <class T, int H>
@@ -542,18 +545,23 @@ static int fast_rows_fwd_8k(pfb_hess_plan *p, const float *x, const float *beam,
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
-static int fast_rows_inv_8k(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st) {
+static int fast_rows_inv_8k(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st,
+                            const PrimalArgsT<float> *pa = nullptr, double *out2 = nullptr) {
     constexpr int M = 8192, RB = 2;
     const HessDims &h = p->h;
     const size_t smem = sizeof(Cx<float>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
-    auto kern = p->dyn ? &k_hessf_rows_inv<float, M, RB, true, 1> : &k_hessf_rows_inv<float, M, RB, false, 1>;
+    auto kern = pa ? (p->dyn ? &k_hessf_rows_inv<float, M, RB, true, 1, true> : &k_hessf_rows_inv<float, M, RB, false, 1, true>)
+                   : (p->dyn ? &k_hessf_rows_inv<float, M, RB, true, 1, false> : &k_hessf_rows_inv<float, M, RB, false, 1, false>);
     PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int nbb = cdiv(h.nx, RB);
     int grid = persistent_grid((const void *)kern, M / 16, smem, nbb * h.nband, p->nsm);
+    if (grid > 4 * p->nsm) grid = 4 * p->nsm;      // size of pd_part
+    PrimalArgsT<float> a = pa ? *pa : PrimalArgsT<float>();
+    a.part = p->pd_part;
     launch(kern, dim3(grid), dim3(M / 16), smem, st, (const Cx<float> *)p->S, out, (const Cx<float> *)p->tabM,
-           (const Cx<float> *)p->twr, h, nbb, ep, p->ctr + 2);
+           (const Cx<float> *)p->twr, h, nbb, ep, p->ctr + 2, a);
     PFB_CHECK_LAUNCH();
-    return PFB_OK;
+    return pa ? primal_finish(p, grid, out2, st) : PFB_OK;
 }
 
 #define PFB_SIZE_SWITCH(n, CALL)                         \
@@ -575,13 +583,14 @@ template <class T> static int fast_rows_fwd_d(pfb_hess_plan *p, const T *x, cons
     PFB_SIZE_SWITCH(p->h.M, PFB_C)
 #undef PFB_C
 }
-template <class T> static int fast_rows_inv_d(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
+template <class T> static int fast_rows_inv_d(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st,
+                                              const PrimalArgsT<T> *pa = nullptr, double *out2 = nullptr) {
     if (p->RB == 4) {
-#define PFB_C(N) fast_rows_inv<T, N, 4>(p, out, ep, st)
+#define PFB_C(N) fast_rows_inv<T, N, 4>(p, out, ep, st, pa, out2)
         PFB_SIZE_SWITCH(p->h.M, PFB_C)
 #undef PFB_C
     }
-#define PFB_C(N) fast_rows_inv<T, N, 2>(p, out, ep, st)
+#define PFB_C(N) fast_rows_inv<T, N, 2>(p, out, ep, st, pa, out2)
     PFB_SIZE_SWITCH(p->h.M, PFB_C)
 #undef PFB_C
 }
@@ -739,42 +748,19 @@ static int mixed_fwd_cols(pfb_hess_plan *p, const T *x, const T *beam_in, cudaSt
     return PFB_OK;
 }
 
+// Passes A and B (everything that needs x only).  `alt` = every other array the row passes will
+// touch with 2-element vector accesses (their alignment decides between the fast and the generic
+// row kernels, and both row passes must take the same decision).
 template <class T>
-static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T *beam_out,
-                        const T *addx, double sigmainv, int has_wsum, double wsum, T *out,
-                        cudaStream_t st) {
+static int hess_fwd_cols_t(pfb_hess_plan *p, const T *x, const T *beam_in, uintptr_t alt, cudaStream_t st) {
     const HessDims &h0 = p->h;
     const Cx<T> *tw = (const Cx<T> *)p->tw;
     Cx<T> *S = (Cx<T> *)p->S;
-    // the fast row passes use 2-element vector accesses on x / out / beam
+    if (p->mixed) return mixed_fwd_cols<T>(p, x, beam_in, st);
     const uintptr_t al = 2 * sizeof(T) - 1;
-    const bool fast_rows = p->fast && !(((uintptr_t)x | (uintptr_t)out | (uintptr_t)beam_in |
-                                         (uintptr_t)beam_out | (uintptr_t)addx) & al);
-    Epilogue<T> ep;
-    ep.beam = beam_out;
-    ep.x = addx;
-    ep.wsum = (T)wsum;
-    ep.sigmainv = (T)sigmainv;
-    ep.has_wsum = has_wsum;
-    if (p->mixed) {
-        if (int rc = mixed_fwd_cols<T>(p, x, beam_in, st)) return rc;
-        HessDims h = h0;
-        h.R = p->Lrow;
-        if (p->prow.m) {
-            if (int rc = peel_rows_inv_d<T>(p, out, ep, st)) return rc;
-        } else {
-            const size_t smr = mx_smem_bytes(h.M, h.R, sizeof(Cx<T>));
-            const int tr = mixed_threads((long)h.M * h.R / 4);
-            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_inv<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
-            launch(&k_hessm_rows_inv<T>, dim3(cdiv(h.nx, h.R), h.nband), dim3(tr), smr, st, (const Cx<T> *)S, out,
-                   (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h, ep);
-        }
-        PFB_CHECK_LAUNCH();
-        return PFB_OK;
-    }
-    const bool rows8k = p->fastrows && sizeof(T) == 4 &&
-                        !(((uintptr_t)x | (uintptr_t)out | (uintptr_t)beam_in | (uintptr_t)beam_out |
-                           (uintptr_t)addx) & al);
+    const bool aligned = !(((uintptr_t)x | (uintptr_t)beam_in | alt) & al);
+    const bool fast_rows = p->fast && aligned;
+    const bool rows8k = p->fastrows && sizeof(T) == 4 && aligned;
     if ((p->fast || p->fastcols || p->fastrows) && p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
     if (fast_rows) {
         if (int rc = fast_rows_fwd_d<T>(p, x, beam_in, st)) return rc;
@@ -804,21 +790,77 @@ static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T 
         PFB_BY_THREADS(nthr, k_hess_cols, smem, dim3(cdiv(h.nyo2, h.R), h.nband), st,
                        S, (const Cx<T> *)p->psfT, tw, p->dcol, h);
     }
-    if (fast_rows) {
-        if (int rc = fast_rows_inv_d<T>(p, out, ep, st)) return rc;
-    } else if (rows8k) {
-        if constexpr (sizeof(T) == 4) {
-            if (int rc = fast_rows_inv_8k(p, out, ep, st)) return rc;
-        }
-    } else {
-        HessDims h = h0;
-        h.R = p->Rrow;
-        size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.M) * h.R;
-        int nthr = p->drow.NT * h.R;
-        PFB_BY_THREADS(nthr, k_hess_rows_inv, smem, dim3(cdiv(h.nx, h.R), h.nband), st,
-                       (const Cx<T> *)S, out, tw, p->drow, h, ep);
-    }
     return PFB_OK;
+}
+
+// Pass C.  pa != nullptr: the primal step is its epilogue (only where hess_can_fuse says so).
+template <class T>
+static int hess_rows_inv_t(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, bool aligned, cudaStream_t st,
+                           const PrimalArgsT<T> *pa = nullptr, double *out2 = nullptr) {
+    const HessDims &h0 = p->h;
+    const Cx<T> *tw = (const Cx<T> *)p->tw;
+    Cx<T> *S = (Cx<T> *)p->S;
+    if (p->mixed) {
+        HessDims h = h0;
+        h.R = p->Lrow;
+        if (p->prow.m) {
+#ifndef PFB_EMU
+            if constexpr (sizeof(T) == 4) {
+                if (pa) return peel_rows_inv_primal_d(p, *pa, out2, st);
+            }
+#endif
+            if (pa) return fail(PFB_ERR_BAD_ARG, "fused primal pass: not available for this plan");
+            return peel_rows_inv_d<T>(p, out, ep, st);
+        }
+        if (pa) return fail(PFB_ERR_BAD_ARG, "fused primal pass: not available for this plan");
+        const size_t smr = mx_smem_bytes(h.M, h.R, sizeof(Cx<T>));
+        const int tr = mixed_threads((long)h.M * h.R / 4);
+        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessm_rows_inv<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smr));
+        launch(&k_hessm_rows_inv<T>, dim3(cdiv(h.nx, h.R), h.nband), dim3(tr), smr, st, (const Cx<T> *)S, out,
+               (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots, p->mrow, h, ep);
+        PFB_CHECK_LAUNCH();
+        return PFB_OK;
+    }
+    if (p->fast && aligned) return fast_rows_inv_d<T>(p, out, ep, st, pa, out2);
+    if (p->fastrows && sizeof(T) == 4 && aligned) {
+        if constexpr (sizeof(T) == 4) return fast_rows_inv_8k(p, out, ep, st, pa, out2);
+    }
+    if (pa) return fail(PFB_ERR_BAD_ARG, "fused primal pass: not available for this plan");
+    HessDims h = h0;
+    h.R = p->Rrow;
+    size_t smem = sizeof(Cx<T>) * (size_t)fft_smem_elems(h.M) * h.R;
+    int nthr = p->drow.NT * h.R;
+    PFB_BY_THREADS(nthr, k_hess_rows_inv, smem, dim3(cdiv(h.nx, h.R), h.nband), st,
+                   (const Cx<T> *)S, out, tw, p->drow, h, ep);
+    return PFB_OK;
+}
+
+template <class T>
+static int hess_apply_t(pfb_hess_plan *p, const T *x, const T *beam_in, const T *beam_out,
+                        const T *addx, double sigmainv, int has_wsum, double wsum, T *out,
+                        cudaStream_t st) {
+    // the fast row passes use 2-element vector accesses on x / out / beam
+    const uintptr_t al = 2 * sizeof(T) - 1;
+    const uintptr_t alt = (uintptr_t)out | (uintptr_t)beam_out | (uintptr_t)addx;
+    const bool aligned = !(((uintptr_t)x | (uintptr_t)beam_in | alt) & al);
+    Epilogue<T> ep;
+    ep.beam = beam_out;
+    ep.x = addx;
+    ep.wsum = (T)wsum;
+    ep.sigmainv = (T)sigmainv;
+    ep.has_wsum = has_wsum;
+    if (int rc = hess_fwd_cols_t<T>(p, x, beam_in, alt, st)) return rc;
+    return hess_rows_inv_t<T>(p, out, ep, aligned, st);
+}
+
+template <class T>
+static int primal_end_t(pfb_hess_plan *p, const void *xp, const void *w, const void *wprev, const void *data,
+                        double tau, int positivity, void *x, double *out2, cudaStream_t st) {
+    PrimalArgsT<T> pa;
+    pa.xp = (const T *)xp; pa.w = (const T *)w; pa.wprev = (const T *)wprev;
+    pa.data = (const T *)data; pa.x = (T *)x; pa.tau = (T)tau; pa.positivity = positivity;
+    pa.part = nullptr;
+    return hess_rows_inv_t<T>(p, (T *)nullptr, Epilogue<T>(), true, st, &pa, out2);
 }
 
 // lines per CTA: fill up to 1024 threads / kMaxSmem, capped at `want`
@@ -1114,11 +1156,13 @@ int pfb_hess_plan_create(pfb_hess_plan **out, int nband, int nx, int ny, int nxp
         p->fastrows = fastrows ? 1 : 0;
 #ifndef PFB_EMU
         p->have_tma = (fast && dtype == PFB_F32 && nx % 2 == 0 && make_tma_S(p)) ? 1 : 0;
-        if (p->have_tma && cudaMalloc((void **)&p->pd_part, sizeof(double) * 2 * 4 * p->nsm) != cudaSuccess) {
+#endif
+        // eps partials of the fused primal epilogue (every fast pass C kernel takes it)
+        if ((p->fast || p->fastrows) &&
+            cudaMalloc((void **)&p->pd_part, sizeof(double) * 2 * 4 * p->nsm) != cudaSuccess) {
             cudaGetLastError();
             p->pd_part = nullptr;
         }
-#endif
         // Dynamic distribution costs ~5 % when the GPU is otherwise idle (measured on the
         // column pass) and wins when a concurrent kernel holds SMs (NCCL all-reduce of
         // the band-sharded solver): off by default, the sharded solver turns it on.
@@ -1201,16 +1245,16 @@ int pfb_hess_plan_kernels(const pfb_hess_plan *p) {
 }
 
 int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *p) {
+    if (!p || getenv("PFB_HESS_NOFUSE")) return 0;
+    if (p->mixed) {                              // peeled pass C (hess_peel.cuh), fp32
 #ifndef PFB_EMU
-    if (!p || p->dtype != PFB_F32 || getenv("PFB_HESS_NOFUSE")) return 0;
-    if (p->mixed) return (p->prow.m && p->pd_partP) ? 1 : 0;     // peeled pass C (hess_peel.cuh)
-    if (!p->fast || !p->have_tma || !p->pd_part || p->h.nx % 2) return 0;
-    if (getenv("PFB_HESS_NOTMA") || getenv("PFB_HESS_NOPIPE")) return 0;
-    return tma_fits_m(p->h.M) ? 1 : 0;
+        return (p->prow.m && p->pd_partP && p->dtype == PFB_F32) ? 1 : 0;
 #else
-    (void)p;
-    return 0;
+        return 0;
 #endif
+    }
+    // power-of-two fast paths: every pass C kernel of hess_fast.cuh takes the primal epilogue
+    return ((p->fast || p->fastrows) && p->pd_part) ? 1 : 0;
 }
 
 static int primal_args_ok(const pfb_hess_plan *p, const char *who) {
@@ -1222,40 +1266,28 @@ static int primal_args_ok(const pfb_hess_plan *p, const char *who) {
 }
 
 int pfb_hess_apply_primal_begin(pfb_hess_plan *p, const void *xp, void *stream) {
-#ifndef PFB_EMU
     if (int rc = primal_args_ok(p, "pfb_hess_apply_primal_begin")) return rc;
-    if (!xp || ((uintptr_t)xp & 7)) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_begin: bad argument");
+    const size_t al = 2 * dtype_size(p->dtype) - 1;
+    if (!xp || ((uintptr_t)xp & al)) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_begin: bad argument");
     cudaStream_t st = as_stream(stream);
-    if (p->mixed) return mixed_fwd_cols<float>(p, (const float *)xp, nullptr, st);
-    if (p->dyn) PFB_CUDA_OK(cudaMemsetAsync(p->ctr, 0, 3 * sizeof(int), st));
-    if (int rc = fast_rows_fwd_d<float>(p, (const float *)xp, nullptr, st)) return rc;
-    return fast_cols_d<float>(p, st);
-#else
-    (void)p; (void)xp; (void)stream;
-    return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_begin: not available in the emulator build");
-#endif
+    if (p->dtype == PFB_F32) return hess_fwd_cols_t<float>(p, (const float *)xp, nullptr, 0, st);
+    return hess_fwd_cols_t<double>(p, (const double *)xp, nullptr, 0, st);
 }
 
 int pfb_hess_apply_primal_end(pfb_hess_plan *p, const void *xp, const void *w, const void *wprev,
                               const void *data, double tau, int positivity, void *x, double *out2,
                               void *stream) {
-#ifndef PFB_EMU
     if (int rc = primal_args_ok(p, "pfb_hess_apply_primal_end")) return rc;
     if (!xp || !w || !wprev || !data || !x || !out2 || (positivity != 0 && positivity != 1))
         return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: bad argument");
     if (x == xp) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: x must not alias xp");
-    if (((uintptr_t)xp | (uintptr_t)w | (uintptr_t)wprev | (uintptr_t)data | (uintptr_t)x) & 7)
-        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: arrays must be 8-byte aligned");
-    PrimalArgs pa;
-    pa.xp = (const float *)xp; pa.w = (const float *)w; pa.wprev = (const float *)wprev;
-    pa.data = (const float *)data; pa.x = (float *)x; pa.tau = (float)tau; pa.positivity = positivity;
-    pa.part = nullptr;
-    if (p->mixed) return peel_rows_inv_primal_d(p, pa, out2, as_stream(stream));
-    return run_primal_m(p, pa, out2, as_stream(stream));
-#else
-    (void)p; (void)xp; (void)w; (void)wprev; (void)data; (void)tau; (void)positivity; (void)x; (void)out2; (void)stream;
-    return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: not available in the emulator build");
-#endif
+    const size_t al = 2 * dtype_size(p->dtype) - 1;
+    if (((uintptr_t)xp | (uintptr_t)w | (uintptr_t)wprev | (uintptr_t)data | (uintptr_t)x) & al)
+        return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: arrays must be aligned to two elements");
+    if (p->h.ny % 2) return fail(PFB_ERR_BAD_ARG, "pfb_hess_apply_primal_end: ny must be even");
+    cudaStream_t st = as_stream(stream);
+    if (p->dtype == PFB_F32) return primal_end_t<float>(p, xp, w, wprev, data, tau, positivity, x, out2, st);
+    return primal_end_t<double>(p, xp, w, wprev, data, tau, positivity, x, out2, st);
 }
 
 int pfb_hess_apply_primal(pfb_hess_plan *p, const void *xp, const void *w, const void *wprev,

@@ -287,12 +287,78 @@ k_hessf_cols(Cx<T> *S, const Cx<T> *__restrict__ psfE, const Cx<T> *__restrict__
     if (PF) cp_async_wait<0>();
 }
 
+// ------------------------------------------------------------------ fused primal epilogue
+// The primal step of primal_dual_optimised (pfb/opt/primal_dual.py:138-150) as the epilogue of
+// pass C: with conv = this row of PSF (*) xp still in registers,
+//     x = P+( xp - tau * (2 w - wprev + conv - data) ),   eps terms sum (x-xp)^2, sum x^2,
+// same arithmetic and order as k_pd_primal_vec, so the model is bit-identical.  The convolution
+// result is never written, and the separate primal kernel (one more read of it plus a launch)
+// disappears.
+template <class T> struct PrimalArgsT {
+    const T *xp, *w, *wprev, *data;
+    T *x;
+    T tau;
+    int positivity;      // 0 none, 1 clamp
+    double *part;        // 2 partial sums per CTA
+};
+// one column pair (c0, c0 + 1) of the row at element offset ro; c = the convolution values
+template <class T>
+__device__ __forceinline__ void primal_pair(const PrimalArgsT<T> &pa, long off, T cx0, T cx1,
+                                            double &acc0, double &acc1) {
+    typedef typename V2<T>::type T2;
+    const T2 p2 = *reinterpret_cast<const T2 *>(pa.xp + off);
+    const T2 w2 = *reinterpret_cast<const T2 *>(pa.w + off);
+    const T2 q2 = *reinterpret_cast<const T2 *>(pa.wprev + off);
+    const T2 d2 = *reinterpret_cast<const T2 *>(pa.data + off);
+    const T pv[2] = {p2.x, p2.y}, wv[2] = {w2.x, w2.y}, qv[2] = {q2.x, q2.y};
+    const T dv[2] = {d2.x, d2.y}, cv[2] = {cx0, cx1};
+    T xo[2];
+#pragma unroll
+    for (int z = 0; z < 2; ++z) {
+        T ge = (T)2 * wv[z] - qv[z];
+        const T gr = cv[z] - dv[z];
+        ge = ge + gr;
+        T xi = pv[z] - pa.tau * ge;
+        if (pa.positivity == 1 && xi < (T)0) xi = (T)0;
+        xo[z] = xi;
+        const T df = xi - pv[z];
+        acc0 += (double)(df * df);
+        acc1 += (double)(xi * xi);
+    }
+    T2 o;
+    o.x = xo[0]; o.y = xo[1];
+    *reinterpret_cast<T2 *>(pa.x + off) = o;
+}
+// fixed-order block sum of the two eps terms -> part[2 blockIdx.x ..]
+__device__ __forceinline__ void primal_block_sum(double acc0, double acc1, double *part) {
+    __shared__ double s_pred[2][32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        acc0 += __shfl_down_sync(0xffffffffu, acc0, o);
+        acc1 += __shfl_down_sync(0xffffffffu, acc1, o);
+    }
+    const int wid = threadIdx.x >> 5, ln = threadIdx.x & 31;
+    if (ln == 0) { s_pred[0][wid] = acc0; s_pred[1][wid] = acc1; }
+    __syncthreads();
+    if (wid == 0) {
+        const int nw = blockDim.x >> 5;
+        double a0 = ln < nw ? s_pred[0][ln] : 0.0, a1 = ln < nw ? s_pred[1][ln] : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a0 += __shfl_down_sync(0xffffffffu, a0, o);
+            a1 += __shfl_down_sync(0xffffffffu, a1, o);
+        }
+        if (ln == 0) { part[2 * blockIdx.x] = a0; part[2 * blockIdx.x + 1] = a1; }
+    }
+}
+
 // ------------------------------------------------------------------ pass C
-template <class T, int M, int RB, bool DYN, int NG = 2>
+template <class T, int M, int RB, bool DYN, int NG = 2, bool PRIMAL = false>
 __global__ void __launch_bounds__(NG * M / 16, 1)
 k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
                  const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twr, HessDims h,
-                 int nbatch_band, Epilogue<T> ep, int *counter) {
+                 int nbatch_band, Epilogue<T> ep, int *counter, PrimalArgsT<T> pa = PrimalArgsT<T>()) {
+    double acc0 = 0.0, acc1 = 0.0;
     PFB_DYN_SMEM(raw);
     Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
     Cx<T> *tab = bufs + RB * ct_stride(M);
@@ -334,7 +400,16 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
                 v[e] = cx<T>(A.x - wB.y, A.y + wB.x);
             }
             ct_fft<T, M, +1>(v, t, buf, tab, bar);
-            if (row < h.nx) {
+            if (PRIMAL) {
+                if (row < h.nx) {
+                    const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        const int c0 = 2 * (t + e * NT);
+                        if (c0 < h.ny) primal_pair<T>(pa, ro + c0, v[e].x, v[e].y, acc0, acc1);
+                    }
+                }
+            } else if (row < h.nx) {
                 const long ro = ((long)band * h.nx + row) * h.ny;
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
@@ -358,6 +433,7 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
         }
         batch = q.publish();
     }
+    if (PRIMAL) primal_block_sum(acc0, acc1, pa.part);
 }
 
 // Pass C, pipelined: the CTA owns four lines; while its two transform groups work
@@ -369,11 +445,12 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
 // copy the two rows of a pair (one 16-byte run per k); the other half of each
 // 32-byte sector is fetched by the next pair, one transform later (L2 hit).
 // TWS: twr (M entries) is staged in shared memory.
-template <class T, int M, bool TWS, bool DYN>
+template <class T, int M, bool TWS, bool DYN, bool PRIMAL = false>
 __global__ void __launch_bounds__(M / 8, 1)
 k_hessf_rows_inv2(const Cx<T> *__restrict__ S, T *__restrict__ out,
                   const Cx<T> *__restrict__ tabg, const Cx<T> *__restrict__ twrg, HessDims h,
-                  int nbatch_band, Epilogue<T> ep, int *counter) {
+                  int nbatch_band, Epilogue<T> ep, int *counter, PrimalArgsT<T> pa = PrimalArgsT<T>()) {
+    double acc0 = 0.0, acc1 = 0.0;
     PFB_DYN_SMEM(raw);
     Cx<T> *bufs = reinterpret_cast<Cx<T> *>(raw);
     Cx<T> *tab = bufs + 4 * ct_stride(M);
@@ -439,7 +516,16 @@ k_hessf_rows_inv2(const Cx<T> *__restrict__ S, T *__restrict__ out,
             }
             __syncthreads();                     // both rows are in registers: the stage becomes the exchange lines
             ct_fft<T, M, +1>(v, t, buf, tab, bar);
-            if (row < h.nx) {
+            if (PRIMAL) {
+                if (row < h.nx) {
+                    const long ro = ((long)band * h.nx + row) * h.ny;
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        const int c0 = 2 * (t + e * NT);
+                        if (c0 < h.ny) primal_pair<T>(pa, ro + c0, v[e].x, v[e].y, acc0, acc1);
+                    }
+                }
+            } else if (row < h.nx) {
                 const long ro = ((long)band * h.nx + row) * h.ny;
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
@@ -466,6 +552,7 @@ k_hessf_rows_inv2(const Cx<T> *__restrict__ S, T *__restrict__ out,
         nxt = q.publish();
     }
     cp_async_wait<0>();
+    if (PRIMAL) primal_block_sum(acc0, acc1, pa.part);
 }
 
 // Pass B, one transform group per CTA: the CTA's NT = H/16 threads run the even
@@ -610,13 +697,7 @@ template <int M> __host__ __device__ constexpr int tma_stage_elems() {
 //     x = P+( xp - tau * (2 w - wprev + conv - data) ),   eps terms sum (x-xp)^2, sum x^2,
 // same arithmetic and order as k_pd_primal_vec.  The convolution result is never written, and
 // the separate primal kernel (one more read of it plus a launch) disappears.
-struct PrimalArgs {
-    const float *xp, *w, *wprev, *data;
-    float *x;
-    float tau;
-    int positivity;      // 0 none, 1 clamp
-    double *part;        // gridDim.x * 2 partial sums
-};
+typedef PrimalArgsT<float> PrimalArgs;
 
 template <int M, bool DYN, bool PRIMAL>
 __global__ void __launch_bounds__(M / 8, 1)
@@ -781,6 +862,8 @@ k_hessf_rows_inv_tma(const __grid_constant__ CUtensorMap tmS, float *__restrict_
     }
 }
 
+#endif  // !PFB_EMU
+
 // out2[j] = sum over the n CTAs of part[2 c + j], fixed order
 __global__ void k_hess_red_final(const double *__restrict__ part, int n, double *__restrict__ out2) {
     double a0 = 0.0, a1 = 0.0;
@@ -816,6 +899,6 @@ k_hess_red_final_wide(const double *__restrict__ part, int n, double *__restrict
         if (ln == 0) { out2[0] = a0; out2[1] = a1; }
     }
 }
-#endif  // !PFB_EMU
+
 
 }  // namespace pfb

@@ -273,9 +273,10 @@ def primal_dual_optimised(x, v, lam, psiH, psi, L, prox, l1weight, reweighter, g
     shard_ok = (not parallel.active()) or (nat and not os.environ.get("PFB_PAR_NOREC")
                                              and not os.environ.get("PFB_PAR_NOFUSE"))
     if (lin and bound is not None and data is not None and positivity in (0, 1)
-            and shard_ok and xa.dtype == torch.float32
+            and shard_ok and xa.shape[-1] % 2 == 0 and xa.data_ptr() % (2 * xa.element_size()) == 0
             and not os.environ.get("PFB_PD_NOFUSE")):
-        if str(bound[0].dtype).endswith("complex64"):
+        want = "complex64" if xa.dtype == torch.float32 else "complex128"
+        if str(bound[0].dtype).endswith(want):
             from ..operators.psf import get_plan
             cand = get_plan(bound[0], bound[1], tuple(xa.shape), _dev.dcode(xa))
             if cand.can_fuse_primal():

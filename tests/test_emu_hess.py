@@ -152,3 +152,38 @@ def test_hess_plan_errors():
     assert EmuHess(1, 8, 8, 32, 76, np.float64).rc == 4      # nyp/2 = 38 = 2 * 19
     assert EmuHess(1, 8, 8, 32, 2 * 15000, np.float64).rc == 4   # two lines beyond shared memory
     assert EmuHess(1, 40, 8, 32, 32, np.float64).rc == 1     # image larger than PSF
+
+
+@pmp("dtype", [np.float32, np.float64])
+def test_fused_primal_pass_emulated(dtype):
+    """pfb_hess_apply_primal (primal step of primal_dual_optimised as the epilogue of pass C,
+    pipelined and basic kernels of hess_fast.cuh) against pfb_hess_apply + pfb_pd_primal_lin:
+    bit-identical model, eps terms equal to rounding."""
+    rng = np.random.default_rng(31)
+    nband, nx, ny, nxp, nyp = 1, 6, 400, 1024, 1024
+    cdt = np.complex64 if dtype == np.float32 else np.complex128
+    psf = rng.standard_normal((nband, nxp, nyp))
+    psfhat = np.fft.rfft2(np.fft.ifftshift(psf, axes=(1, 2)), axes=(1, 2)).astype(cdt)
+    H = EmuHess(nband, nx, ny, nxp, nyp, dtype)
+    assert H.rc == 0 and H.L.pfb_hess_plan_kernels(H.plan) & 1
+    H.set_psfhat(psfhat)
+    assert H.L.pfb_hess_plan_can_fuse_primal(H.plan) == 1
+    xp, w, wprev, data = (rng.standard_normal((nband, nx, ny)).astype(dtype) for _ in range(4))
+    code = 0 if dtype == np.float32 else 1
+    conv = H.apply(xp)
+    for pos in (1,):                             # positivity 0: GPU suite
+        x_ref = np.full(xp.shape, np.nan, dtype)
+        t_ref = np.zeros(2)
+        ok(H.L.pfb_pd_primal_lin(ptr(x_ref), ptr(xp), ptr(w), ptr(wprev), ptr(conv), ptr(data), 0.37, pos, nband,
+                                 nx * ny, code, ptr(t_ref), None))
+        x = np.full(xp.shape, np.nan, dtype)
+        t = np.zeros(2)
+        ok(H.L.pfb_hess_apply_primal(H.plan, ptr(xp), ptr(w), ptr(wprev), ptr(data), 0.37, pos, ptr(x), ptr(t), None))
+        assert np.array_equal(x, x_ref)
+        assert np.allclose(t, t_ref, rtol=1e-12, atol=0)
+    # the two halves give the same result as the single call
+    x2, t2 = np.full(xp.shape, np.nan, dtype), np.zeros(2)
+    ok(H.L.pfb_hess_apply_primal_begin(H.plan, ptr(xp), None))
+    ok(H.L.pfb_hess_apply_primal_end(H.plan, ptr(xp), ptr(w), ptr(wprev), ptr(data), 0.37, 1, ptr(x2), ptr(t2), None))
+    assert np.array_equal(x2, x) and np.array_equal(t2, t)
+    assert H.L.pfb_hess_apply_primal(H.plan, ptr(xp), ptr(w), ptr(wprev), ptr(data), 0.37, 1, ptr(xp), ptr(t), None) == 1

@@ -506,22 +506,31 @@ def test_pd_tolerance_exit_lagged_check(dtype, monkeypatch):
     assert np.array_equal(res[True][0], res[False][0]) and np.array_equal(res[True][1], res[False][1])
 
 
-@pmp("nx", [1024, 1536])
-def test_fused_primal_pass_matches_unfused(monkeypatch, nx):
+@pmp("nx,dtype,env", [(1024, np.float32, None), (1536, np.float32, None), (1024, np.float64, None),
+                       (2048, np.float64, None), (1024, np.float32, "PFB_HESS_NOTMA"),
+                       (1024, np.float32, "PFB_HESS_NOPIPE")])
+def test_fused_primal_pass_matches_unfused(monkeypatch, nx, dtype, env):
     """pfb_hess_apply_primal (primal step as the epilogue of pass C: the TMA kernel at 1024^2 /
     2048^2, the peeled kernel of hess_peel.cuh at 1536^2 / 3072^2, lines of 3 x 512 points)
     against the separate pfb_hess_apply + pfb_pd_primal_lin kernels: same arithmetic in
-    the same order, so the model is bit-identical; both positivity modes the fused pass takes."""
+    the same order, so the model is bit-identical; both positivity modes the fused pass takes;
+    fp64 (pipelined kernel at 1024, basic kernel at 2048 -- four fp64 lines do not fit there)
+    and the fp32 fall-backs behind PFB_HESS_NOTMA / PFB_HESS_NOPIPE."""
     from pfb_b200.operators.psf import psf_convolve_cube
     from pfb_b200.operators.psi import Psi
     from pfb_b200.opt.primal_dual import primal_dual_optimised, Grad21
+    from pfb_b200.operators import psf as P
     nband = 2
-    psfhat, dirty, _, _ = _problem(nband, nx, np.float32)
+    if env:                                  # the pipelined (no TMA) / basic (no pipeline) pass C kernels
+        monkeypatch.setenv(env, "1")
+    P.clear_plan_cache()
+    psfhat, dirty, _, _ = _problem(nband, nx, dtype)
+    tdt = torch.float32 if dtype == np.float32 else torch.float64
     dev = torch.device("cuda")
     psfd, dd = torch.from_numpy(psfhat).to(dev), torch.from_numpy(dirty).to(dev)
     psi = Psi(nband, nx, nx, BASES, 3, 1)
     shape_v = (nband, 5, psi.Nymax, psi.Nxmax)
-    w = torch.ones(shape_v[1:], dtype=torch.float32, device=dev)
+    w = torch.ones(shape_v[1:], dtype=tdt, device=dev)
     lam = 0.5 * float(dd.sum(dim=0).std())
     res = {}
     for positivity in (1, 0):
@@ -532,7 +541,7 @@ def test_fused_primal_pass_matches_unfused(monkeypatch, nx):
                 monkeypatch.setenv("PFB_PD_NOFUSE", "1")
             xout = torch.empty_like(dd)
             conv = partial(psf_convolve_cube, None, None, xout, psfd, 2 * nx)
-            x, v = torch.zeros_like(dd), torch.zeros(shape_v, dtype=torch.float32, device=dev)
+            x, v = torch.zeros_like(dd), torch.zeros(shape_v, dtype=tdt, device=dev)
             primal_dual_optimised(x, v, lam, psi.hdot, psi.dot, 1.3, None, w, None, Grad21(conv, dd),
                                   nu=5, tol=0.0, maxit=6, positivity=positivity, verbosity=0)
             assert primal_dual_optimised.last_fused == fuse
