@@ -563,3 +563,35 @@ def test_library_is_the_one_loaded():
     t = torch.ones(1000, device="cuda")
     _vec.axpby(t, 1.0, t, 1.0, t)
     assert L.lib().pfb_launch_count() == n0 + 1
+
+
+@pmp("nband,nx,ny,nxp,dtype", [(1, 8192, 8192, 16384, np.float32), (2, 1000, 1024, 2048, np.float64),
+                                (2, 3000, 3072, 6144, np.float32), (3, 512, 500, 1024, np.float32)])
+def test_fused_primal_entry_point_direct(nband, nx, ny, nxp, dtype):
+    """pfb_hess_apply_primal and its begin / end halves against pfb_hess_apply + pfb_pd_primal_lin
+    through the C-ABI on random arrays: the 16384-point row kernels (config 4), fp64, a peeled
+    plan, and an image narrower than the padding allows."""
+    from pfb_b200 import _dev, _lib
+    from pfb_b200.operators.psf import get_plan
+    tdt, cdt = (torch.float32, torch.complex64) if dtype == np.float32 else (torch.float64, torch.complex128)
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(11)
+    psfhat = torch.view_as_complex(torch.randn((nband, nxp, nxp // 2 + 1, 2), generator=g, device=dev, dtype=tdt))
+    xp, w, wprev, data = (torch.randn((nband, nx, ny), generator=g, device=dev, dtype=tdt) for _ in range(4))
+    plan = get_plan(psfhat, nxp, (nband, nx, ny), _dev.dcode(xp))
+    assert plan.can_fuse_primal()
+    L = _lib.lib()
+    conv = torch.empty_like(xp)
+    plan.apply(xp, conv)
+    x_ref, t_ref = torch.empty_like(xp), _dev.scalars(2)
+    _lib.check(L.pfb_pd_primal_lin(_dev.ptr(x_ref), _dev.ptr(xp), _dev.ptr(w), _dev.ptr(wprev), _dev.ptr(conv),
+                                   _dev.ptr(data), 0.37, 1, nband, nx * ny, _dev.dcode(xp), _dev.ptr(t_ref),
+                                   _dev.stream()))
+    x, t = torch.empty_like(xp), _dev.scalars(2)
+    plan.apply_primal(xp, w, wprev, data, 0.37, 1, x, t)
+    assert torch.equal(x, x_ref)
+    assert torch.allclose(t, t_ref, rtol=1e-10, atol=0)
+    x2, t2 = torch.empty_like(xp), _dev.scalars(2)
+    plan.apply_primal_begin(xp)
+    plan.apply_primal_end(xp, w, wprev, data, 0.37, 1, x2, t2)
+    assert torch.equal(x2, x) and torch.equal(t2, t)
