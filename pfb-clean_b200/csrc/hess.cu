@@ -1253,8 +1253,11 @@ int pfb_hess_plan_can_fuse_primal(const pfb_hess_plan *p) {
         return 0;
 #endif
     }
-    // power-of-two fast paths: every pass C kernel of hess_fast.cuh takes the primal epilogue
-    return ((p->fast || p->fastrows) && p->pd_part) ? 1 : 0;
+    // power-of-two fast paths: every pass C kernel of hess_fast.cuh takes the primal epilogue.  On the
+    // 16384-point row kernel it measured 0.1 ms slower than the separate primal kernel (config 4 on
+    // 8 GPUs: 1.94 vs 1.36 + 0.48 ms), so there it is opt-in.
+    if (p->fastrows && !p->fast) return (p->pd_part && getenv("PFB_HESS_FUSE_ROWS16K")) ? 1 : 0;
+    return (p->fast && p->pd_part) ? 1 : 0;
 }
 
 static int primal_args_ok(const pfb_hess_plan *p, const char *who) {

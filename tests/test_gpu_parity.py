@@ -567,7 +567,7 @@ def test_library_is_the_one_loaded():
 
 @pmp("nband,nx,ny,nxp,dtype", [(1, 8192, 8192, 16384, np.float32), (2, 1000, 1024, 2048, np.float64),
                                 (2, 3000, 3072, 6144, np.float32), (3, 512, 500, 1024, np.float32)])
-def test_fused_primal_entry_point_direct(nband, nx, ny, nxp, dtype):
+def test_fused_primal_entry_point_direct(monkeypatch, nband, nx, ny, nxp, dtype):
     """pfb_hess_apply_primal and its begin / end halves against pfb_hess_apply + pfb_pd_primal_lin
     through the C-ABI on random arrays: the 16384-point row kernels (config 4), fp64, a peeled
     plan, and an image narrower than the padding allows."""
@@ -579,6 +579,9 @@ def test_fused_primal_entry_point_direct(nband, nx, ny, nxp, dtype):
     psfhat = torch.view_as_complex(torch.randn((nband, nxp, nxp // 2 + 1, 2), generator=g, device=dev, dtype=tdt))
     xp, w, wprev, data = (torch.randn((nband, nx, ny), generator=g, device=dev, dtype=tdt) for _ in range(4))
     plan = get_plan(psfhat, nxp, (nband, nx, ny), _dev.dcode(xp))
+    if nxp == 16384:                 # opt-in there: measured slower than the separate primal kernel
+        assert not plan.can_fuse_primal()
+        monkeypatch.setenv("PFB_HESS_FUSE_ROWS16K", "1")
     assert plan.can_fuse_primal()
     L = _lib.lib()
     conv = torch.empty_like(xp)
