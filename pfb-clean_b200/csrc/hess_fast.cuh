@@ -329,6 +329,18 @@ __device__ __forceinline__ void primal_pair(const PrimalArgsT<T> &pa, long off, 
     o.x = xo[0]; o.y = xo[1];
     *reinterpret_cast<T2 *>(pa.x + off) = o;
 }
+// the four input rows of the primal epilogue: DRAM -> L2 while the row is still being transformed
+// (NT threads of one transform group cooperate; ny elements per row)
+template <class T>
+__device__ __forceinline__ void primal_prefetch(const PrimalArgsT<T> &pa, long ro, int ny, int t, int NT) {
+    constexpr int PL = 128 / (int)sizeof(T);
+    for (int i = t * PL; i < ny; i += NT * PL) {
+        prefetch_l2(pa.xp + ro + i);
+        prefetch_l2(pa.w + ro + i);
+        prefetch_l2(pa.wprev + ro + i);
+        prefetch_l2(pa.data + ro + i);
+    }
+}
 // fixed-order block sum of the two eps terms -> part[2 blockIdx.x ..]
 __device__ __forceinline__ void primal_block_sum(double acc0, double acc1, double *part) {
     __shared__ double s_pred[2][32];
@@ -389,6 +401,7 @@ k_hessf_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out,
         for (int ph = 0; ph < RB / NG; ++ph) {
             const int l = NG * ph + g, row = row0 + l;
             Cx<T> *buf = bufs + l * ct_stride(M);
+            if (PRIMAL && row < h.nx) primal_prefetch<T>(pa, ((long)band * h.nx + row) * h.ny, h.ny, t, NT);
             // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m])
             Cx<T> v[16];
 #pragma unroll
@@ -504,6 +517,7 @@ k_hessf_rows_inv2(const Cx<T> *__restrict__ S, T *__restrict__ out,
             const int row = row0 + 2 * ph + g;
             Cx<T> *buf = bufs + (2 * c + g) * ct_stride(M);
             const Cx<T> *stg = bufs + 2 * c * ct_stride(M) + g;
+            if (PRIMAL && row < h.nx) primal_prefetch<T>(pa, ((long)band * h.nx + row) * h.ny, h.ny, t, NT);
             // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m])
             Cx<T> v[16];
 #pragma unroll
