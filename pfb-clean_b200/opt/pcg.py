@@ -185,7 +185,11 @@ def _pcg_dev(A, bd, x, minv, nseg, tol, maxit, minit, verbosity, report_freq, ba
 
     r = torch.empty_like(bd)
     _vec.axpby(r, 1.0, apply_A(x, None), -1.0, bd)
-    y = r if minv == 1.0 else r * minv
+    if minv == 1.0:
+        y = r
+    else:
+        y = torch.empty_like(r)
+        _vec.axpby(y, float(minv), r, 0.0, r)
     dot(r, y, 0)
     dot(y, y, 7)
     h = _state_read(st, pinned, ev)

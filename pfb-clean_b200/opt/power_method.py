@@ -19,7 +19,7 @@ def power_method(A, imsize, b0=None, tol=1e-5, maxit=250, verbosity=1, report_fr
     bp = _dev.to_dev(b0, copy=True)
     s2 = _dev.scalars(2)
     n0 = parallel.allreduce_sum(_vec.vdot2(bp, bp, out=s2)).tolist()[0]
-    bp = bp / math.sqrt(n0)
+    _vec.axpby(bp, 1.0 / math.sqrt(n0), bp, 0.0, bp)      # b0 / ||b0||  (power_method.py:20-21)
     beta = 1.0
     eps = 1.0
     k = 0
