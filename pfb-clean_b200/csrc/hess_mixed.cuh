@@ -73,6 +73,40 @@ template <class T, int R, int DIR> struct MxDft {
         for (int q = 0; q < R; ++q) u[q] = o[q];
     }
 };
+// 3- and 5-point butterflies in their symmetric form (pairs x[n], x[R-n] share their cosine /
+// sine products): 16 and 56 real operations instead of 36 and 136 for the direct sums above --
+// these two radices carry most of the arithmetic of the good_size paddings (2^a 3^b 5^c)
+template <class T, int DIR> struct MxDft<T, 3, DIR> {
+    static __device__ __forceinline__ void run(Cx<T> (&u)[3], const Cx<T> *) {
+        const T s = (T)0.86602540378443864676;                 // sin(2 pi / 3)
+        const Cx<T> t1 = u[1] + u[2], d = u[1] - u[2];
+        const Cx<T> m1 = cx<T>(u[0].x - (T)0.5 * t1.x, u[0].y - (T)0.5 * t1.y);
+        // forward: -i s d = (s d.y, -s d.x); inverse: +i s d
+        const Cx<T> m2 = DIR < 0 ? cx<T>(s * d.y, -s * d.x) : cx<T>(-s * d.y, s * d.x);
+        u[0] = u[0] + t1;
+        u[1] = m1 + m2;
+        u[2] = m1 - m2;
+    }
+};
+template <class T, int DIR> struct MxDft<T, 5, DIR> {
+    static __device__ __forceinline__ void run(Cx<T> (&u)[5], const Cx<T> *) {
+        const T c1 = (T)0.30901699437494742410, c2 = (T)-0.80901699437494742410;   // cos(2 pi/5), cos(4 pi/5)
+        const T s1 = (T)0.95105651629515357212, s2 = (T)0.58778525229247312917;    // sin(2 pi/5), sin(4 pi/5)
+        const Cx<T> t1 = u[1] + u[4], t2 = u[2] + u[3], t3 = u[1] - u[4], t4 = u[2] - u[3];
+        const Cx<T> a1 = cx<T>(u[0].x + c1 * t1.x + c2 * t2.x, u[0].y + c1 * t1.y + c2 * t2.y);
+        const Cx<T> a2 = cx<T>(u[0].x + c2 * t1.x + c1 * t2.x, u[0].y + c2 * t1.y + c1 * t2.y);
+        const Cx<T> b1 = cx<T>(s1 * t3.x + s2 * t4.x, s1 * t3.y + s2 * t4.y);
+        const Cx<T> b2 = cx<T>(s2 * t3.x - s1 * t4.x, s2 * t3.y - s1 * t4.y);
+        // forward: X1 = a1 - i b1, X4 = a1 + i b1, X2 = a2 - i b2, X3 = a2 + i b2; inverse: conjugate roles
+        const Cx<T> ib1 = DIR < 0 ? cx<T>(b1.y, -b1.x) : cx<T>(-b1.y, b1.x);      // -/+ i b1
+        const Cx<T> ib2 = DIR < 0 ? cx<T>(b2.y, -b2.x) : cx<T>(-b2.y, b2.x);
+        u[0] = u[0] + t1 + t2;
+        u[1] = a1 + ib1;
+        u[4] = a1 - ib1;
+        u[2] = a2 + ib2;
+        u[3] = a2 - ib2;
+    }
+};
 template <class T, int DIR> struct MxDft<T, 2, DIR> {
     static __device__ __forceinline__ void run(Cx<T> (&u)[2], const Cx<T> *) { Dft<T, 2, DIR>::run(u); }
 };
