@@ -195,6 +195,26 @@ __device__ __forceinline__ void mx_load_tables(Cx<T> *rt, const Cx<T> *__restric
     for (int i = threadIdx.x; i < n; i += blockDim.x) rt[40 + i] = tw[i];
 }
 
+// Element loops of the passes: thread t takes elements t, t + nthreads, ...; U of them are
+// fetched (ld) before the first is used (st), so U global / L2 latencies overlap instead of
+// queueing one behind the other (ncu r02q / r02zf: 34-48 % of the stall samples of the
+// one-at-a-time loops were long-scoreboard waits on single loads).
+template <int U, class LD, class ST>
+__device__ __forceinline__ void peel_batched(int n, LD ld, ST st) {
+    for (int base = threadIdx.x; base < n; base += U * (int)blockDim.x) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * (int)blockDim.x;
+            if (i < n) ld(u, i);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * (int)blockDim.x;
+            if (i < n) st(u, i);
+        }
+    }
+}
+
 // ------------------------------------------------------------------ pass A
 template <class T>
 __global__ void __launch_bounds__(512)
@@ -207,29 +227,36 @@ k_hessm_rows_fwd(const T *__restrict__ x, const T *__restrict__ beam, Cx<T> *__r
     Cx<T> *A = rt + kMxHead, *B = A + (long)L * M;
     const int band = blockIdx.y, row0 = blockIdx.x * L;
     mx_load_tables(rt, roots, tw, M);
-    for (int i = threadIdx.x; i < L * M; i += blockDim.x) {
-        const int l = i / M, m = i - l * M, row = row0 + l, c0 = 2 * m;
-        T a = (T)0, b = (T)0;
-        if (row < h.nx) {
-            const long ro = ((long)band * h.nx + row) * h.ny;
-            if (c0 < h.ny) { a = x[ro + c0]; if (beam) a *= beam[ro + c0]; }
-            if (c0 + 1 < h.ny) { b = x[ro + c0 + 1]; if (beam) b *= beam[ro + c0 + 1]; }
-        }
-        A[i] = cx<T>(a, b);
+    {
+        T va[8], vb[8];
+        peel_batched<8>(L * M,
+            [&](int u, int i) {
+                const int l = i / M, m = i - l * M, row = row0 + l, c0 = 2 * m;
+                va[u] = vb[u] = (T)0;
+                if (row < h.nx) {
+                    const long ro = ((long)band * h.nx + row) * h.ny;
+                    if (c0 < h.ny) { va[u] = x[ro + c0]; if (beam) va[u] *= beam[ro + c0]; }
+                    if (c0 + 1 < h.ny) { vb[u] = x[ro + c0 + 1]; if (beam) vb[u] *= beam[ro + c0 + 1]; }
+                }
+            },
+            [&](int u, int i) { A[i] = cx<T>(va[u], vb[u]); });
     }
     __syncthreads();
     const Cx<T> *Z = mx_fft<T, -1>(A, B, L, d, rt + 40, rt);
     // X[k] = E + w^k O,  E = (Z[k] + conj Z[M-k])/2,  O = -i (Z[k] - conj Z[M-k])/2
-    for (int i = threadIdx.x; i < (M + 1) * L; i += blockDim.x) {
-        const int k = i / L, l = i - k * L;
-        const Cx<T> *z = Z + (long)l * M;
-        const Cx<T> zk = z[k == M ? 0 : k], zm = cconj(z[k == 0 ? 0 : M - k]);
-        const Cx<T> E = cx<T>((T)0.5 * (zk.x + zm.x), (T)0.5 * (zk.y + zm.y));
-        const Cx<T> D = cx<T>((T)0.5 * (zk.x - zm.x), (T)0.5 * (zk.y - zm.y));
-        const Cx<T> O = cx<T>(D.y, -D.x);
-        const Cx<T> X = E + cmul(twr[k], O);
-        if (row0 + l < h.nx) S[((long)band * h.nyo2 + k) * h.nx + row0 + l] = X;
-    }
+    Cx<T> w[4];
+    peel_batched<4>((M + 1) * L,
+        [&](int u, int i) { w[u] = twr[i / L]; },
+        [&](int u, int i) {
+            const int k = i / L, l = i - k * L;
+            const Cx<T> *z = Z + (long)l * M;
+            const Cx<T> zk = z[k == M ? 0 : k], zm = cconj(z[k == 0 ? 0 : M - k]);
+            const Cx<T> E = cx<T>((T)0.5 * (zk.x + zm.x), (T)0.5 * (zk.y + zm.y));
+            const Cx<T> D = cx<T>((T)0.5 * (zk.x - zm.x), (T)0.5 * (zk.y - zm.y));
+            const Cx<T> O = cx<T>(D.y, -D.x);
+            const Cx<T> X = E + cmul(w[u], O);
+            if (row0 + l < h.nx) S[((long)band * h.nyo2 + k) * h.nx + row0 + l] = X;
+        });
 }
 
 // ------------------------------------------------------------------ pass B
@@ -247,11 +274,17 @@ k_hessm_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
     const Cx<T> *pl = psfT + ((long)band * h.nyo2 + col) * h.nxp;
     mx_load_tables(rt, roots, tw, N);
     const Cx<T> *tws = rt + 40;
-    for (int n = threadIdx.x; n < N; n += blockDim.x) A[n] = n < h.nx ? line[n] : cx<T>((T)0, (T)0);
+    constexpr int U1 = sizeof(T) == 4 ? 8 : 4, U2 = U1 / 2;   // batch depths by register budget
+    Cx<T> v[U1], g[U2];
+    peel_batched<U1>(N,
+        [&](int u, int n) { v[u] = n < h.nx ? line[n] : cx<T>((T)0, (T)0); },
+        [&](int u, int n) { A[n] = v[u]; });
     __syncthreads();
     Cx<T> *c = mx_fft<T, -1>(A, B, 1, d, tws, rt);
     Cx<T> *o = c == A ? B : A;
-    for (int n = threadIdx.x; n < N; n += blockDim.x) c[n] = cmul(c[n], pl[n]);
+    peel_batched<U1>(N,
+        [&](int u, int n) { v[u] = pl[n]; },
+        [&](int u, int n) { c[n] = cmul(c[n], v[u]); });
     __syncthreads();
     Cx<T> *r = mx_fft<T, +1>(c, o, 1, d, tws, rt);
     if (!SPLIT) {
@@ -260,19 +293,26 @@ k_hessm_cols(Cx<T> *S, const Cx<T> *__restrict__ psfT, const Cx<T> *__restrict__
     }
     // odd spectrum: input a[n] w^n; park the even result in the (now dead) S line
     o = r == A ? B : A;
-    for (int n = threadIdx.x; n < N; n += blockDim.x)
-        o[n] = n < h.nx ? cmul(line[n], modg[n]) : cx<T>((T)0, (T)0);
+    peel_batched<U2>(N,
+        [&](int u, int n) {
+            v[u] = cx<T>((T)0, (T)0);
+            if (n < h.nx) { v[u] = line[n]; g[u] = modg[n]; }
+        },
+        [&](int u, int n) { o[n] = n < h.nx ? cmul(v[u], g[u]) : cx<T>((T)0, (T)0); });
     __syncthreads();                              // every read of the line is done
     for (int n = threadIdx.x; n < h.nx; n += blockDim.x) line[n] = r[n];
     __syncthreads();
     c = mx_fft<T, -1>(o, r, 1, d, tws, rt);
     o = c == A ? B : A;
-    for (int n = threadIdx.x; n < N; n += blockDim.x) c[n] = cmul(c[n], pl[N + n]);
+    peel_batched<U1>(N,
+        [&](int u, int n) { v[u] = pl[N + n]; },
+        [&](int u, int n) { c[n] = cmul(c[n], v[u]); });
     __syncthreads();
     r = mx_fft<T, +1>(c, o, 1, d, tws, rt);
     // same thread wrote line[n] above (same index mapping): no fence needed
-    for (int n = threadIdx.x; n < h.nx; n += blockDim.x)
-        line[n] = line[n] + cmul(r[n], cconj(modg[n]));
+    peel_batched<U2>(h.nx,
+        [&](int u, int n) { v[u] = line[n]; g[u] = modg[n]; },
+        [&](int u, int n) { line[n] = v[u] + cmul(r[n], cconj(g[u])); });
 }
 
 // ------------------------------------------------------------------ pass C
@@ -288,17 +328,27 @@ k_hessm_rows_inv(const Cx<T> *__restrict__ S, T *__restrict__ out, const Cx<T> *
     const int band = blockIdx.y, row0 = blockIdx.x * L;
     mx_load_tables(rt, roots, tw, M);
     // Z'[m] = (X[m] + conj X[M-m]) + i w^-m (X[m] - conj X[M-m])   (= 2 Z[m]), m < M
-    for (int i = threadIdx.x; i < M * L; i += blockDim.x) {
-        const int m = i / L, l = i - m * L;
-        Cx<T> xm = cx<T>((T)0, (T)0), xr = xm;
-        if (row0 + l < h.nx) {
-            const Cx<T> *col = S + (long)band * h.nyo2 * h.nx + row0 + l;
-            xm = col[(long)m * h.nx];
-            xr = cconj(col[(long)(M - m) * h.nx]);
-        }
-        const Cx<T> P = xm + xr, Q = xm - xr;
-        const Cx<T> wQ = cmul(cconj(twr[m]), Q);
-        A[(long)l * M + m] = cx<T>(P.x - wQ.y, P.y + wQ.x);
+    {
+        constexpr int U3 = sizeof(T) == 4 ? 8 : 2;
+        Cx<T> xm[U3], xr[U3], w[U3];
+        peel_batched<U3>(M * L,
+            [&](int u, int i) {
+                const int m = i / L, l = i - m * L;
+                xm[u] = xr[u] = cx<T>((T)0, (T)0);
+                if (row0 + l < h.nx) {
+                    const Cx<T> *col = S + (long)band * h.nyo2 * h.nx + row0 + l;
+                    xm[u] = col[(long)m * h.nx];
+                    xr[u] = col[(long)(M - m) * h.nx];
+                }
+                w[u] = twr[m];
+            },
+            [&](int u, int i) {
+                const int m = i / L, l = i - m * L;
+                const Cx<T> c = cconj(xr[u]);
+                const Cx<T> P = xm[u] + c, Q = xm[u] - c;
+                const Cx<T> wQ = cmul(cconj(w[u]), Q);
+                A[(long)l * M + m] = cx<T>(P.x - wQ.y, P.y + wQ.x);
+            });
     }
     __syncthreads();
     const Cx<T> *Z = mx_fft<T, +1>(A, B, L, d, rt + 40, rt);

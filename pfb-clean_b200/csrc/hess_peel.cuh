@@ -117,26 +117,6 @@ __device__ __forceinline__ void peel_load_tables(Cx<T> *rt, const Cx<T> *__restr
     for (int i = threadIdx.x; i < ct_tab_size(P2); i += blockDim.x) tab[i] = tabg[i];
 }
 
-// Element loops of the passes: thread t takes elements t, t + nthreads, ...; U of them are
-// fetched (ld) before the first is used (st), so U global / L2 latencies overlap instead of
-// queueing one behind the other (ncu r02q: 38-48 % of the stall samples of the first version
-// were long-scoreboard waits on single loads).
-template <int U, class LD, class ST>
-__device__ __forceinline__ void peel_batched(int n, LD ld, ST st) {
-    for (int base = threadIdx.x; base < n; base += U * (int)blockDim.x) {
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int i = base + u * (int)blockDim.x;
-            if (i < n) ld(u, i);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int i = base + u * (int)blockDim.x;
-            if (i < n) st(u, i);
-        }
-    }
-}
-
 // Column pass, spectrum side: forward butterflies, multiplication with the PSF spectrum and
 // inverse butterflies (+ conjugate twiddles) in one walk over the segments -- the spectrum
 // never goes back to shared memory in between.  pl: this column's (half of the) PSF spectrum.
