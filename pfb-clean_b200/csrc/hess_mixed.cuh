@@ -138,9 +138,10 @@ __device__ __forceinline__ void mx_stage(const Cx<T> *src, Cx<T> *dst, int L, in
                                          const Cx<T> *tws, const Cx<T> *rt) {
     const int nb = N / R;
     const int twm = N / (Ns * R);
+    const bool pow2 = (Ns & (Ns - 1)) == 0;       // every stage up to the first odd radix
     for (int i = threadIdx.x; i < nb * L; i += blockDim.x) {
-        const int l = i / nb, j = i - l * nb;
-        const int k = j % Ns;
+        const int l = L == 1 ? 0 : i / nb, j = i - l * nb;
+        const int k = pow2 ? (j & (Ns - 1)) : j % Ns;
         const Cx<T> *s = src + (long)l * N + j;
         Cx<T> u[R];
 #pragma unroll
