@@ -102,7 +102,8 @@ MIXED = [(8, 8, 24, 32), (8, 8, 16, 16), (5, 6, 10, 12), (12, 14, 24, 28), (9, 2
          # (3, 5, 7) x power of two: hess_peel.cuh -- rows (M = 1536, 2560), split columns
          # (H = 1536, 3584), full columns (nxp = 3072), both at once
          (6, 1500, 12, 3072), (2, 2500, 4, 5120), (1500, 6, 3072, 12), (3000, 4, 7168, 8),
-         (2000, 6, 3072, 12), (2, 3500, 4, 7168)]       # both passes peeled at once: GPU suite
+         (2000, 6, 3072, 12), (2, 3500, 4, 7168),       # both passes peeled at once: GPU suite
+         (5, 1499, 10, 3072), (1537, 3, 3072, 6)]        # odd image sizes on peeled plans
 
 
 @pmp("dtype", [np.float32, np.float64])
