@@ -19,9 +19,7 @@
 //                  (beam, /wsum, + sigmainv*x) fused into the store.
 // HBM traffic per band: x + out + psfhat^T + 4 x (nx x nyo2 complex) instead
 // of the reference's ~5 passes over the 4x larger padded arrays.
-#include "hess_fast.cuh"
-#include "hess_mixed.cuh"
-#include "hess_peel.cuh"
+#include "hess_plan.cuh"
 #include <cmath>
 #include <vector>
 
@@ -250,47 +248,9 @@ __global__ void k_psfhat_prepare(const Cx<T> *__restrict__ in, Cx<T> *__restrict
 
 }  // namespace pfb
 
-struct pfb_hess_plan {
-    int dtype;
-    pfb::HessDims h;
-    pfb::FftDesc drow, dcol;
-    int Rrow, Rcol;          // lines per CTA in the row / column passes
-    void *tw;                // twN complex twiddles exp(-2 pi i m / twN)
-    void *S;                 // (nband, nyo2, nx) complex scratch
-    void *psfT;              // (nband, nyo2, nxp) complex, scaled
-    int have_psf;
-    // fast path (hess_fast.cuh): nxp = 2H >= 2nx, nyp = 2M >= 2ny, H, M in [512, 4096]
-    int fast, RB, nsm;
-    int fastcols;            // fp32, nxp = 16384: pass B on k_hessf_cols1<8192>
-    int fastrows;            // fp32, nyp = 16384: passes A / C on the one-group row kernels (M = 8192)
-    void *tabM, *tabH;       // ct_fft stage tables for lengths M and H
-    void *twr;               // exp(-2 pi i k / nyp), k = 0..M
-    void *modg;              // exp(-2 pi i n / nxp), n = 0..H-1
-    int *ctr;                // work counters of the three persistent kernels (ItemQueue)
-    int dyn;                 // hand items out dynamically (see pfb_hess_set_dynamic)
-    // mixed-radix path (hess_mixed.cuh): padded sizes that are not powers of two
-    int mixed, split, Lrow;  // split: even/odd pruned column pass (nxp = 2H, nx <= H)
-    pfb::MxDesc mrow, mcol;
-    void *mtwM, *mtwC, *mroots;   // length-M / length-(H or nxp) twiddle tables, odd-radix roots
-    int deint;               // psfT rows stored [even | odd] per column
-    // odd factor x power of two (hess_peel.cuh): passes whose length is m * P2 leave the
-    // run-time radix list for m compile-time transforms of length P2
-    pfb::PeelDesc prow, pcol;
-    int LrowP, inplR;        // rows per CTA of the peeled row passes; lines transformed in place
-    void *ptabR, *ptabC;     // ct_fft stage tables of prow.P2 / pcol.P2
-    double *pd_partP;        // partial eps sums of the peeled pass C's primal epilogue (2 per CTA)
-    int pcol2;               // column pass on k_hessp_cols2 (psfT stored permuted [q][k] per half)
-#ifndef PFB_EMU
-    CUtensorMap tmS;         // S as (band, k, row) tensor of 8-byte elements, box 2 rows x 256 k (fp32 fast path)
-#endif
-    int have_tma;
-    double *pd_part;         // partial eps sums of the fused primal epilogue (2 per CTA)
-};
 
 namespace pfb {
 
-static const size_t kMaxSmem = 200 * 1024;
-static const size_t kMaxSmemFast = 224 * 1024;
 
 // kernels are compiled for several block-size caps so that the register
 // allocation always fits (1024 threads -> 64 regs, 512 -> 128, <= 256 -> 255)
@@ -329,18 +289,6 @@ static int hess_set_psf_t(pfb_hess_plan *p, const void *psfhat, cudaStream_t st)
 
 
 // ---------------------------------------------------------------- fast path
-static int persistent_grid(const void *func, int threads, size_t smem, int total, int nsm) {
-#ifdef PFB_EMU
-    (void)func; (void)threads; (void)smem; (void)nsm;
-    return total < 2 ? total : 2;
-#else
-    int per = 1;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, func, threads, smem) != cudaSuccess || per < 1)
-        per = 1;
-    long g = (long)per * nsm;
-    return (int)(g < total ? g : total);
-#endif
-}
 
 template <class T, int M, int RB, bool TWS>
 static int fast_rows_fwd_k(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st, size_t smem) {
@@ -362,32 +310,6 @@ static int fast_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream
     if (smem_tw <= kMaxSmemFast && !getenv("PFB_HESS_NOTWS"))
         return fast_rows_fwd_k<T, M, RB, true>(p, x, beam, st, smem_tw);
     return fast_rows_fwd_k<T, M, RB, false>(p, x, beam, st, smem);
-}
-
-// eps terms of a fused primal pass: fixed-order sum of the CTAs' partials
-static int primal_finish(pfb_hess_plan *p, int grid, double *out2, cudaStream_t st) {
-    launch(&k_hess_red_final, dim3(1), dim3(32), 0, st, (const double *)p->pd_part, grid, out2);
-    PFB_CHECK_LAUNCH();
-    return PFB_OK;
-}
-
-// pa != nullptr: the primal step is the epilogue (PrimalArgsT), eps terms -> out2
-template <class T, int M, bool TWS>
-static int fast_rows_inv2(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st, size_t smem,
-                          const PrimalArgsT<T> *pa = nullptr, double *out2 = nullptr) {
-    const HessDims &h = p->h;
-    auto kern = pa ? (p->dyn ? &k_hessf_rows_inv2<T, M, TWS, true, true> : &k_hessf_rows_inv2<T, M, TWS, false, true>)
-                   : (p->dyn ? &k_hessf_rows_inv2<T, M, TWS, true, false> : &k_hessf_rows_inv2<T, M, TWS, false, false>);
-    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int nbb = cdiv(h.nx, 4);
-    int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
-    if (grid > 4 * p->nsm) grid = 4 * p->nsm;      // size of pd_part
-    PrimalArgsT<T> a = pa ? *pa : PrimalArgsT<T>();
-    a.part = p->pd_part;
-    launch(kern, dim3(grid), dim3(M / 8), smem, st, (const Cx<T> *)p->S, out, (const Cx<T> *)p->tabM,
-           (const Cx<T> *)p->twr, h, nbb, ep, p->ctr + 2, a);
-    PFB_CHECK_LAUNCH();
-    return pa ? primal_finish(p, grid, out2, st) : PFB_OK;
 }
 
 #ifndef PFB_EMU
@@ -415,79 +337,7 @@ static bool make_tma_S(pfb_hess_plan *p) {
     return rc == CUDA_SUCCESS;
 }
 
-template <int M, bool PRIMAL>
-static int fast_rows_inv_tma(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, PrimalArgs pa,
-                             double *out2, cudaStream_t st) {
-    const HessDims &h = p->h;
-    const size_t smem = sizeof(Cx<float>) * ((size_t)2 * tma_stage_elems<M>() + ct_tab_size(M) + M) + 16 + 128;
-    auto kern = p->dyn ? &k_hessf_rows_inv_tma<M, true, PRIMAL> : &k_hessf_rows_inv_tma<M, false, PRIMAL>;
-    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int nbb = cdiv(h.nx, 4);
-    int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
-    if (grid > 4 * p->nsm) grid = 4 * p->nsm;      // size of pd_part
-    pa.part = p->pd_part;
-    launch(kern, dim3(grid), dim3(M / 8), smem, st, p->tmS, out, (const Cx<float> *)p->tabM,
-           (const Cx<float> *)p->twr, h, nbb, ep, pa, p->ctr + 2);
-    PFB_CHECK_LAUNCH();
-    if (PRIMAL) {
-        launch(&k_hess_red_final, dim3(1), dim3(32), 0, st, (const double *)p->pd_part, grid, out2);
-        PFB_CHECK_LAUNCH();
-    }
-    return PFB_OK;
-}
-template <class T, int M> struct RowsInvTma {
-    static bool fits() { return false; }
-    static int run(pfb_hess_plan *, T *, const Epilogue<T> &, cudaStream_t) { return PFB_ERR_BAD_ARG; }
-    static int run_primal(pfb_hess_plan *, const PrimalArgs &, double *, cudaStream_t) { return PFB_ERR_BAD_ARG; }
-};
-template <int M> struct RowsInvTma<float, M> {
-    static bool fits() {
-        return sizeof(Cx<float>) * ((size_t)2 * tma_stage_elems<M>() + ct_tab_size(M) + M) + 144 <= kMaxSmemFast;
-    }
-    static int run(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st) {
-        return fast_rows_inv_tma<M, false>(p, out, ep, PrimalArgs(), nullptr, st);
-    }
-    static int run_primal(pfb_hess_plan *p, const PrimalArgs &pa, double *out2, cudaStream_t st) {
-        return fast_rows_inv_tma<M, true>(p, nullptr, Epilogue<float>(), pa, out2, st);
-    }
-};
-
 #endif
-
-template <class T, int M, int RB>
-static int fast_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st,
-                         const PrimalArgsT<T> *pa = nullptr, double *out2 = nullptr) {
-    const HessDims &h = p->h;
-#ifndef PFB_EMU
-    if (p->have_tma && h.nx % 2 == 0 && RowsInvTma<T, M>::fits() && !getenv("PFB_HESS_NOTMA") &&
-        !getenv("PFB_HESS_NOPIPE")) {
-        if constexpr (sizeof(T) == 4) {
-            if (pa) return RowsInvTma<T, M>::run_primal(p, *pa, out2, st);
-        }
-        return RowsInvTma<T, M>::run(p, out, ep, st);
-    }
-#endif
-    // pipelined kernel (four lines: gather of the next row pair under the transforms) when it fits
-    const size_t smem4 = sizeof(Cx<T>) * ((size_t)4 * ct_stride(M) + ct_tab_size(M));
-    if (!getenv("PFB_HESS_NOPIPE") && h.nx % 2 == 0) {
-        if (smem4 + sizeof(Cx<T>) * M <= kMaxSmemFast)
-            return fast_rows_inv2<T, M, true>(p, out, ep, st, smem4 + sizeof(Cx<T>) * M, pa, out2);
-        if (smem4 <= kMaxSmemFast) return fast_rows_inv2<T, M, false>(p, out, ep, st, smem4, pa, out2);
-    }
-    size_t smem = sizeof(Cx<T>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
-    auto kern = pa ? (p->dyn ? &k_hessf_rows_inv<T, M, RB, true, 2, true> : &k_hessf_rows_inv<T, M, RB, false, 2, true>)
-                   : (p->dyn ? &k_hessf_rows_inv<T, M, RB, true, 2, false> : &k_hessf_rows_inv<T, M, RB, false, 2, false>);
-    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int nbb = cdiv(h.nx, RB);
-    int grid = persistent_grid((const void *)kern, M / 8, smem, nbb * h.nband, p->nsm);
-    if (grid > 4 * p->nsm) grid = 4 * p->nsm;      // size of pd_part
-    PrimalArgsT<T> a = pa ? *pa : PrimalArgsT<T>();
-    a.part = p->pd_part;
-    launch(kern, dim3(grid), dim3(M / 8), smem, st, (const Cx<T> *)p->S, out, (const Cx<T> *)p->tabM,
-           (const Cx<T> *)p->twr, h, nbb, ep, p->ctr + 2, a);
-    PFB_CHECK_LAUNCH();
-    return pa ? primal_finish(p, grid, out2, st) : PFB_OK;
-}
 
 template <class T, int H>
 static int fast_cols1(pfb_hess_plan *p, cudaStream_t st) {
@@ -545,33 +395,7 @@ static int fast_rows_fwd_8k(pfb_hess_plan *p, const float *x, const float *beam,
     PFB_CHECK_LAUNCH();
     return PFB_OK;
 }
-static int fast_rows_inv_8k(pfb_hess_plan *p, float *out, const Epilogue<float> &ep, cudaStream_t st,
-                            const PrimalArgsT<float> *pa = nullptr, double *out2 = nullptr) {
-    constexpr int M = 8192, RB = 2;
-    const HessDims &h = p->h;
-    const size_t smem = sizeof(Cx<float>) * ((size_t)RB * ct_stride(M) + ct_tab_size(M));
-    auto kern = pa ? (p->dyn ? &k_hessf_rows_inv<float, M, RB, true, 1, true> : &k_hessf_rows_inv<float, M, RB, false, 1, true>)
-                   : (p->dyn ? &k_hessf_rows_inv<float, M, RB, true, 1, false> : &k_hessf_rows_inv<float, M, RB, false, 1, false>);
-    PFB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int nbb = cdiv(h.nx, RB);
-    int grid = persistent_grid((const void *)kern, M / 16, smem, nbb * h.nband, p->nsm);
-    if (grid > 4 * p->nsm) grid = 4 * p->nsm;      // size of pd_part
-    PrimalArgsT<float> a = pa ? *pa : PrimalArgsT<float>();
-    a.part = p->pd_part;
-    launch(kern, dim3(grid), dim3(M / 16), smem, st, (const Cx<float> *)p->S, out, (const Cx<float> *)p->tabM,
-           (const Cx<float> *)p->twr, h, nbb, ep, p->ctr + 2, a);
-    PFB_CHECK_LAUNCH();
-    return pa ? primal_finish(p, grid, out2, st) : PFB_OK;
-}
 
-#define PFB_SIZE_SWITCH(n, CALL)                         \
-    switch (n) {                                         \
-    case 512: return CALL(512);                          \
-    case 1024: return CALL(1024);                        \
-    case 2048: return CALL(2048);                        \
-    case 4096: return CALL(4096);                        \
-    default: return fail(PFB_ERR_FFT_SIZE, "fast path: unsupported length %d", (int)(n)); \
-    }
 
 template <class T> static int fast_rows_fwd_d(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
     if (p->RB == 4) {
@@ -583,132 +407,9 @@ template <class T> static int fast_rows_fwd_d(pfb_hess_plan *p, const T *x, cons
     PFB_SIZE_SWITCH(p->h.M, PFB_C)
 #undef PFB_C
 }
-template <class T> static int fast_rows_inv_d(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st,
-                                              const PrimalArgsT<T> *pa = nullptr, double *out2 = nullptr) {
-    if (p->RB == 4) {
-#define PFB_C(N) fast_rows_inv<T, N, 4>(p, out, ep, st, pa, out2)
-        PFB_SIZE_SWITCH(p->h.M, PFB_C)
-#undef PFB_C
-    }
-#define PFB_C(N) fast_rows_inv<T, N, 2>(p, out, ep, st, pa, out2)
-    PFB_SIZE_SWITCH(p->h.M, PFB_C)
-#undef PFB_C
-}
 template <class T> static int fast_cols_d(pfb_hess_plan *p, cudaStream_t st) {
 #define PFB_C(N) fast_cols<T, N>(p, st)
     PFB_SIZE_SWITCH(p->h.nxp / 2, PFB_C)
-#undef PFB_C
-}
-
-// ---- odd factor x power of two (hess_peel.cuh)
-#define PFB_PEEL_SWITCH(n, CALL)                         \
-    switch (n) {                                         \
-    case 512: return CALL(512);                          \
-    case 1024: return CALL(1024);                        \
-    case 2048: return CALL(2048);                        \
-    case 4096: return CALL(4096);                        \
-    default: return fail(PFB_ERR_FFT_SIZE, "peeled transform: unsupported power of two %d", (int)(n)); \
-    }
-template <class T, int P2>
-static int peel_rows_fwd(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
-    HessDims h = p->h;
-    h.R = p->LrowP;
-    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R, p->inplR != 0);
-    const int nthr = p->inplR ? p->prow.m * (P2 / 16) : peel_threads(p->prow.m, P2, h.R);
-    PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_fwd<T, P2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    launch(&k_hessp_rows_fwd<T, P2>, dim3(cdiv(h.nx, h.R), h.nband), dim3(nthr), smem, st,
-           x, beam, (Cx<T> *)p->S, (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots,
-           (const Cx<T> *)p->ptabR, p->prow.m, p->inplR, h);
-    PFB_CHECK_LAUNCH();
-    return PFB_OK;
-}
-template <class T, int P2>
-static int peel_rows_inv(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
-    HessDims h = p->h;
-    h.R = p->LrowP;
-    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(h.M, p->prow.m, P2, h.R, p->inplR != 0);
-    const int nthr = p->inplR ? p->prow.m * (P2 / 16) : peel_threads(p->prow.m, P2, h.R);
-    PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_inv<T, P2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    launch(&k_hessp_rows_inv<T, P2, false>, dim3(cdiv(h.nx, h.R), h.nband), dim3(nthr), smem, st,
-           (const Cx<T> *)p->S, out, (const Cx<T> *)p->mtwM, (const Cx<T> *)p->twr, (const Cx<T> *)p->mroots,
-           (const Cx<T> *)p->ptabR, p->prow.m, p->inplR, h, ep, PeelPrimal());
-    PFB_CHECK_LAUNCH();
-    return PFB_OK;
-}
-#ifndef PFB_EMU
-// pass C with the primal step as its epilogue (fp32), then the fixed-order sum of the CTAs' eps terms
-template <int P2>
-static int peel_rows_inv_primal(pfb_hess_plan *p, PrimalArgs pa, double *out2, cudaStream_t st) {
-    HessDims h = p->h;
-    h.R = p->LrowP;
-    const size_t smem = sizeof(Cx<float>) * peel_smem_elems(h.M, p->prow.m, P2, h.R, p->inplR != 0);
-    const int nthr = p->inplR ? p->prow.m * (P2 / 16) : peel_threads(p->prow.m, P2, h.R);
-    const dim3 grid(cdiv(h.nx, h.R), h.nband);
-    pa.part = p->pd_partP;
-    PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_rows_inv<float, P2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    launch(&k_hessp_rows_inv<float, P2, true>, grid, dim3(nthr), smem, st,
-           (const Cx<float> *)p->S, (float *)nullptr, (const Cx<float> *)p->mtwM, (const Cx<float> *)p->twr,
-           (const Cx<float> *)p->mroots, (const Cx<float> *)p->ptabR, p->prow.m, p->inplR, h, Epilogue<float>(), pa);
-    PFB_CHECK_LAUNCH();
-    launch(&k_hess_red_final_wide, dim3(1), dim3(1024), 0, st, (const double *)p->pd_partP, (int)(grid.x * grid.y), out2);
-    PFB_CHECK_LAUNCH();
-    return PFB_OK;
-}
-static int peel_rows_inv_primal_d(pfb_hess_plan *p, const PrimalArgs &pa, double *out2, cudaStream_t st) {
-#define PFB_C(N) peel_rows_inv_primal<N>(p, pa, out2, st)
-    PFB_PEEL_SWITCH(p->prow.P2, PFB_C)
-#undef PFB_C
-}
-#endif
-template <class T, int P2>
-static int peel_cols(pfb_hess_plan *p, cudaStream_t st) {
-    const HessDims &h = p->h;
-    if (p->pcol2) {
-        const size_t smem2 = sizeof(Cx<T>) * peel_smem_elems_cols2(p->pcol.N, p->pcol.m, P2, p->split != 0);
-        const dim3 grid2(h.nyo2, h.nband), blk2(p->pcol.m * (P2 / 16));
-        if (p->split) {
-            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_cols2<T, P2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-            launch(&k_hessp_cols2<T, P2, true>, grid2, blk2, smem2, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
-                   (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, (const Cx<T> *)p->ptabC,
-                   p->pcol.m, h);
-        } else {
-            PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_cols2<T, P2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-            launch(&k_hessp_cols2<T, P2, false>, grid2, blk2, smem2, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
-                   (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, (const Cx<T> *)p->ptabC,
-                   p->pcol.m, h);
-        }
-        PFB_CHECK_LAUNCH();
-        return PFB_OK;
-    }
-    const size_t smem = sizeof(Cx<T>) * peel_smem_elems(p->pcol.N, p->pcol.m, P2, 1);
-    const dim3 grid(h.nyo2, h.nband), blk(peel_threads(p->pcol.m, P2, 1));
-    if (p->split) {
-        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_cols<T, P2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        launch(&k_hessp_cols<T, P2, true>, grid, blk, smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
-               (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, (const Cx<T> *)p->ptabC,
-               p->pcol.m, h);
-    } else {
-        PFB_CUDA_OK(cudaFuncSetAttribute(&k_hessp_cols<T, P2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        launch(&k_hessp_cols<T, P2, false>, grid, blk, smem, st, (Cx<T> *)p->S, (const Cx<T> *)p->psfT,
-               (const Cx<T> *)p->mtwC, (const Cx<T> *)p->modg, (const Cx<T> *)p->mroots, (const Cx<T> *)p->ptabC,
-               p->pcol.m, h);
-    }
-    PFB_CHECK_LAUNCH();
-    return PFB_OK;
-}
-template <class T> static int peel_rows_fwd_d(pfb_hess_plan *p, const T *x, const T *beam, cudaStream_t st) {
-#define PFB_C(N) peel_rows_fwd<T, N>(p, x, beam, st)
-    PFB_PEEL_SWITCH(p->prow.P2, PFB_C)
-#undef PFB_C
-}
-template <class T> static int peel_rows_inv_d(pfb_hess_plan *p, T *out, const Epilogue<T> &ep, cudaStream_t st) {
-#define PFB_C(N) peel_rows_inv<T, N>(p, out, ep, st)
-    PFB_PEEL_SWITCH(p->prow.P2, PFB_C)
-#undef PFB_C
-}
-template <class T> static int peel_cols_d(pfb_hess_plan *p, cudaStream_t st) {
-#define PFB_C(N) peel_cols<T, N>(p, st)
-    PFB_PEEL_SWITCH(p->pcol.P2, PFB_C)
 #undef PFB_C
 }
 

@@ -879,7 +879,7 @@ k_hessf_rows_inv_tma(const __grid_constant__ CUtensorMap tmS, float *__restrict_
 #endif  // !PFB_EMU
 
 // out2[j] = sum over the n CTAs of part[2 c + j], fixed order
-__global__ void k_hess_red_final(const double *__restrict__ part, int n, double *__restrict__ out2) {
+static __global__ void k_hess_red_final(const double *__restrict__ part, int n, double *__restrict__ out2) {
     double a0 = 0.0, a1 = 0.0;
     for (int c = threadIdx.x; c < n; c += 32) { a0 += part[2 * c]; a1 += part[2 * c + 1]; }
 #pragma unroll
@@ -890,7 +890,7 @@ __global__ void k_hess_red_final(const double *__restrict__ part, int n, double 
     if (threadIdx.x == 0) { out2[0] = a0; out2[1] = a1; }
 }
 // the same sum over many CTAs (one per row batch of the peeled pass C): 1024 threads, fixed order
-__global__ void __launch_bounds__(1024)
+static __global__ void __launch_bounds__(1024)
 k_hess_red_final_wide(const double *__restrict__ part, int n, double *__restrict__ out2) {
     __shared__ double s_red[2][32];
     double a0 = 0.0, a1 = 0.0;
